@@ -1,0 +1,200 @@
+"""ctypes binding of libcupt.so (include/cupt.h) — the Python face of the C-ABI used by tests and bench.
+
+There is no CPU fallback: everything that renders or traces goes through the CUDA kernels in libcupt.so
+and raises CuptError when the library or a CUDA device is missing.  Host-side entry points (scene ingest,
+the reference-layout BVH2, the wide-BVH builder, PPM output) work without a GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcupt.so")
+
+# numpy views of the reference PODs (sizes pinned in tests/test_abi.py)
+VEC3 = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4")])
+TRIANGLE = np.dtype([("v0", "<i4"), ("v1", "<i4"), ("v2", "<i4"), ("norm", "<f4", (3,)), ("mat", "<i4")])
+MATERIAL = np.dtype([("albedo", "<f8", (3,)), ("emission", "<f8", (3,))])
+CAMERA = np.dtype([("pos", "<f4", (3,)), ("distFromFilm", "<f4"), ("focalLength", "<f4"), ("radius", "<f4"),
+                   ("pxlWidth", "<i4"), ("pxlHeight", "<i4")])
+BVH2_NODE = np.dtype([("lo", "<f4", (3,)), ("hi", "<f4", (3,)), ("left", "<u4"), ("right", "<u4")])
+SPHERE = np.dtype([("pos", "<f4", (3,)), ("rad", "<f4"), ("diffuse", "<f8", (3,)), ("emm", "<f8", (3,))])
+assert (VEC3.itemsize, TRIANGLE.itemsize, MATERIAL.itemsize, CAMERA.itemsize, BVH2_NODE.itemsize, SPHERE.itemsize) == (12, 28, 48, 32, 32, 64)
+
+LEAF_FLAG = 0x80000000
+MAX_FLOAT = np.float32(100000.0)
+INTEGRATOR_PT, INTEGRATOR_BDPT = 2, 1
+TRAVERSAL_WIDE, TRAVERSAL_REF_BVH2 = 0, 1
+TRI_REFEXACT, TRI_WATERTIGHT = 0, 1
+
+
+class CuptError(RuntimeError):
+    pass
+
+
+class BvhOpts(C.Structure):
+    _fields_ = [("sah_bins", C.c_int), ("max_leaf_tris", C.c_int), ("threads", C.c_int), ("tie_rank", C.c_void_p)]
+
+
+class BvhInfo(C.Structure):
+    _fields_ = [("num_nodes", C.c_int64), ("num_tri_records", C.c_int64), ("num_tris", C.c_int64),
+                ("num_spheres", C.c_int64), ("depth", C.c_int32), ("node_bytes", C.c_int32), ("tri_bytes", C.c_int32),
+                ("sah_cost", C.c_double), ("build_seconds", C.c_double)]
+
+
+class RenderOpts(C.Structure):
+    _fields_ = [("max_depth", C.c_int32), ("integrator", C.c_int32), ("traversal", C.c_int32), ("tri_test", C.c_int32),
+                ("seed", C.c_uint64), ("samples_per_pass", C.c_int32), ("collect_stats", C.c_int32),
+                ("time_stages", C.c_int32), ("reserved", C.c_int32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("samples", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
+                ("kernel_launches", C.c_uint64), ("ms_raygen", C.c_double), ("ms_extend", C.c_double),
+                ("ms_shade", C.c_double), ("ms_accum", C.c_double), ("extend_launches", C.c_uint64)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None):
+    """dlopen libcupt.so (built in-tree by __graft_entry__.build()); fails loudly when it is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise CuptError(f"{p} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(there is no CPU or PyTorch fallback for the hot path)")
+    lib = C.CDLL(p, mode=C.RTLD_GLOBAL)
+    lib.cupt_last_error.restype = C.c_char_p
+    lib.cupt_scene_total_light_area.restype = C.c_float
+    lib.cupt_scene_total_light_area.argtypes = [C.c_void_p]
+    for name in ("cupt_scene_destroy", "cupt_bvh_destroy", "cupt_destroy", "cupt_bvh2_free"):
+        getattr(lib, name).restype = None
+        getattr(lib, name).argtypes = [C.c_void_p]
+    _lib = lib
+    return lib
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise CuptError(f"cupt error {rc}: {load_library().cupt_last_error().decode(errors='replace')}")
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def make_camera(width: int, height: int, pos=(0.0, 1.0, 3.0), distFromFilm=1.0, focalLength=3.0, radius=0.0) -> np.ndarray:
+    cam = np.zeros(1, dtype=CAMERA)
+    cam["pos"][0] = pos
+    cam["distFromFilm"], cam["focalLength"], cam["radius"] = distFromFilm, focalLength, radius
+    cam["pxlWidth"], cam["pxlHeight"] = width, height
+    return cam
+
+
+class SceneHandle:
+    """cupt_scene: the reference's globals verts/tris/mats/lights/totalLightArea (modelLoader.h:43-47)."""
+
+    def __init__(self):
+        self.lib = load_library()
+        h = C.c_void_p()
+        _check(self.lib.cupt_scene_create(C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            self.lib.cupt_scene_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def clear(self):
+        _check(self.lib.cupt_scene_clear(self.h))
+
+    def load_obj(self, path: str, mtl_dir: Optional[str] = None, origin=(0.0, 0.0, 0.0), scale: float = 1.0, flip: bool = False):
+        """loadOBJ(filename, origin, scale, flipNormals) — modelLoader.h:125"""
+        o = (C.c_float * 3)(*origin)
+        _check(self.lib.cupt_scene_load_obj(self.h, path.encode(), None if mtl_dir is None else mtl_dir.encode(),
+                                            o, C.c_float(scale), int(flip)))
+
+    def add_materials(self, mats: np.ndarray, duplicate_table: bool = True) -> int:
+        mats = np.ascontiguousarray(mats, dtype=MATERIAL)
+        first = C.c_int()
+        _check(self.lib.cupt_scene_add_materials(self.h, _ptr(mats), len(mats), int(duplicate_table), C.byref(first)))
+        return first.value
+
+    def add_shape(self, positions, indices, material: int, origin=(0.0, 0.0, 0.0), scale=1.0, flip=False):
+        positions = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 3)
+        indices = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1, 3)
+        o = (C.c_float * 3)(*origin)
+        _check(self.lib.cupt_scene_add_shape(self.h, _ptr(positions), len(positions), _ptr(indices), len(indices),
+                                             int(material), o, C.c_float(scale), int(flip)))
+
+    def add_scene(self, scene, origin=(0.0, 0.0, 0.0), scale=1.0, flip=False, duplicate_table=True):
+        """append a cudapathtracer_b200.scenes.Scene the way loadOBJ appends an OBJ file"""
+        mats = np.zeros(len(scene.materials), dtype=MATERIAL)
+        for i, (_, kd, ke) in enumerate(scene.materials):
+            mats["albedo"][i] = np.asarray(kd, dtype=np.float32)   # MTL values pass through float (tinyobj material_t)
+            mats["emission"][i] = np.asarray(ke, dtype=np.float32)
+        first = self.add_materials(mats, duplicate_table)
+        for sh in scene.shapes:
+            self.add_shape(sh.positions, sh.indices, sh.material + first, origin, scale, flip)
+
+    def add_spheres(self, spheres: np.ndarray):
+        spheres = np.ascontiguousarray(spheres, dtype=SPHERE)
+        _check(self.lib.cupt_scene_add_spheres(self.h, _ptr(spheres), len(spheres)))
+
+    def set_arrays(self, verts, tris, mats, lights, total_light_area: float):
+        verts = np.ascontiguousarray(verts, dtype=VEC3)
+        tris = np.ascontiguousarray(tris, dtype=TRIANGLE)
+        mats = np.ascontiguousarray(mats, dtype=MATERIAL)
+        lights = np.ascontiguousarray(lights, dtype=np.int32)
+        _check(self.lib.cupt_scene_set_arrays(self.h, _ptr(verts), len(verts), _ptr(tris), len(tris), _ptr(mats), len(mats),
+                                              _ptr(lights), len(lights), C.c_float(total_light_area)))
+
+    def counts(self):
+        out = (C.c_int * 5)()
+        _check(self.lib.cupt_scene_counts(self.h, out))
+        return tuple(out)
+
+    @property
+    def total_light_area(self) -> np.float32:
+        return np.float32(self.lib.cupt_scene_total_light_area(self.h))
+
+    def arrays(self):
+        nv, nt, nm, nl, _ = self.counts()
+        verts, tris = np.zeros(nv, dtype=VEC3), np.zeros(nt, dtype=TRIANGLE)
+        mats, lights = np.zeros(nm, dtype=MATERIAL), np.zeros(nl, dtype=np.int32)
+        _check(self.lib.cupt_scene_get_arrays(self.h, _ptr(verts), _ptr(tris), _ptr(mats), _ptr(lights)))
+        return verts, tris, mats, lights
+
+    def build_bvh2(self):
+        """buildBVH() — BVH.h:443: returns (nodes[BVH2_NODE], depth)"""
+        p, size, depth = C.c_void_p(), C.c_int(), C.c_int()
+        _check(self.lib.cupt_bvh2_build(self.h, C.byref(p), C.byref(size), C.byref(depth)))
+        try:
+            buf = (C.c_char * (size.value * BVH2_NODE.itemsize)).from_address(p.value)
+            nodes = np.frombuffer(buf, dtype=BVH2_NODE).copy()
+        finally:
+            self.lib.cupt_bvh2_free(p)
+        return nodes, depth.value
+
+    def build_bvh(self, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None) -> "BvhHandle":
+        return BvhHandle(self, sah_bins, max_leaf_tris, threads, tie_rank)
+
+
+def bvh2_leaf_order(nodes: np.ndarray, ntris: int) -> np.ndarray:
+    lib = load_library()
+    nodes = np.ascontiguousarray(nodes, dtype=BVH2_NODE)
+    rank = np.zeros(ntris, dtype=np.uint32)
+    _check(lib.cupt_bvh2_leaf_order(_ptr(nodes), len(nodes), ntris, _ptr(rank)))
+    return rank

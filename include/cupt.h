@@ -1,0 +1,198 @@
+/* cupt.h — C-ABI of the B200-native path-tracing hot path (drop-in for CulDeVu/CUDAPathTracer's render loop).
+ *
+ * The reference has no FFI: its "API" is the set of PODs, globals and free functions that main()
+ * (reference kernel.cu:565-790) uses inside one translation unit.  Every entry point below names the
+ * reference interface it replaces (file:line relative to the reference tree).  All functions return
+ * 0 on success and a negative cupt_status on failure (the reference printf()s and continues,
+ * kernel.cu:37-42, or exit(0)s, BVH.h:339-340; this library never exits and never throws across
+ * the ABI); cupt_last_error() gives the message for the calling thread.
+ *
+ * Signatures carry plain pointers and sizes only.  POD layouts are byte-identical to the reference's
+ * (sizes pinned by tests/test_abi.py against the reference compiled in oracle/_ref).
+ */
+#ifndef CUPT_H
+#define CUPT_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CUPT_VERSION 100
+
+typedef enum cupt_status {
+	CUPT_OK = 0,
+	CUPT_ERR_INVALID = -1,   /* bad argument / bad call order */
+	CUPT_ERR_CUDA = -2,      /* CUDA runtime error (message carries cudaGetErrorString) */
+	CUPT_ERR_NO_DEVICE = -3, /* no CUDA device: there is NO CPU fallback */
+	CUPT_ERR_IO = -4,        /* file could not be opened / written */
+	CUPT_ERR_PARSE = -5,     /* OBJ / MTL parse error */
+	CUPT_ERR_LIMIT = -6,     /* BVH depth / index limit (kernel.cu:627-631, BVH.h:337-341) */
+	CUPT_ERR_NOMEM = -7
+} cupt_status;
+
+/* ---- PODs, byte-identical to the reference ---------------------------------------------------- */
+typedef struct cupt_vec3 { float x, y, z; } cupt_vec3;                       /* vec3.h:4-8, 12 B   */
+typedef struct cupt_triangle {                                               /* modelLoader.h:14-19, 28 B */
+	int32_t v0, v1, v2;
+	cupt_vec3 norm;
+	int32_t mat;
+} cupt_triangle;
+typedef struct cupt_material {                                               /* modelLoader.h:21-25 + color.h:4-6, 48 B */
+	double albedo[3];
+	double emission[3];   /* the reference spells it `emmision` */
+} cupt_material;
+typedef struct cupt_camera {                                                 /* camera.h:26-35, 32 B */
+	cupt_vec3 pos;
+	float distFromFilm, focalLength, radius;
+	int32_t pxlWidth, pxlHeight;
+} cupt_camera;
+typedef struct cupt_bvh2_node {                                              /* BVH.h:111-115, 32 B */
+	cupt_vec3 lo, hi;
+	uint32_t left, right;   /* inner index, or triangle | CUPT_BVH_LEAF_FLAG (limits.h:7) */
+} cupt_bvh2_node;
+typedef struct cupt_sphere {                                                 /* sphere.h:7-13, 64 B */
+	cupt_vec3 pos;
+	float rad;
+	double diffuse[3];
+	double emm[3];
+} cupt_sphere;
+
+#define CUPT_BVH_LEAF_FLAG 0x80000000u   /* limits.h:7 */
+#define CUPT_MAX_BVH_INDEX 0x7fffffffu   /* limits.h:6 */
+#define CUPT_MAX_FLOAT 100000.0f         /* limits.h:3 — the reference's "infinity": miss = {id -1, t 1e5} */
+#define CUPT_MAX_BVH2_DEPTH 64           /* kernel.cu:35 */
+
+typedef struct cupt_scene cupt_scene;       /* host scene: the reference's globals verts/tris/mats/lights/totalLightArea (modelLoader.h:43-47) */
+typedef struct cupt_bvh cupt_bvh;           /* host image of the wide quantised BVH (replaces BVH.h:133-474) */
+typedef struct cupt_context cupt_context;   /* one per GPU: device scene, BVH, wavefront state, accumulator */
+
+const char* cupt_last_error(void);
+int cupt_version(void);
+/* sizes of the PODs above as compiled into the library, in declaration order (7 values) */
+int cupt_struct_sizes(int* out7);
+
+/* ---- scene ingest (host) — replaces loadOBJ + the globals, modelLoader.h:43-47,125-210 -------- */
+int cupt_scene_create(cupt_scene** out);
+void cupt_scene_destroy(cupt_scene* s);
+int cupt_scene_clear(cupt_scene* s);
+/* loadOBJ(filename, origin, scale, flipNormals) — modelLoader.h:125.  `mtl_dir` is the MTL base path the
+ * reference hard-codes as "models/" (modelLoader.h:132); NULL means "models/".  Appends, like the reference. */
+int cupt_scene_load_obj(cupt_scene* s, const char* path, const char* mtl_dir,
+                        const float origin[3], float scale, int flip_normals);
+/* the same append for an in-memory shape: materials first (appended twice like modelLoader.h:138-159 when
+ * duplicate_table != 0), then one call per shape with ONE material per shape (modelLoader.h:189). */
+int cupt_scene_add_materials(cupt_scene* s, const cupt_material* mats, int n, int duplicate_table, int* first_index);
+int cupt_scene_add_shape(cupt_scene* s, const float* positions, int nverts, const uint32_t* indices, int ntris,
+                         int material, const float origin[3], float scale, int flip_normals);
+/* per-face materials: like add_shape with material taken per triangle */
+int cupt_scene_add_shape_facemats(cupt_scene* s, const float* positions, int nverts, const uint32_t* indices,
+                                  int ntris, const int32_t* face_materials, const float origin[3], float scale,
+                                  int flip_normals);
+/* spheres: sphere.h:7-13 has the POD only; the intersector is new (parity unpinned) */
+int cupt_scene_add_spheres(cupt_scene* s, const cupt_sphere* spheres, int n);
+/* raw access to the arrays in reference layout */
+int cupt_scene_set_arrays(cupt_scene* s, const cupt_vec3* verts, int nverts, const cupt_triangle* tris, int ntris,
+                          const cupt_material* mats, int nmats, const int32_t* lights, int nlights,
+                          float total_light_area);
+int cupt_scene_counts(const cupt_scene* s, int* out5 /* verts, tris, mats, lights, spheres */);
+int cupt_scene_get_arrays(const cupt_scene* s, cupt_vec3* verts, cupt_triangle* tris, cupt_material* mats,
+                          int32_t* lights);
+float cupt_scene_total_light_area(const cupt_scene* s);
+
+/* ---- reference-layout BVH2 — buildBVH(), BVH.h:443-474 (compatibility + tie-break ranks) ------- */
+/* Returns a malloc'ed BVH_array{root,size,depth} image; reproduces the 3x3x3 grid heuristic bit for bit. */
+int cupt_bvh2_build(const cupt_scene* s, cupt_bvh2_node** nodes, int* size, int* depth);
+void cupt_bvh2_free(cupt_bvh2_node* nodes);
+/* rank[tri] = position of tri in the left-first leaf order of trace() (kernel.cu:139-151): the reference's
+ * tie-break (`t < closestT` strict, kernel.cu:127) expressed so any other tree can reproduce it. */
+int cupt_bvh2_leaf_order(const cupt_bvh2_node* nodes, int size, int ntris, uint32_t* rank);
+
+/* ---- wide BVH (host build) — replaces BVH.h:133-328 -------------------------------------------- */
+typedef struct cupt_bvh_opts {
+	int sah_bins;          /* bins per axis of the binned-SAH BVH2 builder (default 32) */
+	int max_leaf_tris;     /* triangles per BVH8 child leaf, 1..3 (default 3) */
+	int threads;           /* host threads, 0 = all */
+	const uint32_t* tie_rank;  /* optional rank per triangle (cupt_bvh2_leaf_order); NULL = triangle index */
+} cupt_bvh_opts;
+typedef struct cupt_bvh_info {
+	int64_t num_nodes;       /* 80-byte BVH8 nodes */
+	int64_t num_tri_records; /* 48-byte triangle records */
+	int64_t num_tris, num_spheres;
+	int32_t depth;
+	int32_t node_bytes, tri_bytes;
+	double sah_cost;
+	double build_seconds;
+} cupt_bvh_info;
+int cupt_bvh_build(const cupt_scene* s, const cupt_bvh_opts* opts, cupt_bvh** out);
+void cupt_bvh_destroy(cupt_bvh* b);
+int cupt_bvh_get_info(const cupt_bvh* b, cupt_bvh_info* info);
+/* raw images (for tests: structural invariants are checked on the host) */
+int cupt_bvh_get_arrays(const cupt_bvh* b, void* nodes80, void* tris48);
+
+/* ---- device context — replaces the cudaMalloc/cudaMemcpy block, kernel.cu:633-700 -------------- */
+int cupt_create(int device, cupt_context** out);
+void cupt_destroy(cupt_context* c);
+int cupt_set_stream(cupt_context* c, void* cuda_stream);          /* default: a stream owned by the context */
+int cupt_set_scene(cupt_context* c, const cupt_scene* s);         /* kernel.cu:664-684 */
+int cupt_set_bvh(cupt_context* c, const cupt_bvh* b);             /* kernel.cu:686-691 (wide layout) */
+int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int depth); /* kernel.cu:686-691 verbatim */
+int cupt_set_camera(cupt_context* c, const cupt_camera* cam);     /* kernel.cu:642-651 */
+
+enum { CUPT_INTEGRATOR_PT = 2 /* radianceAlongSingleStep2, kernel.cu:417-515 */,
+       CUPT_INTEGRATOR_BDPT = 1 /* radianceAlongSingleStep, kernel.cu:217-415 */ };
+enum { CUPT_TRAVERSAL_WIDE = 0, CUPT_TRAVERSAL_REF_BVH2 = 1 /* trace(), kernel.cu:112-161 op for op */ };
+enum { CUPT_TRI_REFEXACT = 0 /* triIntersect, modelLoader.h:49-82, bit-identical */, CUPT_TRI_WATERTIGHT = 1 };
+
+typedef struct cupt_render_opts {
+	int32_t max_depth;        /* NUM_BOUNCES (kernel.cu:33) made run-time: path segments per sample */
+	int32_t integrator;       /* CUPT_INTEGRATOR_* */
+	int32_t traversal;        /* CUPT_TRAVERSAL_* */
+	int32_t tri_test;         /* CUPT_TRI_* */
+	uint64_t seed;            /* kernel.cu:532 uses 1234 */
+	int32_t samples_per_pass; /* samples of every pixel in flight per wavefront pass (0 = auto) */
+	int32_t collect_stats;    /* 1: count node visits / triangle tests (slower; for the roofline's bytes/ray) */
+	int32_t time_stages;      /* 1: CUDA events around every stage launch */
+	int32_t reserved;
+} cupt_render_opts;
+int cupt_default_render_opts(cupt_render_opts* o);
+int cupt_set_render_opts(cupt_context* c, const cupt_render_opts* o);
+
+/* drawPixel<<<>>> loop, kernel.cu:709-736: adds samples [first_sample, first_sample+num_samples) of every
+ * pixel to the float sum accumulator.  Asynchronous on the context's stream. */
+int cupt_render(cupt_context* c, int first_sample, int num_samples);
+int cupt_sync(cupt_context* c);                                   /* cudaDeviceSynchronize, kernel.cu:716 */
+int cupt_reset_accum(cupt_context* c);                            /* setupImgBuffer, kernel.cu:520-526 */
+/* image readback, kernel.cu:760: row-major P*3 floats; normalise != 0 divides by the samples accumulated */
+int cupt_read_accum(cupt_context* c, float* rgb_host, int normalise);
+/* device-side view of the accumulator (P*3 f32 sums) for the multi-GPU reduce: copies into caller memory */
+int cupt_copy_accum_device(cupt_context* c, float* dst_device);
+int cupt_add_accum_device(cupt_context* c, const float* src_device, int samples);
+/* parity hooks: primary hit triangle id and raw t per pixel (row-major), and closest hits for caller rays */
+int cupt_read_primary_hits(cupt_context* c, int32_t* tri_id, float* t);
+int cupt_trace_rays(cupt_context* c, const float* rays_host /* n*6: o, dir */, int64_t n, int32_t* tri_id, float* t);
+int cupt_camera_rays(cupt_context* c, float* rays_host /* P*6 */);
+
+typedef struct cupt_stats {
+	uint64_t rays;            /* extend invocations (one ray = one trace(), counted not nominal) */
+	uint64_t samples;         /* pixel-samples started */
+	uint64_t nodes_visited;   /* wide-node fetches (collect_stats) */
+	uint64_t tris_tested;     /* triangle records fetched (collect_stats) */
+	uint64_t kernel_launches; /* launches of this library's kernels */
+	double ms_raygen, ms_extend, ms_shade, ms_accum;  /* time_stages */
+	uint64_t extend_launches;
+} cupt_stats;
+int cupt_get_stats(cupt_context* c, cupt_stats* out);
+int cupt_reset_stats(cupt_context* c);
+
+/* ---- output — kernel.cu:763-778 ------------------------------------------------------------------ */
+/* P3 PPM: x mirrored, Reinhard c/(c+1) (color.h:59-62), gamma 1/2.2 (color.h:68-71), (int)(c*255) truncation */
+int cupt_write_ppm(const char* path, const float* rgb_mean, int width, int height);
+int cupt_tonemap(const float* rgb_mean, int64_t npixels, int32_t* out_rgb255);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CUPT_H */
