@@ -1,0 +1,103 @@
+"""TEST INFRASTRUCTURE: ctypes binding of oracle/liboracle.so (the C restatement, oracle/oracle.c).
+Only tests/, bench.py's cpu_baseline / reference arm and __graft_entry__.smoke() may import this."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from cudapathtracer_b200.api import BVH2_NODE, CAMERA, MATERIAL, TRIANGLE, VEC3
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
+
+
+class _Scene(C.Structure):
+    _fields_ = [("verts", C.c_void_p), ("tris", C.c_void_p), ("mats", C.c_void_p), ("lights", C.c_void_p),
+                ("numVerts", C.c_int32), ("numTris", C.c_int32), ("numMats", C.c_int32), ("numLights", C.c_int32),
+                ("totalLightArea", C.c_float), ("nodes", C.c_void_p), ("numNodes", C.c_int32)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        l = C.CDLL(ORACLE_SO)
+        l.orc_render_pt.restype = C.c_ulonglong
+        _lib = l
+    return _lib
+
+
+def available() -> bool:
+    return os.path.exists(ORACLE_SO)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class OracleScene:
+    """scene arrays in reference layout + a reference-layout BVH2 node array"""
+
+    def __init__(self, verts, tris, mats, lights, total_light_area, nodes):
+        self.verts = np.ascontiguousarray(verts, dtype=VEC3)
+        self.tris = np.ascontiguousarray(tris, dtype=TRIANGLE)
+        self.mats = np.ascontiguousarray(mats, dtype=MATERIAL)
+        self.lights = np.ascontiguousarray(lights, dtype=np.int32)
+        self.nodes = np.ascontiguousarray(nodes, dtype=BVH2_NODE)
+        self.c = _Scene(self.verts.ctypes.data, self.tris.ctypes.data, self.mats.ctypes.data, self.lights.ctypes.data,
+                        len(self.verts), len(self.tris), len(self.mats), len(self.lights),
+                        float(total_light_area), self.nodes.ctypes.data, len(self.nodes))
+
+    def camera_rays(self, cam, u1=0.5, u2=0.5):
+        cam = np.ascontiguousarray(cam, dtype=CAMERA)
+        n = int(cam["pxlWidth"][0]) * int(cam["pxlHeight"][0])
+        rays = np.zeros((n, 6), dtype=np.float32)
+        lib().orc_camera_rays(_p(cam), C.c_float(u1), C.c_float(u2), _p(rays))
+        return rays
+
+    def primary_hits(self, cam, u1=0.5, u2=0.5):
+        cam = np.ascontiguousarray(cam, dtype=CAMERA)
+        n = int(cam["pxlWidth"][0]) * int(cam["pxlHeight"][0])
+        ids, ts = np.zeros(n, dtype=np.int32), np.zeros(n, dtype=np.float32)
+        lib().orc_primary_hits(C.byref(self.c), _p(cam), C.c_float(u1), C.c_float(u2), _p(ids), _p(ts))
+        return ids, ts
+
+    def trace_rays(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        ids, ts = np.zeros(len(rays), dtype=np.int32), np.zeros(len(rays), dtype=np.float32)
+        lib().orc_trace_rays(C.byref(self.c), _p(rays), C.c_longlong(len(rays)), _p(ids), _p(ts))
+        return ids, ts
+
+    def brute_force(self, rays, rank=None):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        if rank is not None:
+            rank = np.ascontiguousarray(rank, dtype=np.uint32)
+        ids, ts = np.zeros(len(rays), dtype=np.int32), np.zeros(len(rays), dtype=np.float32)
+        lib().orc_brute_force(C.byref(self.c), _p(rank), _p(rays), C.c_longlong(len(rays)), _p(ids), _p(ts))
+        return ids, ts
+
+    def render_pt(self, cam, num_bounces=5, seed=1234, first_sample=0, num_samples=1):
+        """(mean[P,3] f64, sum[P,3] f64, rays)"""
+        cam = np.ascontiguousarray(cam, dtype=CAMERA)
+        n = int(cam["pxlWidth"][0]) * int(cam["pxlHeight"][0])
+        mean, ssum = np.zeros((n, 3)), np.zeros((n, 3))
+        rays = lib().orc_render_pt(C.byref(self.c), _p(cam), num_bounces, C.c_uint64(seed), first_sample, num_samples,
+                                   _p(mean), _p(ssum))
+        return mean, ssum, int(rays)
+
+
+def philox_uniforms(seed, x, y, sample, n):
+    out = np.zeros(n, dtype=np.float32)
+    lib().orc_philox_uniforms(C.c_uint64(seed), x, y, sample, n, _p(out))
+    return out
+
+
+def tonemap(rgb):
+    rgb = np.ascontiguousarray(rgb, dtype=np.float64).reshape(-1, 3)
+    out = np.zeros((len(rgb), 3), dtype=np.int32)
+    lib().orc_tonemap(_p(rgb), C.c_longlong(len(rgb)), _p(out))
+    return out
