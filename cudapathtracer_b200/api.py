@@ -198,3 +198,150 @@ def bvh2_leaf_order(nodes: np.ndarray, ntris: int) -> np.ndarray:
     rank = np.zeros(ntris, dtype=np.uint32)
     _check(lib.cupt_bvh2_leaf_order(_ptr(nodes), len(nodes), ntris, _ptr(rank)))
     return rank
+
+
+NODE8 = np.dtype([("p", "<f4", (3,)), ("e", "u1", (3,)), ("imask", "u1"), ("child_base", "<u4"), ("tri_base", "<u4"),
+                  ("meta", "u1", (8,)), ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])
+PRIM48 = np.dtype([("a", "<f4", (3,)), ("b", "<f4", (3,)), ("c", "<f4", (3,)), ("id", "<u4"), ("rank", "<u4"), ("kind", "<u4")])
+assert NODE8.itemsize == 80 and PRIM48.itemsize == 48
+
+
+class BvhHandle:
+    """cupt_bvh: host image of the 8-wide quantised BVH (replaces buildBVH, BVH.h:443-474)."""
+
+    def __init__(self, scene: SceneHandle, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None):
+        self.lib = load_library()
+        self._rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, dtype=np.uint32)
+        opts = BvhOpts(sah_bins, max_leaf_tris, threads, None if self._rank is None else self._rank.ctypes.data)
+        h = C.c_void_p()
+        _check(self.lib.cupt_bvh_build(scene.h, C.byref(opts), C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            self.lib.cupt_bvh_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def info(self) -> dict:
+        i = BvhInfo()
+        _check(self.lib.cupt_bvh_get_info(self.h, C.byref(i)))
+        return {n: getattr(i, n) for n, _ in BvhInfo._fields_}
+
+    def arrays(self):
+        i = self.info()
+        nodes = np.zeros(i["num_nodes"], dtype=NODE8)
+        prims = np.zeros(i["num_tri_records"], dtype=PRIM48)
+        _check(self.lib.cupt_bvh_get_arrays(self.h, _ptr(nodes), _ptr(prims)))
+        return nodes, prims
+
+
+class Context:
+    """cupt_context: one GPU.  Mirrors the reference's main() flow (kernel.cu:633-761): set_scene / set_bvh /
+    set_camera once, render(first_sample, n) any number of times, read_accum()."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        _check(self.lib.cupt_create(device, C.byref(h)))
+        self.h = h
+        self.opts = RenderOpts()
+        _check(self.lib.cupt_default_render_opts(C.byref(self.opts)))
+        self._cam = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.cupt_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def set_stream(self, cuda_stream: int):
+        _check(self.lib.cupt_set_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def set_scene(self, scene: SceneHandle):
+        _check(self.lib.cupt_set_scene(self.h, scene.h))
+
+    def set_bvh(self, bvh: BvhHandle):
+        _check(self.lib.cupt_set_bvh(self.h, bvh.h))
+
+    def set_bvh2(self, nodes: np.ndarray, depth: int):
+        nodes = np.ascontiguousarray(nodes, dtype=BVH2_NODE)
+        _check(self.lib.cupt_set_bvh2(self.h, _ptr(nodes), len(nodes), depth))
+
+    def set_camera(self, cam: np.ndarray):
+        self._cam = np.ascontiguousarray(cam, dtype=CAMERA)
+        _check(self.lib.cupt_set_camera(self.h, _ptr(self._cam)))
+
+    def set_options(self, **kw):
+        for k, v in kw.items():
+            if not hasattr(self.opts, k):
+                raise AttributeError(k)
+            setattr(self.opts, k, v)
+        _check(self.lib.cupt_set_render_opts(self.h, C.byref(self.opts)))
+
+    @property
+    def shape(self):
+        return int(self._cam["pxlHeight"][0]), int(self._cam["pxlWidth"][0])
+
+    def render(self, first_sample: int, num_samples: int):
+        _check(self.lib.cupt_render(self.h, first_sample, num_samples))
+
+    def sync(self):
+        _check(self.lib.cupt_sync(self.h))
+
+    def reset_accum(self):
+        _check(self.lib.cupt_reset_accum(self.h))
+
+    def read_accum(self, normalise: bool = True, out: Optional[np.ndarray] = None) -> np.ndarray:
+        h, w = self.shape
+        if out is None:
+            out = np.empty((h * w, 3), dtype=np.float32)
+        _check(self.lib.cupt_read_accum(self.h, _ptr(out), int(normalise)))
+        return out
+
+    def copy_accum_device(self, dst_ptr: int):
+        _check(self.lib.cupt_copy_accum_device(self.h, C.c_void_p(dst_ptr)))
+
+    def add_accum_device(self, src_ptr: int, samples: int):
+        _check(self.lib.cupt_add_accum_device(self.h, C.c_void_p(src_ptr), samples))
+
+    def primary_hits(self):
+        h, w = self.shape
+        ids, ts = np.empty(h * w, dtype=np.int32), np.empty(h * w, dtype=np.float32)
+        _check(self.lib.cupt_read_primary_hits(self.h, _ptr(ids), _ptr(ts)))
+        return ids, ts
+
+    def camera_rays(self):
+        h, w = self.shape
+        rays = np.empty((h * w, 6), dtype=np.float32)
+        _check(self.lib.cupt_camera_rays(self.h, _ptr(rays)))
+        return rays
+
+    def trace_rays(self, rays: np.ndarray):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        ids, ts = np.empty(len(rays), dtype=np.int32), np.empty(len(rays), dtype=np.float32)
+        _check(self.lib.cupt_trace_rays(self.h, _ptr(rays), C.c_int64(len(rays)), _ptr(ids), _ptr(ts)))
+        return ids, ts
+
+    def stats(self) -> dict:
+        s = Stats()
+        _check(self.lib.cupt_get_stats(self.h, C.byref(s)))
+        return s.as_dict()
+
+    def reset_stats(self):
+        _check(self.lib.cupt_reset_stats(self.h))
+
+
+def write_ppm(path: str, rgb_mean: np.ndarray, width: int, height: int):
+    """kernel.cu:763-778"""
+    rgb_mean = np.ascontiguousarray(rgb_mean, dtype=np.float32)
+    _check(load_library().cupt_write_ppm(path.encode(), _ptr(rgb_mean), width, height))
+
+
+def tonemap(rgb_mean: np.ndarray) -> np.ndarray:
+    rgb_mean = np.ascontiguousarray(rgb_mean, dtype=np.float32).reshape(-1, 3)
+    out = np.empty((len(rgb_mean), 3), dtype=np.int32)
+    _check(load_library().cupt_tonemap(_ptr(rgb_mean), C.c_int64(len(rgb_mean)), _ptr(out)))
+    return out

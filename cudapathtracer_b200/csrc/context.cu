@@ -1,0 +1,553 @@
+// Device context and the render loop behind the C-ABI (include/cupt.h): the replacement of the
+// cudaMalloc/cudaMemcpy block and the per-sample launch loop of the reference's main() (kernel.cu:633-761).
+// One context per GPU; every launch goes to the context's stream; nothing here synchronises the device except
+// cupt_sync and the read-back calls.  There is no CPU fallback: without a CUDA device cupt_create fails.
+#include "host_common.h"
+#include "layout.h"
+#include "kernels.cuh"
+#include <algorithm>
+#include <cstring>
+
+using namespace cupt;
+
+#define CK(call)                                                                                           \
+	do {                                                                                                   \
+		cudaError_t e_ = (call);                                                                           \
+		if (e_ != cudaSuccess)                                                                             \
+			return set_error(CUPT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+	} while (0)
+
+struct StageEvent {
+	cudaEvent_t a, b;
+	int stage;  // 0 raygen, 1 extend, 2 shade, 3 accumulate
+};
+
+struct cupt_context {
+	int device = 0, num_sms = 0;
+	cudaStream_t stream = nullptr;
+	bool own_stream = false;
+	// scene
+	float* d_verts = nullptr; cupt_triangle* d_tris = nullptr; float4* d_trishade = nullptr; float4* d_mats = nullptr;
+	float4* d_lights = nullptr;
+	int64_t num_tris = 0; int num_lights = 0; float total_light_area = 0.f;
+	// acceleration structures
+	uint4* d_nodes = nullptr; float4* d_prims = nullptr; int bvh_depth = 0; int64_t num_nodes = 0, num_prims = 0;
+	cupt_bvh2_node* d_bvh2 = nullptr; int bvh2_size = 0, bvh2_depth = 0;
+	// camera / options
+	cupt_camera cam{}; bool have_cam = false;
+	cupt_render_opts opts{};
+	// wavefront state
+	PathBuffers pb{}; size_t path_capacity = 0;
+	float* d_accum = nullptr; size_t accum_pixels = 0; uint64_t samples_accumulated = 0;
+	// bookkeeping
+	uint64_t launches = 0, extend_launches = 0;
+	double ms[4] = {0, 0, 0, 0};
+	std::vector<StageEvent> pending, pool;
+	int extend_blocks[2] = {0, 0};
+};
+
+namespace {
+
+template <class T>
+int upload(T** dst, const void* src, size_t bytes, cudaStream_t st)
+{
+	if (*dst) { CK(cudaFree(*dst)); *dst = nullptr; }
+	if (bytes == 0) return CUPT_OK;
+	CK(cudaMalloc((void**)dst, bytes));
+	CK(cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, st));
+	CK(cudaStreamSynchronize(st));  // the host staging buffers are temporaries
+	return CUPT_OK;
+}
+
+int ensure_paths(cupt_context* c, size_t n)
+{
+	if (n <= c->path_capacity) return CUPT_OK;
+	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
+	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]);
+	c->pb.rayA = c->pb.rayB = c->pb.st0 = c->pb.st1 = nullptr; c->pb.queue[0] = c->pb.queue[1] = nullptr;
+	c->path_capacity = 0;
+	CK(cudaMalloc((void**)&c->pb.rayA, n * sizeof(float4)));
+	CK(cudaMalloc((void**)&c->pb.rayB, n * sizeof(float4)));
+	CK(cudaMalloc((void**)&c->pb.st0, n * sizeof(float4)));
+	CK(cudaMalloc((void**)&c->pb.st1, n * sizeof(float4)));
+	CK(cudaMalloc((void**)&c->pb.queue[0], n * sizeof(uint32_t)));
+	CK(cudaMalloc((void**)&c->pb.queue[1], n * sizeof(uint32_t)));
+	c->path_capacity = n;
+	return CUPT_OK;
+}
+
+int ensure_accum(cupt_context* c)
+{
+	const size_t P = (size_t)c->cam.pxlWidth * c->cam.pxlHeight;
+	if (c->d_accum && c->accum_pixels == P) return CUPT_OK;
+	if (c->d_accum) { CK(cudaFree(c->d_accum)); c->d_accum = nullptr; }
+	CK(cudaMalloc((void**)&c->d_accum, P * 3 * sizeof(float)));
+	CK(cudaMemsetAsync(c->d_accum, 0, P * 3 * sizeof(float), c->stream));
+	c->accum_pixels = P;
+	c->samples_accumulated = 0;
+	return CUPT_OK;
+}
+
+void stage_begin(cupt_context* c, int stage, StageEvent& ev)
+{
+	if (!c->opts.time_stages) return;
+	if (!c->pool.empty()) { ev = c->pool.back(); c->pool.pop_back(); }
+	else { cudaEventCreate(&ev.a); cudaEventCreate(&ev.b); }
+	ev.stage = stage;
+	cudaEventRecord(ev.a, c->stream);
+}
+void stage_end(cupt_context* c, StageEvent& ev)
+{
+	if (!c->opts.time_stages) return;
+	cudaEventRecord(ev.b, c->stream);
+	c->pending.push_back(ev);
+}
+void drain_events(cupt_context* c)
+{
+	for (StageEvent& ev : c->pending) {
+		float ms = 0.f;
+		if (cudaEventSynchronize(ev.b) == cudaSuccess && cudaEventElapsedTime(&ms, ev.a, ev.b) == cudaSuccess)
+			c->ms[ev.stage] += ms;
+		c->pool.push_back(ev);
+	}
+	c->pending.clear();
+}
+
+PassParams make_pass(const cupt_context* c, int first_sample, int samples, int fixed_lens)
+{
+	PassParams pp;
+	pp.cam = c->cam;
+	pp.seed = c->opts.seed;
+	pp.first_sample = first_sample;
+	pp.samples = samples;
+	pp.tiles_x = (c->cam.pxlWidth + 7) / 8;
+	pp.tiles_y = (c->cam.pxlHeight + 3) / 4;
+	pp.p_pad = pp.tiles_x * pp.tiles_y * 32;
+	pp.max_depth = c->opts.max_depth;
+	pp.fixed_lens = fixed_lens;
+	return pp;
+}
+
+DevScene make_scene(const cupt_context* c)
+{
+	DevScene sc;
+	sc.nodes = c->d_nodes; sc.prims = c->d_prims; sc.bvh2 = c->d_bvh2; sc.verts = c->d_verts; sc.tris = c->d_tris;
+	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.lights = c->d_lights;
+	sc.numLights = c->num_lights; sc.totalLightArea = c->total_light_area;
+	sc.stack_cap = std::max(c->bvh_depth, 1);
+	return sc;
+}
+
+int check_ready(const cupt_context* c, bool need_shading)
+{
+	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
+	if (!c->have_cam) return set_error(CUPT_ERR_INVALID, "no camera set (cupt_set_camera)");
+	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE && !c->d_nodes) return set_error(CUPT_ERR_INVALID, "no wide BVH set (cupt_set_bvh)");
+	if (c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 && (!c->d_bvh2 || !c->d_tris)) return set_error(CUPT_ERR_INVALID, "no reference BVH2 / scene set");
+	if (need_shading && !c->d_trishade) return set_error(CUPT_ERR_INVALID, "no scene set (cupt_set_scene)");
+	return CUPT_OK;
+}
+
+// persistent launch of the extend stage for queue `depth`
+int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
+{
+	const int mode = c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 ? 1 : 0;
+	const bool stats = c->opts.collect_stats != 0;
+	const size_t smem = mode == 0 ? (size_t)sc.stack_cap * 128 * sizeof(uint2) : 0;
+	void (*kern)(DevScene, PathBuffers, int, int) =
+		mode == 0 ? (stats ? k_extend<0, true> : k_extend<0, false>) : (stats ? k_extend<1, true> : k_extend<1, false>);
+	if (c->extend_blocks[mode] == 0 || mode == 0) {
+		if (smem > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		int per_sm = 0;
+		CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+		c->extend_blocks[mode] = std::max(1, per_sm) * c->num_sms;
+	}
+	StageEvent ev;
+	stage_begin(c, 1, ev);
+	kern<<<c->extend_blocks[mode], 128, smem, c->stream>>>(sc, c->pb, depth, qsel);
+	stage_end(c, ev);
+	CK(cudaGetLastError());
+	c->launches++; c->extend_launches++;
+	return CUPT_OK;
+}
+
+__global__ void k_add(float* __restrict__ dst, const float* __restrict__ src, size_t n)
+{
+	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) dst[i] += src[i];
+}
+
+}  // namespace
+
+extern "C" {
+
+int cupt_create(int device, cupt_context** out)
+{
+	if (!out) return set_error(CUPT_ERR_INVALID, "null output");
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n <= 0)
+		return set_error(CUPT_ERR_NO_DEVICE, "no CUDA device (%s): the hot path has no CPU fallback", cudaGetErrorString(e));
+	if (device < 0 || device >= n) return set_error(CUPT_ERR_INVALID, "device %d out of range (%d devices)", device, n);
+	CK(cudaSetDevice(device));
+	cupt_context* c = new (std::nothrow) cupt_context();
+	if (!c) return set_error(CUPT_ERR_NOMEM, "out of memory");
+	c->device = device;
+	cudaDeviceProp prop;
+	CK(cudaGetDeviceProperties(&prop, device));
+	c->num_sms = prop.multiProcessorCount;
+	CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+	c->own_stream = true;
+	CK(cudaMalloc((void**)&c->pb.counters, 128 * sizeof(uint32_t)));
+	CK(cudaMalloc((void**)&c->pb.stats, 8 * sizeof(unsigned long long)));
+	CK(cudaMemset(c->pb.counters, 0, 128 * sizeof(uint32_t)));
+	CK(cudaMemset(c->pb.stats, 0, 8 * sizeof(unsigned long long)));
+	cupt_default_render_opts(&c->opts);
+	*out = c;
+	return CUPT_OK;
+}
+
+void cupt_destroy(cupt_context* c)
+{
+	if (!c) return;
+	cudaSetDevice(c->device);
+	cudaStreamSynchronize(c->stream);
+	drain_events(c);
+	for (StageEvent& ev : c->pool) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
+	cudaFree(c->d_verts); cudaFree(c->d_tris); cudaFree(c->d_trishade); cudaFree(c->d_mats); cudaFree(c->d_lights);
+	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2);
+	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
+	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats);
+	cudaFree(c->d_accum);
+	if (c->own_stream) cudaStreamDestroy(c->stream);
+	delete c;
+}
+
+int cupt_set_stream(cupt_context* c, void* cuda_stream)
+{
+	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
+	CK(cudaStreamSynchronize(c->stream));
+	if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
+	c->stream = (cudaStream_t)cuda_stream;
+	return CUPT_OK;
+}
+
+int cupt_default_render_opts(cupt_render_opts* o)
+{
+	if (!o) return set_error(CUPT_ERR_INVALID, "null output");
+	memset(o, 0, sizeof(*o));
+	o->max_depth = 3;                  // NUM_BOUNCES, kernel.cu:33
+	o->integrator = CUPT_INTEGRATOR_PT;
+	o->traversal = CUPT_TRAVERSAL_WIDE;
+	o->tri_test = CUPT_TRI_REFEXACT;
+	o->seed = 1234;                    // kernel.cu:532
+	return CUPT_OK;
+}
+
+int cupt_set_render_opts(cupt_context* c, const cupt_render_opts* o)
+{
+	if (!c || !o) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (o->max_depth < 1 || o->max_depth > 62) return set_error(CUPT_ERR_INVALID, "max_depth must be in 1..62");
+	if (o->integrator != CUPT_INTEGRATOR_PT)
+		return set_error(CUPT_ERR_INVALID, "integrator %d is not implemented (only CUPT_INTEGRATOR_PT, kernel.cu:417-515)", o->integrator);
+	if (o->traversal != CUPT_TRAVERSAL_WIDE && o->traversal != CUPT_TRAVERSAL_REF_BVH2) return set_error(CUPT_ERR_INVALID, "bad traversal");
+	if (o->tri_test != CUPT_TRI_REFEXACT) return set_error(CUPT_ERR_INVALID, "tri_test %d is not implemented", o->tri_test);
+	c->opts = *o;
+	return CUPT_OK;
+}
+
+int cupt_set_camera(cupt_context* c, const cupt_camera* cam)
+{
+	if (!c || !cam) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (cam->pxlWidth < 1 || cam->pxlHeight < 1 || cam->pxlWidth > 65535 || cam->pxlHeight > 65535)
+		return set_error(CUPT_ERR_INVALID, "image size %dx%d outside 1..65535 (pixel coordinates are uint16_t, camera.h:36)", cam->pxlWidth, cam->pxlHeight);
+	c->cam = *cam;
+	c->have_cam = true;
+	return CUPT_OK;
+}
+
+int cupt_set_scene(cupt_context* c, const cupt_scene* s)
+{
+	if (!c || !s) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (s->tris.empty()) return set_error(CUPT_ERR_INVALID, "scene has no triangles");
+	CK(cudaSetDevice(c->device));
+	const size_t nt = s->tris.size(), nm = s->mats.size(), nl = s->lights.size();
+	int rc;
+	if ((rc = upload(&c->d_verts, s->verts.data(), s->verts.size() * sizeof(cupt_vec3), c->stream))) return rc;
+	if ((rc = upload(&c->d_tris, s->tris.data(), nt * sizeof(cupt_triangle), c->stream))) return rc;
+	std::vector<TriShade> ts(nt);
+	for (size_t i = 0; i < nt; ++i) {
+		ts[i].n[0] = s->tris[i].norm.x; ts[i].n[1] = s->tris[i].norm.y; ts[i].n[2] = s->tris[i].norm.z;
+		ts[i].mat = s->tris[i].mat;
+	}
+	if ((rc = upload(&c->d_trishade, ts.data(), nt * sizeof(TriShade), c->stream))) return rc;
+	std::vector<MatF> mf(nm);
+	for (size_t i = 0; i < nm; ++i) {
+		for (int k = 0; k < 3; ++k) { mf[i].albedo[k] = (float)s->mats[i].albedo[k]; mf[i].emission[k] = (float)s->mats[i].emission[k]; }
+		mf[i].emissive_flag = s->mats[i].emission[0] != 0 ? 1.f : 0.f;  // kernel.cu:453 tests the f64 value
+		mf[i].pad = 0.f;
+	}
+	if ((rc = upload(&c->d_mats, mf.data(), nm * sizeof(MatF), c->stream))) return rc;
+	// light table: per light v0, a1 = v1 - v0, a2 = v2 - v0 and area = length(cross(a1, a2)) / 2 (kernel.cu:472-477),
+	// plus the fallback entry for `selectedTri = 0` (kernel.cu:469)
+	std::vector<LightTri> lt(nl + 1);
+	for (size_t j = 0; j <= nl; ++j) {
+		const cupt_triangle& t = s->tris[j < nl ? (size_t)s->lights[j] : 0];
+		const V3 v0 = toV3(s->verts[t.v0]), a1 = toV3(s->verts[t.v1]) - v0, a2 = toV3(s->verts[t.v2]) - v0;
+		memset(&lt[j], 0, sizeof(LightTri));
+		lt[j].v0[0] = v0.x; lt[j].v0[1] = v0.y; lt[j].v0[2] = v0.z;
+		lt[j].a1[0] = a1.x; lt[j].a1[1] = a1.y; lt[j].a1[2] = a1.z;
+		lt[j].a2[0] = a2.x; lt[j].a2[1] = a2.y; lt[j].a2[2] = a2.z;
+		lt[j].area = length3(cross3(a1, a2)) / 2;
+	}
+	if ((rc = upload(&c->d_lights, lt.data(), lt.size() * sizeof(LightTri), c->stream))) return rc;
+	c->num_tris = (int64_t)nt; c->num_lights = (int)nl; c->total_light_area = s->totalLightArea;
+	return CUPT_OK;
+}
+
+int cupt_set_bvh(cupt_context* c, const cupt_bvh* b)
+{
+	if (!c || !b) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (b->depth > 64) return set_error(CUPT_ERR_LIMIT, "wide BVH depth %d exceeds the traversal stack (64)", b->depth);
+	CK(cudaSetDevice(c->device));
+	int rc;
+	if ((rc = upload(&c->d_nodes, b->nodes.data(), b->nodes.size() * sizeof(Node8), c->stream))) return rc;
+	if ((rc = upload(&c->d_prims, b->prims.data(), b->prims.size() * sizeof(Prim48), c->stream))) return rc;
+	c->bvh_depth = b->depth; c->num_nodes = (int64_t)b->nodes.size(); c->num_prims = (int64_t)b->prims.size();
+	c->extend_blocks[0] = 0;
+	return CUPT_OK;
+}
+
+int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int depth)
+{
+	if (!c || !nodes || size < 1) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (depth >= CUPT_MAX_BVH2_DEPTH)  // kernel.cu:627-631
+		return set_error(CUPT_ERR_LIMIT, "BVH depth is too big (%d >= %d)", depth, CUPT_MAX_BVH2_DEPTH);
+	CK(cudaSetDevice(c->device));
+	int rc;
+	if ((rc = upload(&c->d_bvh2, nodes, (size_t)size * sizeof(cupt_bvh2_node), c->stream))) return rc;
+	c->bvh2_size = size; c->bvh2_depth = depth;
+	return CUPT_OK;
+}
+
+int cupt_render(cupt_context* c, int first_sample, int num_samples)
+{
+	int rc = check_ready(c, true);
+	if (rc) return rc;
+	if (num_samples < 0 || first_sample < 0) return set_error(CUPT_ERR_INVALID, "bad sample range");
+	CK(cudaSetDevice(c->device));
+	if ((rc = ensure_accum(c))) return rc;
+	const DevScene sc = make_scene(c);
+	PassParams probe = make_pass(c, 0, 1, 0);
+	int S = c->opts.samples_per_pass;
+	if (S <= 0) S = (int)std::max<int64_t>(1, (int64_t)(4 << 20) / probe.p_pad);
+	S = std::min(S, std::max(1, num_samples));
+	if ((int64_t)probe.p_pad * S > 0x7fffffff) S = (int)(0x7fffffff / probe.p_pad);
+	if ((rc = ensure_paths(c, (size_t)probe.p_pad * S))) return rc;
+	const int grid = c->num_sms * 8;
+	for (int done = 0; done < num_samples; done += S) {
+		const int s_now = std::min(S, num_samples - done);
+		const PassParams pp = make_pass(c, first_sample + done, s_now, 0);
+		CK(cudaMemsetAsync(c->pb.counters, 0, 128 * sizeof(uint32_t), c->stream));
+		StageEvent ev;
+		stage_begin(c, 0, ev);
+		k_raygen<<<grid, 256, 0, c->stream>>>(pp, c->pb);
+		stage_end(c, ev);
+		c->launches++;
+		for (int depth = 0; depth < pp.max_depth; ++depth) {
+			if ((rc = launch_extend(c, sc, depth, depth & 1))) return rc;
+			stage_begin(c, 2, ev);
+			k_shade<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb, depth, depth & 1);
+			stage_end(c, ev);
+			c->launches++;
+		}
+		stage_begin(c, 3, ev);
+		k_accumulate<<<(pp.p_pad + 255) / 256, 256, 0, c->stream>>>(pp, c->pb, c->d_accum);
+		stage_end(c, ev);
+		c->launches++;
+		CK(cudaGetLastError());
+		c->samples_accumulated += (uint64_t)s_now;
+	}
+	return CUPT_OK;
+}
+
+int cupt_sync(cupt_context* c)
+{
+	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
+	CK(cudaStreamSynchronize(c->stream));
+	drain_events(c);
+	return CUPT_OK;
+}
+
+int cupt_reset_accum(cupt_context* c)
+{
+	if (!c || !c->have_cam) return set_error(CUPT_ERR_INVALID, "no camera set");
+	CK(cudaSetDevice(c->device));
+	int rc = ensure_accum(c);
+	if (rc) return rc;
+	CK(cudaMemsetAsync(c->d_accum, 0, c->accum_pixels * 3 * sizeof(float), c->stream));
+	c->samples_accumulated = 0;
+	return CUPT_OK;
+}
+
+int cupt_read_accum(cupt_context* c, float* rgb_host, int normalise)
+{
+	if (!c || !rgb_host || !c->d_accum) return set_error(CUPT_ERR_INVALID, "nothing rendered");
+	CK(cudaSetDevice(c->device));
+	const size_t n = c->accum_pixels * 3;
+	CK(cudaMemcpyAsync(rgb_host, c->d_accum, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	drain_events(c);
+	if (normalise && c->samples_accumulated > 0) {
+		const float inv = 1.0f / (float)c->samples_accumulated;
+		for (size_t i = 0; i < n; ++i) rgb_host[i] *= inv;
+	}
+	return CUPT_OK;
+}
+
+int cupt_copy_accum_device(cupt_context* c, float* dst_device)
+{
+	if (!c || !dst_device || !c->d_accum) return set_error(CUPT_ERR_INVALID, "nothing rendered");
+	CK(cudaMemcpyAsync(dst_device, c->d_accum, c->accum_pixels * 3 * sizeof(float), cudaMemcpyDeviceToDevice, c->stream));
+	return CUPT_OK;
+}
+
+int cupt_add_accum_device(cupt_context* c, const float* src_device, int samples)
+{
+	if (!c || !src_device || samples < 0) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	int rc = check_ready(c, false);
+	if (rc) return rc;
+	if ((rc = ensure_accum(c))) return rc;
+	const size_t n = c->accum_pixels * 3;
+	k_add<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->d_accum, src_device, n);
+	CK(cudaGetLastError());
+	c->launches++;
+	c->samples_accumulated += (uint64_t)samples;
+	return CUPT_OK;
+}
+
+static int primary_pass(cupt_context* c, int32_t* tri_id, float* t, float* rays6)
+{
+	int rc = check_ready(c, false);
+	if (rc) return rc;
+	CK(cudaSetDevice(c->device));
+	const PassParams pp = make_pass(c, 0, 1, 1);
+	if ((rc = ensure_paths(c, (size_t)pp.p_pad))) return rc;
+	const size_t P = (size_t)c->cam.pxlWidth * c->cam.pxlHeight;
+	int32_t* d_ids = nullptr; float* d_t = nullptr; float* d_r = nullptr;
+	if (tri_id) { CK(cudaMalloc((void**)&d_ids, P * sizeof(int32_t))); CK(cudaMalloc((void**)&d_t, P * sizeof(float))); }
+	if (rays6) CK(cudaMalloc((void**)&d_r, P * 6 * sizeof(float)));
+	CK(cudaMemsetAsync(c->pb.counters, 0, 128 * sizeof(uint32_t), c->stream));
+	k_raygen<<<c->num_sms * 8, 256, 0, c->stream>>>(pp, c->pb);
+	c->launches++;
+	if (tri_id) { const DevScene sc = make_scene(c); if ((rc = launch_extend(c, sc, 0, 0))) return rc; }
+	k_gather_primary<<<(pp.p_pad + 255) / 256, 256, 0, c->stream>>>(pp, c->pb, d_ids, d_t, d_r);
+	c->launches++;
+	CK(cudaGetLastError());
+	if (tri_id) {
+		CK(cudaMemcpyAsync(tri_id, d_ids, P * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+		CK(cudaMemcpyAsync(t, d_t, P * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+	}
+	if (rays6) CK(cudaMemcpyAsync(rays6, d_r, P * 6 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	drain_events(c);
+	cudaFree(d_ids); cudaFree(d_t); cudaFree(d_r);
+	return CUPT_OK;
+}
+
+int cupt_read_primary_hits(cupt_context* c, int32_t* tri_id, float* t)
+{
+	if (!tri_id || !t) return set_error(CUPT_ERR_INVALID, "null output");
+	return primary_pass(c, tri_id, t, nullptr);
+}
+
+int cupt_camera_rays(cupt_context* c, float* rays_host)
+{
+	if (!c || !rays_host) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (!c->have_cam) return set_error(CUPT_ERR_INVALID, "no camera set");
+	// raygen alone needs no acceleration structure
+	const int saved = c->opts.traversal;
+	int rc;
+	{
+		CK(cudaSetDevice(c->device));
+		const PassParams pp = make_pass(c, 0, 1, 1);
+		if ((rc = ensure_paths(c, (size_t)pp.p_pad))) return rc;
+		const size_t P = (size_t)c->cam.pxlWidth * c->cam.pxlHeight;
+		float* d_r = nullptr;
+		CK(cudaMalloc((void**)&d_r, P * 6 * sizeof(float)));
+		CK(cudaMemsetAsync(c->pb.counters, 0, 128 * sizeof(uint32_t), c->stream));
+		k_raygen<<<c->num_sms * 8, 256, 0, c->stream>>>(pp, c->pb);
+		k_gather_primary<<<(pp.p_pad + 255) / 256, 256, 0, c->stream>>>(pp, c->pb, nullptr, nullptr, d_r);
+		c->launches += 2;
+		CK(cudaGetLastError());
+		CK(cudaMemcpyAsync(rays_host, d_r, P * 6 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+		CK(cudaStreamSynchronize(c->stream));
+		cudaFree(d_r);
+	}
+	(void)saved;
+	return CUPT_OK;
+}
+
+int cupt_trace_rays(cupt_context* c, const float* rays_host, int64_t n, int32_t* tri_id, float* t)
+{
+	if (!c || !rays_host || !tri_id || !t || n < 0) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE && !c->d_nodes) return set_error(CUPT_ERR_INVALID, "no wide BVH set (cupt_set_bvh)");
+	if (c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 && (!c->d_bvh2 || !c->d_tris)) return set_error(CUPT_ERR_INVALID, "no reference BVH2 / scene set");
+	CK(cudaSetDevice(c->device));
+	const int64_t chunk = 8 << 20;
+	int rc;
+	if ((rc = ensure_paths(c, (size_t)std::min<int64_t>(std::max<int64_t>(n, 1), chunk)))) return rc;
+	float* d_r = nullptr; int32_t* d_ids = nullptr; float* d_t = nullptr;
+	const size_t cap = (size_t)std::min<int64_t>(std::max<int64_t>(n, 1), chunk);
+	CK(cudaMalloc((void**)&d_r, cap * 6 * sizeof(float)));
+	CK(cudaMalloc((void**)&d_ids, cap * sizeof(int32_t)));
+	CK(cudaMalloc((void**)&d_t, cap * sizeof(float)));
+	const DevScene sc = make_scene(c);
+	for (int64_t off = 0; off < n; off += chunk) {
+		const uint32_t m = (uint32_t)std::min<int64_t>(chunk, n - off);
+		CK(cudaMemcpyAsync(d_r, rays_host + 6 * off, (size_t)m * 6 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+		CK(cudaMemsetAsync(c->pb.counters, 0, 128 * sizeof(uint32_t), c->stream));
+		CK(cudaMemcpyAsync(c->pb.counters, &m, sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+		k_load_rays<<<(m + 255) / 256, 256, 0, c->stream>>>(d_r, m, 0u, c->pb);
+		c->launches++;
+		if ((rc = launch_extend(c, sc, 0, 0))) return rc;
+		k_store_hits<<<(m + 255) / 256, 256, 0, c->stream>>>(m, 0u, c->pb, d_ids, d_t);
+		c->launches++;
+		CK(cudaGetLastError());
+		CK(cudaMemcpyAsync(tri_id + off, d_ids, (size_t)m * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+		CK(cudaMemcpyAsync(t + off, d_t, (size_t)m * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+		CK(cudaStreamSynchronize(c->stream));
+	}
+	drain_events(c);
+	cudaFree(d_r); cudaFree(d_ids); cudaFree(d_t);
+	return CUPT_OK;
+}
+
+int cupt_get_stats(cupt_context* c, cupt_stats* out)
+{
+	if (!c || !out) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	CK(cudaSetDevice(c->device));
+	CK(cudaStreamSynchronize(c->stream));
+	drain_events(c);
+	unsigned long long h[8];
+	CK(cudaMemcpy(h, c->pb.stats, sizeof(h), cudaMemcpyDeviceToHost));
+	memset(out, 0, sizeof(*out));
+	out->rays = h[0]; out->nodes_visited = h[1]; out->tris_tested = h[2]; out->samples = h[3];
+	out->kernel_launches = c->launches; out->extend_launches = c->extend_launches;
+	out->ms_raygen = c->ms[0]; out->ms_extend = c->ms[1]; out->ms_shade = c->ms[2]; out->ms_accum = c->ms[3];
+	return CUPT_OK;
+}
+
+int cupt_reset_stats(cupt_context* c)
+{
+	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
+	CK(cudaSetDevice(c->device));
+	CK(cudaStreamSynchronize(c->stream));
+	drain_events(c);
+	CK(cudaMemsetAsync(c->pb.stats, 0, 8 * sizeof(unsigned long long), c->stream));
+	c->launches = c->extend_launches = 0;
+	for (int i = 0; i < 4; ++i) c->ms[i] = 0;
+	return CUPT_OK;
+}
+
+}  // extern "C"

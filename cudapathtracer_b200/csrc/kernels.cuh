@@ -1,0 +1,328 @@
+// Wavefront pipeline: raygen -> [extend -> shade]* -> accumulate, replacing the megakernel drawPixel
+// (reference kernel.cu:535-553) and the integrator radianceAlongSingleStep2 (kernel.cu:417-515).
+//
+// A pass renders S samples of every pixel: path slot i = s_local * P_pad + tile * 32 + lane, tiles of 8x4 pixels
+// so that one warp of primary rays is a compact screen tile (the reference gets the same effect from Morton
+// indexing, camera.h:57-65, which only covers square power-of-two images).  Pixel, sample and RNG stream are
+// functions of the slot index, so no per-path RNG state exists (the reference carries 48 bytes of XORWOW state
+// per pixel, kernel.cu:527-533).
+//
+// Per-path records (all 16-byte aligned, indexed by slot):
+//   rayA  float4  o.xyz, d.x
+//   rayB  float4  d.y, d.z, t (extend output), triangle id (extend output, int bits)
+//   st0   float4  weight rgb, packed {iter (bits 0-7), next Philox draw index (bits 8-15)}
+//   st1   float4  accumulated radiance rgb, unused
+#pragma once
+#include "traverse.cuh"
+
+namespace cupt {
+
+struct DevScene {
+	const uint4* nodes;            // Node8 x5 uint4
+	const float4* prims;           // Prim48 x3 float4
+	const cupt_bvh2_node* bvh2;    // reference layout (parity mode)
+	const float* verts;            // reference layout
+	const cupt_triangle* tris;     // reference layout
+	const float4* trishade;        // TriShade
+	const float4* mats;            // MatF x2 float4
+	const float4* lights;          // LightTri x3 float4, numLights + 1 entries (last = triangle 0 fallback)
+	int32_t numLights;
+	float totalLightArea;
+	int32_t stack_cap;             // shared-memory stack entries per thread
+};
+
+struct PassParams {
+	cupt_camera cam;
+	uint64_t seed;
+	int32_t first_sample;      // global index of s_local = 0
+	int32_t samples;           // S
+	int32_t tiles_x, tiles_y;
+	int32_t p_pad;             // tiles_x * tiles_y * 32
+	int32_t max_depth;         // NUM_BOUNCES made run-time
+	int32_t fixed_lens;        // 1: lens draws fixed at (0.5, 0.5) (primary-hit hook)
+};
+
+struct PathBuffers {
+	float4* rayA;
+	float4* rayB;
+	float4* st0;
+	float4* st1;
+	uint32_t* queue[2];
+	uint32_t* counters;        // [0..63] queue sizes per depth, [64..127] extend fetch cursors per depth
+	unsigned long long* stats; // [0] rays, [1] nodes, [2] tris, [3] samples
+};
+
+__device__ __forceinline__ void slot_to_pixel(const PassParams& pp, uint32_t slot, int& x, int& y, int& s_local)
+{
+	s_local = (int)(slot / (uint32_t)pp.p_pad);
+	const uint32_t r = slot - (uint32_t)s_local * (uint32_t)pp.p_pad;
+	const uint32_t tile = r >> 5, lane = r & 31u;
+	const uint32_t ty = tile / (uint32_t)pp.tiles_x, tx = tile - ty * (uint32_t)pp.tiles_x;
+	x = (int)(tx * 8u + (lane & 7u));
+	y = (int)(ty * 4u + (lane >> 3));
+}
+
+// camera::cameraRay, camera.h:77-97 (with pxlToFilm camera.h:36-43); exact-op arithmetic
+__device__ __forceinline__ void camera_ray(const cupt_camera& c, int px, int py, float u1, float u2, f3& o_out, f3& d_out)
+{
+	f3 prf;
+	prf.x = rsub(rdiv((float)px, (float)c.pxlWidth), 0.5f);
+	prf.y = rsub(rdiv((float)py, (float)c.pxlHeight), 0.5f);
+	const float r = rmul(c.radius, __fsqrt_rn(u1));
+	const float theta = (float)(2 * 3.14159 * (double)u2);
+	const f3 o = mk3(rmul(r, cosf(theta)), rmul(r, sinf(theta)), 0.0f);
+	prf.z = c.distFromFilm;
+	prf = rdiv3(rmul3(prf, -c.focalLength), c.distFromFilm);
+	o_out = radd3(o, mk3(c.pos.x, c.pos.y, c.pos.z));
+	d_out = rnormalized(rsub3(prf, o));
+}
+
+// ---- raygen --------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb)
+{
+	const uint32_t total = (uint32_t)pp.p_pad * (uint32_t)pp.samples;
+	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += gridDim.x * blockDim.x) {
+		const uint32_t slot = base + threadIdx.x;
+		bool valid = false;
+		if (slot < total) {
+			int x, y, sl;
+			slot_to_pixel(pp, slot, x, y, sl);
+			valid = x < pp.cam.pxlWidth && y < pp.cam.pxlHeight;
+			if (valid) {
+				float u1 = 0.5f, u2 = 0.5f;
+				if (!pp.fixed_lens) {
+					PhiloxStream rng;
+					rng.init(pp.seed, (uint32_t)x, (uint32_t)y, (uint32_t)(pp.first_sample + sl));
+					u1 = rng.draw(0); u2 = rng.draw(1);   // kernel.cu:547
+				}
+				f3 o, d;
+				camera_ray(pp.cam, x, y, u1, u2, o, d);
+				pb.rayA[slot] = make_float4(o.x, o.y, o.z, d.x);
+				pb.rayB[slot] = make_float4(d.y, d.z, CUPT_MAX_FLOAT, __int_as_float(-1));
+				pb.st0[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(0u | (2u << 8)));
+				pb.st1[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+			}
+		}
+		const uint32_t m = __ballot_sync(0xffffffffu, valid);
+		if (m) {
+			uint32_t wbase = 0;
+			const uint32_t lane = threadIdx.x & 31u;
+			if (lane == (uint32_t)(__ffs(m) - 1)) wbase = atomicAdd(&pb.counters[0], (uint32_t)__popc(m));
+			wbase = __shfl_sync(0xffffffffu, wbase, __ffs(m) - 1);
+			if (valid) pb.queue[0][wbase + __popc(m & ((1u << lane) - 1u))] = slot;
+		}
+	}
+	if (blockIdx.x == 0 && threadIdx.x == 0)
+		atomicAdd(&pb.stats[3], (unsigned long long)pp.cam.pxlWidth * pp.cam.pxlHeight * pp.samples);
+}
+
+// ---- extend: closest hit for every queued path ---------------------------------------------------------------
+// Persistent warps: each warp pulls 32 queue entries at a time from a global cursor (one atomic per warp) until
+// the queue is empty.  MODE 0 = wide BVH, 1 = reference BVH2 (parity mode).
+template <int MODE, bool STATS>
+__global__ void __launch_bounds__(128) k_extend(DevScene sc, PathBuffers pb, int depth, int qsel)
+{
+	extern __shared__ uint2 smem_stack[];
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t count = pb.counters[depth];
+	uint32_t* cursor = &pb.counters[64 + depth];
+	const uint32_t* __restrict__ queue = pb.queue[qsel];
+	uint32_t n_nodes = 0, n_tris = 0, n_rays = 0;
+	for (;;) {
+		uint32_t base = 0;
+		if (lane == 0) base = atomicAdd(cursor, 32u);
+		base = __shfl_sync(0xffffffffu, base, 0);
+		if (base >= count) break;
+		const uint32_t qi = base + lane;
+		if (qi < count) {
+			const uint32_t slot = queue[qi];
+			const float4 a = pb.rayA[slot];
+			const float4 b = pb.rayB[slot];
+			const f3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, b.x, b.y);
+			Hit hit;
+			if (MODE == 0)
+				traverse_wide<STATS>(sc.nodes, sc.prims, o, d, hit, smem_stack + threadIdx.x, blockDim.x, sc.stack_cap, n_nodes, n_tris);
+			else
+				traverse_bvh2_ref<STATS>(sc.bvh2, sc.verts, sc.tris, o, d, hit, n_nodes, n_tris);
+			reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(hit.t, __int_as_float(hit.id));
+			++n_rays;
+		}
+		__syncwarp();
+	}
+	// one atomic per warp for the ray counter (rays are counted, not nominal: SURVEY.md §8d)
+	for (int ofs = 16; ofs > 0; ofs >>= 1) {
+		n_rays += __shfl_xor_sync(0xffffffffu, n_rays, ofs);
+		if (STATS) { n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, ofs); n_tris += __shfl_xor_sync(0xffffffffu, n_tris, ofs); }
+	}
+	if (lane == 0) {
+		if (n_rays) atomicAdd(&pb.stats[0], (unsigned long long)n_rays);
+		if (STATS) { atomicAdd(&pb.stats[1], (unsigned long long)n_nodes); atomicAdd(&pb.stats[2], (unsigned long long)n_tris); }
+	}
+}
+
+// ---- shade: one iteration of radianceAlongSingleStep2 (kernel.cu:424-512) per queued path ----------------------
+// Consumes the hit, adds emission, draws the 50/50 choice (kernel.cu:459-460) between a cosine-weighted bounce
+// (kernel.cu:462-464) and a light-point sample (kernel.cu:468-507), writes the next segment and pushes the path
+// into the next queue (warp ballot + one atomic per warp).  A path whose weight is exactly zero can never
+// contribute again (the weight is only ever multiplied, kernel.cu:464,506), so it is dropped instead of being
+// traced to the end as the reference does; the light-sample branch jumps to the last iteration exactly like
+// `i = max(i, NUM_BOUNCES - 2)` (kernel.cu:507), which makes the next extend the shadow test.
+__device__ __forceinline__ f3 get_tangent(const f3 n)  // kernel.cu:44-54
+{
+	const f3 c1 = rcross(n, mk3(0.f, 0.f, 1.f)), c2 = rcross(n, mk3(0.f, 1.f, 0.f));
+	return (rdot(c1, c1) > rdot(c2, c2)) ? c1 : c2;
+}
+
+__global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathBuffers pb, int depth, int qsel)
+{
+	const uint32_t count = pb.counters[depth];
+	const uint32_t* __restrict__ qin = pb.queue[qsel];
+	uint32_t* __restrict__ qout = pb.queue[qsel ^ 1];
+	const uint32_t lane = threadIdx.x & 31u;
+	const float kBrdf = (float)(1 / 3.14159);   // BRDF(): mul(albedo, 1 / 3.14159) with a float parameter (kernel.cu:101-104)
+	const float kPi = (float)3.14159;            // color::operator*(const float&) (kernel.cu:463)
+	for (uint32_t base = blockIdx.x * blockDim.x; base < count; base += gridDim.x * blockDim.x) {
+		const uint32_t qi = base + threadIdx.x;
+		bool push = false;
+		uint32_t slot = 0;
+		if (qi < count) {
+			slot = qin[qi];
+			const float4 ra = pb.rayA[slot], rb = pb.rayB[slot], s0 = pb.st0[slot];
+			float4 s1 = pb.st1[slot];
+			const f3 o = mk3(ra.x, ra.y, ra.z), d = mk3(ra.w, rb.x, rb.y);
+			float wr = s0.x, wg = s0.y, wb = s0.z;
+			const uint32_t packed = __float_as_uint(s0.w);
+			int iter = (int)(packed & 0xffu);
+			uint32_t draw = (packed >> 8) & 0xffu;
+			int32_t id = __float_as_int(rb.w);
+			float closestT = (float)((double)rb.z - 0.001);                        // kernel.cu:431
+			if ((double)closestT < 0.001) { wr = wg = wb = 0.f; }                   // kernel.cu:432-435
+			if (closestT > CUPT_MAX_FLOAT - 1) { wr = wg = wb = 0.f; id = 0; closestT = 0.f; }  // kernel.cu:436-441
+			const float4 tsh = sc.trishade[id];
+			const f3 normal = mk3(tsh.x, tsh.y, tsh.z);
+			const int mat = __float_as_int(tsh.w);
+			const float4 m0 = sc.mats[2 * mat], m1 = sc.mats[2 * mat + 1];
+			const f3 pos = radd3(o, rmul3(d, closestT));                            // kernel.cu:449
+			if (m0.w != 0.f) {                                                      // kernel.cu:453-457
+				s1.x += wr * m1.x; s1.y += wg * m1.y; s1.z += wb * m1.z;
+				wr = wg = wb = 0.f;
+			}
+			const bool dead = !(wr != 0.f || wg != 0.f || wb != 0.f);
+			if (dead || iter >= pp.max_depth - 1) {
+				pb.st1[slot] = s1;
+			} else {
+				int x, y, sl;
+				slot_to_pixel(pp, slot, x, y, sl);
+				PhiloxStream rng;
+				rng.init(pp.seed, (uint32_t)x, (uint32_t)y, (uint32_t)(pp.first_sample + sl));
+				const float a = rng.draw(draw++);                                    // kernel.cu:459
+				f3 lDir;
+				if (a < 0.5f) {
+					// cosineWeightedRay, kernel.cu:78-99
+					const float u1 = rng.draw(draw++), u2 = rng.draw(draw++);
+					const float r = __fsqrt_rn(u1);
+					const float theta = (float)(2 * 3.14159 * (double)u2);
+					const float cx = rmul(r, cosf(theta)), cz = rmul(r, sinf(theta));
+					const float cy = __fsqrt_rn(fmaxf(0.0f, rsub(1.0f, u1)));
+					const f3 tangent = get_tangent(normal), bitangent = rcross(normal, tangent);
+					lDir = rnormalized(radd3(radd3(rmul3(normal, cy), rmul3(tangent, cx)), rmul3(bitangent, cz)));
+					const float k = kBrdf * kPi;
+					wr *= m0.x * k; wg *= m0.y * k; wb *= m0.z * k;                  // kernel.cu:463-464
+				} else {
+					// light-point sample, kernel.cu:468-507
+					float randArea = rmul(sc.totalLightArea, rng.draw(draw++));
+					int sel = sc.numLights;   // fallback entry = triangle 0 (`selectedTri = 0`, kernel.cu:469)
+					for (int j = 0; j < sc.numLights; ++j) {
+						const float area = sc.lights[3 * j].w;
+						if (randArea < area && randArea > 0.f) sel = j;
+						randArea = rsub(randArea, area);
+					}
+					float u = rng.draw(draw++), v = rng.draw(draw++);
+					const float4 l0 = sc.lights[3 * sel], l1 = sc.lights[3 * sel + 1], l2 = sc.lights[3 * sel + 2];
+					if (radd(u, v) > 1.0f) {                                          // kernel.cu:491-495
+						u = (float)((double)u + 2 * (0.5 - (double)u));
+						v = (float)((double)v + 2 * (0.5 - (double)v));
+					}
+					const f3 pos1 = radd3(radd3(mk3(l0.x, l0.y, l0.z), rmul3(mk3(l1.x, l1.y, l1.z), u)), rmul3(mk3(l2.x, l2.y, l2.z), v));
+					const f3 dd = rsub3(pos1, pos);
+					lDir = rnormalized(dd);
+					const float cosL = fmaxf(0.0f, rdot(lDir, normal));
+					const float cosO1 = fmaxf(0.0f, rdot(mk3(0.f, -1.f, 0.f), rmul3(lDir, -1.f)));   // hard-coded light normal, kernel.cu:503
+					const float G = rdiv(rmul(cosL, cosO1), rdot(dd, dd));
+					const float k = kBrdf * G * sc.totalLightArea;
+					wr *= m0.x * k; wg *= m0.y * k; wb *= m0.z * k;                  // kernel.cu:506
+					iter = max(iter, pp.max_depth - 2);                              // kernel.cu:507
+				}
+				++iter;
+				push = (wr != 0.f || wg != 0.f || wb != 0.f);
+				pb.st1[slot] = s1;
+				if (push) {
+					pb.rayA[slot] = make_float4(pos.x, pos.y, pos.z, lDir.x);
+					pb.rayB[slot] = make_float4(lDir.y, lDir.z, CUPT_MAX_FLOAT, __int_as_float(-1));
+					pb.st0[slot] = make_float4(wr, wg, wb, __uint_as_float((uint32_t)iter | (draw << 8)));
+				}
+			}
+		}
+		const uint32_t m = __ballot_sync(0xffffffffu, push);
+		if (m) {
+			uint32_t wbase = 0;
+			const int leader = __ffs(m) - 1;
+			if ((int)lane == leader) wbase = atomicAdd(&pb.counters[depth + 1], (uint32_t)__popc(m));
+			wbase = __shfl_sync(0xffffffffu, wbase, leader);
+			if (push) qout[wbase + __popc(m & ((1u << lane) - 1u))] = slot;
+		}
+	}
+}
+
+// ---- accumulate: sum the pass's samples per pixel in a fixed order, add to the f32 sum image ------------------
+// (the reference keeps an f64 running mean per sample launch, kernel.cu:551-552)
+__global__ void __launch_bounds__(256) k_accumulate(PassParams pp, PathBuffers pb, float* __restrict__ accum)
+{
+	const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= (uint32_t)pp.p_pad) return;
+	int x, y, sl;
+	slot_to_pixel(pp, r, x, y, sl);
+	if (x >= pp.cam.pxlWidth || y >= pp.cam.pxlHeight) return;
+	float sr = 0.f, sg = 0.f, sb = 0.f;
+	for (int s = 0; s < pp.samples; ++s) {
+		const float4 v = pb.st1[(size_t)s * pp.p_pad + r];
+		sr += v.x; sg += v.y; sb += v.z;
+	}
+	float* a = accum + 3 * ((size_t)y * pp.cam.pxlWidth + x);
+	a[0] += sr; a[1] += sg; a[2] += sb;
+}
+
+// ---- parity hooks ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_gather_primary(PassParams pp, PathBuffers pb, int32_t* __restrict__ ids, float* __restrict__ ts,
+                                                         float* __restrict__ rays6)
+{
+	const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= (uint32_t)pp.p_pad) return;
+	int x, y, sl;
+	slot_to_pixel(pp, r, x, y, sl);
+	if (x >= pp.cam.pxlWidth || y >= pp.cam.pxlHeight) return;
+	const size_t p = (size_t)y * pp.cam.pxlWidth + x;
+	const float4 a = pb.rayA[r], b = pb.rayB[r];
+	if (ids) { ids[p] = __float_as_int(b.w); ts[p] = b.z; }
+	if (rays6) { float* o = rays6 + 6 * p; o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; }
+}
+
+__global__ void __launch_bounds__(256) k_load_rays(const float* __restrict__ rays6, uint32_t n, uint32_t slot0, PathBuffers pb)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const float* r = rays6 + 6 * (size_t)i;
+	pb.rayA[slot0 + i] = make_float4(r[0], r[1], r[2], r[3]);
+	pb.rayB[slot0 + i] = make_float4(r[4], r[5], CUPT_MAX_FLOAT, __int_as_float(-1));
+	pb.queue[0][i] = slot0 + i;
+}
+
+__global__ void __launch_bounds__(256) k_store_hits(uint32_t n, uint32_t slot0, PathBuffers pb, int32_t* __restrict__ ids, float* __restrict__ ts)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const float4 b = pb.rayB[slot0 + i];
+	ids[i] = __float_as_int(b.w); ts[i] = b.z;
+}
+
+}  // namespace cupt

@@ -1,0 +1,63 @@
+// TEST INFRASTRUCTURE (CPU suite): compiles the product's traversal header (csrc/traverse.cuh) for the host with
+// a shim for the CUDA intrinsics it uses, so that the wide-BVH builder and the traversal logic (slot order,
+// quantisation, tie-break, stack discipline) can be checked against the oracle without a GPU.  This is a
+// structural test of host-built data; it is never used by the product and proves nothing about the kernels'
+// device arithmetic (the GPU tests do that).
+#define CUPT_HOST_EMUL 1
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <vector>
+#include <cuda_runtime.h>
+#undef __device__
+#undef __forceinline__
+#define __device__
+#define __forceinline__ inline
+static inline float __fmul_rn(float a, float b) { return a * b; }   // built with -ffp-contract=off
+static inline float __fadd_rn(float a, float b) { return a + b; }
+static inline float __fsub_rn(float a, float b) { return a - b; }
+static inline float __fdiv_rn(float a, float b) { return a / b; }
+static inline float __fsqrt_rn(float a) { return sqrtf(a); }
+static inline uint32_t __umulhi(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * b) >> 32); }
+static inline float __uint_as_float(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+static inline uint32_t __float_as_uint(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+static inline int __clz(uint32_t x) { return x ? __builtin_clz(x) : 32; }
+static inline int __popc(uint32_t x) { return __builtin_popcount(x); }
+static inline int __ffs(uint32_t x) { return __builtin_ffs((int)x); }
+#include "../../cudapathtracer_b200/csrc/traverse.cuh"
+
+using namespace cupt;
+
+extern "C" int emul_trace_wide(const void* nodes80, const void* prims48, int depth, const float* rays6, long long n,
+                               int32_t* ids, float* ts, unsigned long long* counts)
+{
+	unsigned long long nn = 0, nt = 0;
+	int max_sp_ok = 1;
+#pragma omp parallel for schedule(dynamic, 256) reduction(+ : nn, nt)
+	for (long long i = 0; i < n; ++i) {
+		std::vector<uint2> stack((size_t)depth + 1);
+		Hit h;
+		uint32_t a = 0, b = 0;
+		traverse_wide<true>((const uint4*)nodes80, (const float4*)prims48, mk3(rays6[6 * i], rays6[6 * i + 1], rays6[6 * i + 2]),
+		                    mk3(rays6[6 * i + 3], rays6[6 * i + 4], rays6[6 * i + 5]), h, stack.data(), 1, depth, a, b);
+		ids[i] = h.id; ts[i] = h.t;
+		nn += a; nt += b;
+	}
+	if (counts) { counts[0] = nn; counts[1] = nt; }
+	return max_sp_ok ? 0 : -1;
+}
+
+extern "C" int emul_trace_bvh2(const void* nodes32, const float* verts, const void* tris28, const float* rays6, long long n,
+                               int32_t* ids, float* ts)
+{
+#pragma omp parallel for schedule(dynamic, 256)
+	for (long long i = 0; i < n; ++i) {
+		Hit h;
+		uint32_t a = 0, b = 0;
+		traverse_bvh2_ref<false>((const cupt_bvh2_node*)nodes32, verts, (const cupt_triangle*)tris28,
+		                         mk3(rays6[6 * i], rays6[6 * i + 1], rays6[6 * i + 2]),
+		                         mk3(rays6[6 * i + 3], rays6[6 * i + 4], rays6[6 * i + 5]), h, a, b);
+		ids[i] = h.id; ts[i] = h.t;
+	}
+	return 0;
+}
