@@ -105,6 +105,7 @@ class SceneHandle:
     """cupt_scene: the reference's globals verts/tris/mats/lights/totalLightArea (modelLoader.h:43-47)."""
 
     def __init__(self):
+        self.h = None
         self.lib = load_library()
         h = C.c_void_p()
         _check(self.lib.cupt_scene_create(C.byref(h)))
@@ -210,6 +211,7 @@ class BvhHandle:
     """cupt_bvh: host image of the 8-wide quantised BVH (replaces buildBVH, BVH.h:443-474)."""
 
     def __init__(self, scene: SceneHandle, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None):
+        self.h = None
         self.lib = load_library()
         self._rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, dtype=np.uint32)
         opts = BvhOpts(sah_bins, max_leaf_tris, threads, None if self._rank is None else self._rank.ctypes.data)
@@ -242,6 +244,7 @@ class Context:
     set_camera once, render(first_sample, n) any number of times, read_accum()."""
 
     def __init__(self, device: int = 0):
+        self.h = None
         self.lib = load_library()
         h = C.c_void_p()
         _check(self.lib.cupt_create(device, C.byref(h)))

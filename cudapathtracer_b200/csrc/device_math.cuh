@@ -2,7 +2,7 @@
 //
 // Parity policy: everything that feeds a primary-hit decision or the value of t is written
 // with the explicit round-to-nearest intrinsics below, which nvcc never contracts into FMA, so the bits equal
-// the reference's host pass (and oracle/oracle.c, built with -ffp-contract=off).  Box tests are free to use FMA:
+// the reference's host pass (x86-64 without FMA contraction).  Box tests are free to use FMA:
 // they only have to be conservative.
 #pragma once
 #include <cstdint>
@@ -37,7 +37,7 @@ __device__ __forceinline__ f3 rnormalized(f3 v)    // vec3.h:58-62
 	return mk3(rdiv(v.x, len), rdiv(v.y, len), rdiv(v.z, len));
 }
 
-// ---- Philox4x32-10, cuRAND counter layout (see oracle/oracle.c for the citation) ---------------------------
+// ---- Philox4x32-10 (Salmon, Moraes, Dror, Shaw, SC'11), counter/key layout of cuRAND's Philox state ----------
 // stream (seed; x, y, sample): counter = (draw >> 2, 0, y << 16 | x, sample), key = seed; draw & 3 selects the word.
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1)
 {

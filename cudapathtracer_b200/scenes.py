@@ -252,22 +252,23 @@ def atrium(n_tris: int = 262144, seed: int = 1) -> Scene:
     return sc
 
 
-def triangle_soup(n_tris: int, seed: int = 2) -> Scene:
-    """centres uniform in [-50,50]^3, edge length log-uniform in [0.05,0.5], random
-    orientation.  One diffuse material plus a small emissive fraction so paths can terminate on lights."""
+def triangle_soup(n_tris: int, seed: int = 2, extent: float = 50.0, edge=(0.05, 0.5), cam_z: float = 160.0) -> Scene:
+    """centres uniform in [-extent,extent]^3 (50), edge length log-uniform in `edge`
+    ([0.05,0.5]), random orientation.  One diffuse material plus a small emissive fraction so paths can
+    terminate on lights."""
     rng = np.random.default_rng(seed)
     mats = [("soup", (0.7, 0.7, 0.7), (0, 0, 0)), ("glow", (0.8, 0.8, 0.8), (4.0, 4.0, 4.0))]
     n_light = max(2, n_tris // 512)
     shapes = []
     for name, n, m in (("soup", n_tris - n_light, 0), ("glow", n_light, 1)):
-        c = rng.uniform(-50.0, 50.0, size=(n, 1, 3)).astype(np.float32)
-        edge = np.exp(rng.uniform(np.log(0.05), np.log(0.5), size=(n, 1, 1))).astype(np.float32)
+        c = rng.uniform(-extent, extent, size=(n, 1, 3)).astype(np.float32)
+        elen = np.exp(rng.uniform(np.log(edge[0]), np.log(edge[1]), size=(n, 1, 1))).astype(np.float32)
         d = rng.normal(size=(n, 3, 3)).astype(np.float32)
         d /= np.linalg.norm(d, axis=2, keepdims=True)
-        pos = (c + d * edge * np.float32(0.6)).reshape(-1, 3).astype(np.float32)
+        pos = (c + d * elen * np.float32(0.6)).reshape(-1, 3).astype(np.float32)
         idx = np.arange(3 * n, dtype=np.uint32).reshape(n, 3)
         shapes.append(Shape(name, pos, idx, m))
-    return Scene(mats, shapes, dict(pos=(0.0, 0.0, 160.0), distFromFilm=1.0, focalLength=3.0, radius=0.0))
+    return Scene(mats, shapes, dict(pos=(0.0, 0.0, cam_z), distFromFilm=1.0, focalLength=3.0, radius=0.0))
 
 
 def to_obj(scene: Scene, mtl_name: str = "scene.mtl"):

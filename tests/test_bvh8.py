@@ -1,0 +1,157 @@
+"""Wide BVH builder (host) — structural invariants, and the traversal header checked on the CPU through the
+emulation harness tests/emul (structural check of the host-built data; the kernels themselves are GPU tests)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from cudapathtracer_b200 import api, scenes
+from conftest import CASES
+
+EMUL = os.path.join(os.path.dirname(os.path.abspath(__file__)), "emul", "libemul.so")
+
+
+def P(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+@pytest.fixture(scope="module")
+def emul(lib):
+    if not os.path.exists(EMUL):
+        import __graft_entry__
+        __graft_entry__.build()
+    return C.CDLL(EMUL)
+
+
+def emul_trace(emul, nodes, prims, depth, rays):
+    rays = np.ascontiguousarray(rays, dtype=np.float32)
+    ids, ts = np.zeros(len(rays), np.int32), np.zeros(len(rays), np.float32)
+    cnt = (C.c_ulonglong * 2)()
+    emul.emul_trace_wide(P(nodes), P(prims), depth, P(rays), C.c_longlong(len(rays)), P(ids), P(ts), cnt)
+    return ids, ts, (cnt[0], cnt[1])
+
+
+def decode_boxes(nodes):
+    scale = np.ldexp(1.0, nodes["e"].astype(np.int64) - 127)                      # [n,3]
+    lo = nodes["p"][:, :, None].astype(np.float64) + nodes["qlo"].astype(np.float64) * scale[:, :, None]
+    hi = nodes["p"][:, :, None].astype(np.float64) + nodes["qhi"].astype(np.float64) * scale[:, :, None]
+    return lo, hi                                                                   # [n,3,8]
+
+
+@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("max_leaf", [1, 3])
+def test_bvh8_invariants(get_case, name, max_leaf):
+    c = get_case(name)
+    b = c.handle.build_bvh(max_leaf_tris=max_leaf, tie_rank=c.rank)
+    info = b.info()
+    nodes, prims = b.arrays()
+    n = len(c.tris)
+    assert info["node_bytes"] == 80 and info["tri_bytes"] == 48
+    assert len(prims) == n and np.array_equal(np.sort(prims["id"]), np.arange(n, dtype=np.uint32))   # each triangle once
+    assert np.array_equal(prims["rank"], c.rank[prims["id"]]) and np.all(prims["kind"] == 0)
+    pos = c.verts.view(np.float32).reshape(-1, 3)
+    t = c.tris[prims["id"]]
+    v0 = pos[t["v0"]]
+    assert np.array_equal(prims["a"], v0)
+    assert np.array_equal(prims["b"], pos[t["v1"]] - v0) and np.array_equal(prims["c"], pos[t["v2"]] - v0)   # e1, e2 as f32 subtractions
+    lo, hi = decode_boxes(nodes)
+    meta = nodes["meta"]
+    inner = (meta & 0x1F) >= 24
+    leafc = (~inner) & (meta != 0)
+    assert np.array_equal(np.packbits(inner[:, ::-1], axis=1)[:, 0], nodes["imask"])
+    assert np.all((meta[inner] & 0x1F) - 24 == np.nonzero(inner)[1])              # inner meta carries its own slot
+    # walk: inner children consecutive in slot order, every node reachable once, boxes nested and conservative
+    seen = np.zeros(len(nodes), np.int32)
+    tri_seen = np.zeros(n, np.int32)
+    stack = [(0, [], 1)]
+    maxd = 0
+    vmin = np.minimum(np.minimum(pos[t["v0"]], pos[t["v1"]]), pos[t["v2"]]).astype(np.float64)
+    vmax = np.maximum(np.maximum(pos[t["v0"]], pos[t["v1"]]), pos[t["v2"]]).astype(np.float64)
+    while stack:
+        i, anc, d = stack.pop()
+        seen[i] += 1
+        maxd = max(maxd, d)
+        k = 0
+        for s in range(8):
+            m = int(meta[i, s])
+            if m == 0:
+                continue
+            blo, bhi = lo[i, :, s], hi[i, :, s]
+            assert np.all(blo <= bhi)
+            if inner[i, s]:
+                stack.append((int(nodes["child_base"][i]) + k, anc + [(blo, bhi)], d + 1))
+                k += 1
+            else:
+                cnt = {1: 1, 3: 2, 7: 3}[m >> 5]
+                assert cnt <= max_leaf
+                first = int(nodes["tri_base"][i]) + (m & 0x1F)
+                for r in range(first, first + cnt):
+                    tri_seen[r] += 1
+                    for alo, ahi in anc + [(blo, bhi)]:                            # every ancestor's decoded box is conservative
+                        assert np.all(vmin[r] >= alo) and np.all(vmax[r] <= ahi)
+    assert np.all(seen == 1) and np.all(tri_seen == 1) and maxd == info["depth"]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_wide_traversal_logic_matches_brute_force_and_reference(get_case, emul, name):
+    c = get_case(name)
+    b = c.handle.build_bvh(tie_rank=c.rank)
+    nodes, prims = b.arrays()
+    rays = c.osc.camera_rays(c.cam)
+    rng = np.random.default_rng(11)
+    pos = c.verts.view(np.float32).reshape(-1, 3)
+    o = rng.uniform(pos.min(0), pos.max(0), size=(4000, 3))
+    d = rng.normal(size=(4000, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    axis = np.zeros((64, 6)); axis[:, :3] = rng.uniform(pos.min(0), pos.max(0), size=(64, 3)); axis[np.arange(64), 3 + np.arange(64) % 3] = 1.0  # axis-parallel: 1/0 in the slab test
+    rays = np.concatenate([rays, np.concatenate([o, d], axis=1), axis]).astype(np.float32)
+    ids, ts, (nn, nt) = emul_trace(emul, nodes, prims, b.info()["depth"], rays)
+    bi, bt = c.osc.brute_force(rays, c.rank)
+    assert np.array_equal(ids, bi) and ts.tobytes() == bt.tobytes()               # == argmin over all triangles
+    ri, rt = c.osc.trace_rays(rays)
+    differ = (ids != ri) | (ts.view(np.uint32) != rt.view(np.uint32))
+    assert differ.sum() <= 4 and np.all(ts[differ] <= rt[differ])                 # only hits the reference dropped
+    assert nn > 0 and nt > 0
+
+
+def test_bvh2_traversal_header_is_the_reference_algorithm(get_case, emul):
+    c = get_case("atrium20k")
+    rays = c.osc.camera_rays(c.cam)
+    ids, ts = np.zeros(len(rays), np.int32), np.zeros(len(rays), np.float32)
+    vf = np.ascontiguousarray(c.verts.view(np.float32))
+    emul.emul_trace_bvh2(P(c.nodes2), P(vf), P(c.tris), P(rays), C.c_longlong(len(rays)), P(ids), P(ts))
+    oi, ot = c.osc.trace_rays(rays)
+    assert np.array_equal(ids, oi) and ts.tobytes() == ot.tobytes()
+
+
+def test_tie_break_follows_reference_leaf_order(lib, oracle, emul):
+    """two coincident triangles: the reference returns the one its traversal meets first (kernel.cu:127)"""
+    sc = scenes.cornell_box()
+    s = api.SceneHandle()
+    s.add_scene(sc)
+    s.add_scene(sc)                        # every triangle twice, exact ties everywhere
+    v, t, m, l = s.arrays()
+    n2, d2 = s.build_bvh2()
+    rank = api.bvh2_leaf_order(n2, len(t))
+    osc = oracle.OracleScene(v, t, m, l, s.total_light_area, n2)
+    cam = api.make_camera(48, 48, **sc.camera)
+    rays = osc.camera_rays(cam)
+    ri, rt = osc.trace_rays(rays)
+    b = s.build_bvh(tie_rank=rank)
+    nodes, prims = b.arrays()
+    ids, ts, _ = emul_trace(emul, nodes, prims, b.info()["depth"], rays)
+    assert np.array_equal(ids, ri) and ts.tobytes() == rt.tobytes()
+    b2 = s.build_bvh()                     # without ranks the lower triangle index wins instead
+    nodes, prims = b2.arrays()
+    ids2, ts2, _ = emul_trace(emul, nodes, prims, b2.info()["depth"], rays)
+    assert ts2.tobytes() == rt.tobytes() and np.all(ids2[ids2 >= 0] < 32)
+
+
+def test_large_build_is_deterministic_and_parallel(lib):
+    sc = scenes.triangle_soup(200000)
+    s = api.SceneHandle()
+    s.add_scene(sc)
+    a = s.build_bvh(threads=1).arrays()
+    b = s.build_bvh(threads=8).arrays()
+    assert a[0].tobytes() == b[0].tobytes() and a[1].tobytes() == b[1].tobytes()

@@ -1,0 +1,115 @@
+"""Scene ingest (loadOBJ, modelLoader.h:125-210) against the real reference and the golden vectors."""
+import os
+
+import numpy as np
+import pytest
+
+from cudapathtracer_b200 import api, scenes
+from conftest import CASES, build_case
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load_via_obj(sc, tmp_path, **kw):
+    obj, mtl = scenes.to_obj(sc)
+    d = tmp_path / "models"
+    d.mkdir(exist_ok=True)
+    (d / "scene.obj").write_text(obj)
+    (d / "scene.mtl").write_text(mtl)
+    s = api.SceneHandle()
+    s.load_obj(str(d / "scene.obj"), str(d) + "/", **kw)
+    return s
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_obj_ingest_matches_golden(lib, tmp_path, name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    sc, _, _ = build_case(name)
+    s = load_via_obj(sc, tmp_path)
+    v, t, m, l = s.arrays()
+    assert v.tobytes() == g["verts"].tobytes()
+    assert t.tobytes() == g["tris"].tobytes()
+    assert m.tobytes() == g["mats"].tobytes()      # table duplicated like modelLoader.h:138-159
+    assert l.tobytes() == g["lights"].tobytes()
+    assert s.total_light_area == g["area"]
+    assert len(m) == 2 * len(sc.materials)
+
+
+def test_obj_ingest_transform_and_flip_against_reference(lib, ref, tmp_path):
+    sc = scenes.cornell_box()
+    obj, mtl = scenes.to_obj(sc)
+    ref.reset()
+    ref.load_obj_text(obj, mtl)
+    ref.load_obj_text(obj, mtl, origin=(0.35, 0.6, 0.3), scale=0.75, flip=True)   # composes like kernel.cu:591-592
+    rv, rt, rm, rl, ra = ref.arrays()
+    s = load_via_obj(sc, tmp_path)
+    d = tmp_path / "models"
+    s.load_obj(str(d / "scene.obj"), str(d) + "/", origin=(0.35, 0.6, 0.3), scale=0.75, flip=True)
+    v, t, m, l = s.arrays()
+    assert v.tobytes() == rv.tobytes() and t.tobytes() == rt.tobytes() and m.tobytes() == rm.tobytes()
+    assert l.tobytes() == rl.tobytes() and s.total_light_area == ra
+
+
+def test_obj_syntax_variants_against_reference(lib, ref, tmp_path):
+    """negative indices, v/vt/vn triples, polygons (fan), g / o / usemtl shape splits, exponents, CRLF"""
+    obj = ("mtllib scene.mtl\r\n# comment\r\nv 0 0 0\nv 1 0 0\nv 1 1.5e0 0\nv 0 1 0\nv 0.5 0.5 -1.25E-1\nvt 0 0\nvn 0 0 1\n"
+           "g quad\nusemtl a\nf 1/1/1 2/1/1 3/1/1 4/1/1\n"
+           "o tip\nusemtl b\nf -5 -4 -1\nf 2//1 3//1 5//1\n"
+           "g other extra\nf 3 4 5\nusemtl a\nf 4 1 5\n")
+    mtl = "newmtl a\nKd 0.5 0.25 0.125\nKe 0 0 0\nKa 1 1 1\nnewmtl b\n  Kd 1 1 1\n\tKe 3 2 1\n"
+    ref.reset()
+    ref.load_obj_text(obj, mtl)
+    rv, rt, rm, rl, ra = ref.arrays()
+    d = tmp_path / "models"
+    d.mkdir()
+    (d / "scene.obj").write_text(obj)
+    (d / "scene.mtl").write_text(mtl)
+    s = api.SceneHandle()
+    s.load_obj(str(d / "scene.obj"), str(d) + "/")
+    v, t, m, l = s.arrays()
+    assert len(t) == 6
+    assert v.tobytes() == rv.tobytes() and t.tobytes() == rt.tobytes() and m.tobytes() == rm.tobytes()
+    assert l.tobytes() == rl.tobytes() and s.total_light_area == ra
+
+
+def test_array_ingest_equals_obj_ingest_up_to_vertex_order(lib, tmp_path):
+    """add_scene (in-memory) and the OBJ route produce the same triangles; the OBJ route renumbers vertices in
+    first-use order (tiny_obj_loader.cc:305-339), so compare resolved corner positions and per-triangle data"""
+    sc = scenes.atrium(20000)
+    a = api.SceneHandle()
+    a.add_scene(sc)
+    b = load_via_obj(sc, tmp_path)
+    va, ta, ma, la = a.arrays()
+    vb, tb, mb, lb = b.arrays()
+    pa = va.view(np.float32).reshape(-1, 3)
+    pb = vb.view(np.float32).reshape(-1, 3)
+    for k in ("v0", "v1", "v2"):
+        assert np.array_equal(pa[ta[k]], pb[tb[k]])
+    assert np.array_equal(ta["norm"], tb["norm"], equal_nan=True) and np.array_equal(ta["mat"], tb["mat"])
+    assert ma.tobytes() == mb.tobytes() and la.tobytes() == lb.tobytes() and a.total_light_area == b.total_light_area
+
+
+def test_missing_material_is_an_error_not_an_out_of_bounds_read(lib, tmp_path):
+    d = tmp_path / "models"
+    d.mkdir()
+    (d / "s.obj").write_text("mtllib s.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\n")
+    (d / "s.mtl").write_text("newmtl a\nKd 1 1 1\n")
+    s = api.SceneHandle()
+    with pytest.raises(api.CuptError, match="no material"):
+        s.load_obj(str(d / "s.obj"), str(d) + "/")
+
+
+def test_ppm_writer_matches_reference_tonemap(lib, tmp_path):
+    g = np.load(os.path.join(GOLD, "misc.npz"))
+    x = g["tonemap_in"].astype(np.float32)
+    out = api.tonemap(x)
+    # the golden transform ran on f64 inputs; feed it the same f32-rounded values through the oracle instead
+    import oraclebind
+    assert np.array_equal(out, oraclebind.tonemap(x.astype(np.float64)))
+    w, h = 16, 16
+    p = tmp_path / "img.ppm"
+    api.write_ppm(str(p), x[: w * h], w, h)
+    toks = p.read_text().split()
+    assert toks[:4] == ["P3", "16", "16", "255"]
+    vals = np.array(toks[4:], dtype=np.int32).reshape(h, w, 3)
+    assert np.array_equal(vals[:, ::-1, :].reshape(-1, 3), out[: w * h])   # x mirrored, kernel.cu:768
