@@ -134,7 +134,7 @@ DevScene make_scene(const cupt_context* c)
 	sc.nodes = c->d_nodes; sc.prims = c->d_prims; sc.bvh2 = c->d_bvh2; sc.verts = c->d_verts; sc.tris = c->d_tris;
 	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.lights = c->d_lights;
 	sc.numLights = c->num_lights; sc.totalLightArea = c->total_light_area;
-	sc.stack_cap = std::max(c->bvh_depth, 1);
+	sc.stack_cap = std::max(c->bvh_depth, 1) + CUPT_TRI_SLOTS;
 	return sc;
 }
 
@@ -154,7 +154,10 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
 	const int mode = c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 ? 1 : 0;
 	const bool stats = c->opts.collect_stats != 0;
 	const size_t smem = mode == 0 ? (size_t)sc.stack_cap * 128 * sizeof(uint2) : 0;
-	void (*kern)(DevScene, PathBuffers, int, int) =
+	ExtendTuning tune;
+	tune.fetch_thresh = c->opts.fetch_threshold > 0 ? std::min(c->opts.fetch_threshold, 31) : 24;
+	tune.tri_thresh = c->opts.postpone_threshold > 0 ? std::min(c->opts.postpone_threshold, 32) : 1;
+	void (*kern)(DevScene, PathBuffers, int, int, ExtendTuning) =
 		mode == 0 ? (stats ? k_extend<0, true> : k_extend<0, false>) : (stats ? k_extend<1, true> : k_extend<1, false>);
 	if (c->extend_blocks[mode] == 0 || mode == 0) {
 		if (smem > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -164,7 +167,7 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
 	}
 	StageEvent ev;
 	stage_begin(c, 1, ev);
-	kern<<<c->extend_blocks[mode], 128, smem, c->stream>>>(sc, c->pb, depth, qsel);
+	kern<<<c->extend_blocks[mode], 128, smem, c->stream>>>(sc, c->pb, depth, qsel, tune);
 	stage_end(c, ev);
 	CK(cudaGetLastError());
 	c->launches++; c->extend_launches++;

@@ -117,10 +117,127 @@ __global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb)
 }
 
 // ---- extend: closest hit for every queued path ---------------------------------------------------------------
-// Persistent warps: each warp pulls 32 queue entries at a time from a global cursor (one atomic per warp) until
-// the queue is empty.  MODE 0 = wide BVH, 1 = reference BVH2 (parity mode).
+// Persistent warps over a global queue cursor.  MODE 0 = wide BVH, 1 = reference BVH2 (parity mode).
+//
+// MODE 0 is warp-synchronous: every lane carries its own ray, the warp runs node step / primitive steps / pop in
+// lock step and re-forms after every iteration, and
+//   * a lane whose ray has ended is refilled from the queue as soon as fewer than `fetch_thresh` lanes are busy
+//     (the first version traced 32 rays to the end per fetch and ran at 7 of 32 threads per instruction on
+//     diffuse bounces, profiles/r1a_extend_metrics.md),
+//   * when fewer than `tri_thresh` lanes have primitives to test, lanes that can go on with node work put their
+//     primitive group on the stack and come back to it later, so that primitive tests run with fuller warps
+//     (postponing after Ylitie, Karras, Laine, HPG 2017; the bookkeeping below is ours and bounds the stack:
+//     at most TRI_SLOTS postponed groups per ray, and a lane only postpones when it does a node step next, which
+//     guarantees progress).
+// Queue entries are handed out from warp-private chunks of CHUNK entries (one atomic per chunk).
+struct ExtendTuning {
+	int32_t fetch_thresh;   // refill idle lanes when active lanes <= this
+	int32_t tri_thresh;     // postpone primitive tests when lanes with primitives < this
+};
+#define CUPT_TRI_SLOTS 4      // stack entries reserved for postponed primitive groups
+#define CUPT_QUEUE_CHUNK 64u
+
+template <bool STATS>
+__device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffers& pb, const uint32_t count, uint32_t* cursor,
+                                            const uint32_t* __restrict__ queue, uint2* stack, const int stride,
+                                            const ExtendTuning tune, uint32_t& n_nodes, uint32_t& n_tris, uint32_t& n_rays)
+{
+	const uint32_t FULL = 0xffffffffu;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t lt_mask = (1u << lane) - 1u;
+	const int node_cap = sc.stack_cap - CUPT_TRI_SLOTS;
+	bool active = false, exhausted = false;
+	uint32_t chunk_next = 0u, chunk_end = 0u;
+	WideRay r;
+	uint2 ngroup = make_uint2(0u, 0u), tgroup = make_uint2(0u, 0u);
+	int sp = 0, tpushed = 0;
+	uint32_t slot = 0u;
+	for (;;) {
+		uint32_t act = __ballot_sync(FULL, active);
+		if (!exhausted && __popc(act) <= tune.fetch_thresh) {
+			uint32_t need = ~act;
+			while (need != 0u) {
+				if (chunk_next >= chunk_end) {
+					uint32_t b = 0u;
+					if (lane == 0u) b = atomicAdd(cursor, CUPT_QUEUE_CHUNK);
+					b = __shfl_sync(FULL, b, 0);
+					if (b >= count) { exhausted = true; break; }
+					chunk_next = b; chunk_end = min(b + CUPT_QUEUE_CHUNK, count);
+				}
+				const uint32_t avail = chunk_end - chunk_next;
+				const uint32_t my = __popc(need & lt_mask);
+				if (((need >> lane) & 1u) && my < avail) {
+					slot = queue[chunk_next + my];
+					const float4 a = pb.rayA[slot];
+					const float4 b = pb.rayB[slot];
+					wide_ray_init(r, mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y));
+					ngroup = make_uint2(0u, 0x80000000u); tgroup = make_uint2(0u, 0u);
+					sp = 0; tpushed = 0;
+					active = true;
+					++n_rays;
+				}
+				chunk_next += min((uint32_t)__popc(need), avail);
+				need = ~__ballot_sync(FULL, active);
+			}
+			act = __ballot_sync(FULL, active);
+		}
+		if (act == 0u) break;
+
+		// ---- node step ------------------------------------------------------------------------------------------
+		if (active) {
+			if (group_has_node(ngroup)) {
+				uint2 rest;
+				wide_node_step(sc.nodes, r, ngroup, rest, tgroup);
+				if (group_has_node(rest)) { stack[sp * stride] = rest; ++sp; }
+				if (STATS) ++n_nodes;
+			} else {
+				tgroup = ngroup;
+				ngroup = make_uint2(0u, 0u);
+			}
+		}
+		// ---- primitive steps, warp-synchronous, with postponing ----------------------------------------------------
+		for (;;) {
+			const bool has = active && tgroup.y != 0u;
+			const uint32_t m = __ballot_sync(FULL, has);
+			if (m == 0u) break;
+			bool test = has;
+			if (__popc(m) < tune.tri_thresh) {
+				if (has && tpushed < CUPT_TRI_SLOTS) {
+					if (group_has_node(ngroup)) {                       // node work in hand: primitives go to the stack
+						stack[sp * stride] = tgroup; ++sp; ++tpushed;
+						tgroup.y = 0u; test = false;
+					} else if (sp > 0) {
+						const uint2 top = stack[(sp - 1) * stride];
+						if (group_has_node(top)) {                       // swap with the node group on top of the stack
+							stack[(sp - 1) * stride] = tgroup; ++tpushed;
+							ngroup = top; tgroup.y = 0u; test = false;
+						}
+					}
+				}
+				if (__ballot_sync(FULL, test) == 0u) break;
+			}
+			if (test) {
+				wide_prim_step(sc.prims, r, tgroup);
+				if (STATS) ++n_tris;
+			}
+		}
+		// ---- pop / finish -------------------------------------------------------------------------------------------
+		if (active && !group_has_node(ngroup) && tgroup.y == 0u) {
+			if (sp == 0) {
+				reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(r.best, __int_as_float(r.best_id));
+				active = false;
+			} else {
+				--sp;
+				ngroup = stack[sp * stride];
+				if (!group_has_node(ngroup)) --tpushed;
+			}
+		}
+	}
+	(void)node_cap;
+}
+
 template <int MODE, bool STATS>
-__global__ void __launch_bounds__(128) k_extend(DevScene sc, PathBuffers pb, int depth, int qsel)
+__global__ void __launch_bounds__(128) k_extend(DevScene sc, PathBuffers pb, int depth, int qsel, ExtendTuning tune)
 {
 	extern __shared__ uint2 smem_stack[];
 	const uint32_t lane = threadIdx.x & 31u;
@@ -128,26 +245,26 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathBuffers pb, int
 	uint32_t* cursor = &pb.counters[64 + depth];
 	const uint32_t* __restrict__ queue = pb.queue[qsel];
 	uint32_t n_nodes = 0, n_tris = 0, n_rays = 0;
-	for (;;) {
-		uint32_t base = 0;
-		if (lane == 0) base = atomicAdd(cursor, 32u);
-		base = __shfl_sync(0xffffffffu, base, 0);
-		if (base >= count) break;
-		const uint32_t qi = base + lane;
-		if (qi < count) {
-			const uint32_t slot = queue[qi];
-			const float4 a = pb.rayA[slot];
-			const float4 b = pb.rayB[slot];
-			const f3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, b.x, b.y);
-			Hit hit;
-			if (MODE == 0)
-				traverse_wide<STATS>(sc.nodes, sc.prims, o, d, hit, smem_stack + threadIdx.x, blockDim.x, sc.stack_cap, n_nodes, n_tris);
-			else
-				traverse_bvh2_ref<STATS>(sc.bvh2, sc.verts, sc.tris, o, d, hit, n_nodes, n_tris);
-			reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(hit.t, __int_as_float(hit.id));
-			++n_rays;
+	if (MODE == 0) {
+		extend_wide<STATS>(sc, pb, count, cursor, queue, smem_stack + threadIdx.x, blockDim.x, tune, n_nodes, n_tris, n_rays);
+	} else {
+		for (;;) {
+			uint32_t base = 0;
+			if (lane == 0) base = atomicAdd(cursor, 32u);
+			base = __shfl_sync(0xffffffffu, base, 0);
+			if (base >= count) break;
+			const uint32_t qi = base + lane;
+			if (qi < count) {
+				const uint32_t slot = queue[qi];
+				const float4 a = pb.rayA[slot];
+				const float4 b = pb.rayB[slot];
+				Hit hit;
+				traverse_bvh2_ref<STATS>(sc.bvh2, sc.verts, sc.tris, mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), hit, n_nodes, n_tris);
+				reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(hit.t, __int_as_float(hit.id));
+				++n_rays;
+			}
+			__syncwarp();
 		}
-		__syncwarp();
 	}
 	// one atomic per warp for the ray counter (rays are counted, not nominal: SURVEY.md §8d)
 	for (int ofs = 16; ofs > 0; ofs >>= 1) {

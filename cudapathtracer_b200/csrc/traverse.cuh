@@ -63,111 +63,161 @@ __device__ __forceinline__ float sphere_nearest(const f3 o, const f3 d, const fl
 	return CUPT_MAX_FLOAT;
 }
 
-__device__ __forceinline__ float u8f(uint32_t w, int j) { return (float)((w >> (8 * j)) & 0xffu); }
+// Byte j of w as the float 2^15 + b without I2F (which runs on the quarter-rate XU pipe and was the top stall source
+// of the first profile, profiles/r1a_extend_opcodes.md): one PRMT drops the byte into mantissa bits 8..15 of 2^15.
+// The constant 2^15 is folded into the per-node offset (o' = o - 2^15 s), which costs 2^-9 of a grid cell of
+// accuracy and is covered by the per-axis slack below.
+#define CUPT_QBIAS 32768.0f
+__device__ __forceinline__ float u8f_biased(uint32_t w, int j)
+{
+#ifdef CUPT_HOST_EMUL
+	return CUPT_QBIAS + (float)((w >> (8 * j)) & 0xffu);
+#else
+	return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7604u + ((uint32_t)j << 4)));
+#endif
+}
 
-// stack entry i of this thread lives at stack[i * stride]
+// Per-ray traversal state of the wide BVH (registers).
+struct WideRay {
+	f3 o, d;
+	float ix, iy, iz;      // 1/d, +-1e20 for a (near-)zero component
+	uint32_t oct_inv;      // bit 2/1/0 set when d.x/y/z is non-negative
+	float best;            // current closest t (kernel.cu:117: starts at MAX_FLOAT)
+	int32_t best_id;
+	uint32_t best_rank;    // rank < 0 never holds: a tie can only replace an existing hit
+};
+
+__device__ __forceinline__ void wide_ray_init(WideRay& r, const f3 o, const f3 d)
+{
+	const float big = 1.0e20f;   // keeps 2^15 * scale / d finite for every scene inside the reference's +-1e4 world (BVH.h:21-25)
+	r.o = o; r.d = d;
+	r.ix = fabsf(d.x) > 1.0e-20f ? 1.0f / d.x : copysignf(big, d.x);
+	r.iy = fabsf(d.y) > 1.0e-20f ? 1.0f / d.y : copysignf(big, d.y);
+	r.iz = fabsf(d.z) > 1.0e-20f ? 1.0f / d.z : copysignf(big, d.z);
+	r.oct_inv = (r.ix < 0.0f ? 0u : 4u) | (r.iy < 0.0f ? 0u : 2u) | (r.iz < 0.0f ? 0u : 1u);
+	r.best = CUPT_MAX_FLOAT; r.best_id = -1; r.best_rank = 0u;
+}
+
+// A "group" is {base index, bit mask}: node group = {child_base, hits << 24 | imask} (hit bits in front-to-back
+// order, highest first), primitive group = {tri_base, one bit per 48-byte record}; a group whose mask has no bit
+// above 23 is a primitive group.
+__device__ __forceinline__ bool group_has_node(const uint2 g) { return g.y > 0x00ffffffu; }
+
+// Takes the nearest untested child out of `ngroup` (the caller pushes what is left), fetches its 80-byte node with
+// five 128-bit ld.global.nc and tests the eight quantised child boxes against [0, best]; returns the children hit
+// as a new node group and a primitive group.
+__device__ __forceinline__ void wide_node_step(const uint4* __restrict__ nodes, const WideRay& r, uint2& ngroup, uint2& rest, uint2& tgroup)
+{
+	const uint32_t hits = ngroup.y;
+	const uint32_t bit = 31u - __clz(hits);
+	rest = make_uint2(ngroup.x, hits & ~(1u << bit));
+	const uint32_t slot = (bit - 24u) ^ r.oct_inv;
+	const uint32_t rel = __popc(hits & 0xffu & ~(0xffffffffu << slot));
+	const uint4* np = nodes + (size_t)(ngroup.x + rel) * 5u;
+	const uint4 n0 = ldg_nc_u4(np + 0), n1 = ldg_nc_u4(np + 1), n2 = ldg_nc_u4(np + 2), n3 = ldg_nc_u4(np + 3), n4 = ldg_nc_u4(np + 4);
+	const bool negx = r.ix < 0.0f, negy = r.iy < 0.0f, negz = r.iz < 0.0f;
+	const uint32_t oct_inv4 = r.oct_inv * 0x01010101u;
+	const float sx = __uint_as_float((n0.w & 0xffu) << 23) * r.ix;
+	const float sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * r.iy;
+	const float sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * r.iz;
+	const float ox = (__uint_as_float(n0.x) - r.o.x) * r.ix;
+	const float oy = (__uint_as_float(n0.y) - r.o.y) * r.iy;
+	const float oz = (__uint_as_float(n0.z) - r.o.z) * r.iz;
+	// Plane distances are t = (2^15 + q) * s + (o - 2^15 s).  Rounding slack PER AXIS (a common slack lets an axis
+	// with a zero direction component, |o| ~ 1e30, open every box of the tree): 2^-21 relative to the magnitudes
+	// involved plus 2^-6 of a grid cell, subtracted from the near planes and added to the far planes through the
+	// two offsets, so it costs nothing per child.
+	const float kx = fmaf(fabsf(sx), 0.015625f, fmaf(255.0f, fabsf(sx), fabsf(ox)) * 4.76837158203125e-7f);
+	const float ky = fmaf(fabsf(sy), 0.015625f, fmaf(255.0f, fabsf(sy), fabsf(oy)) * 4.76837158203125e-7f);
+	const float kz = fmaf(fabsf(sz), 0.015625f, fmaf(255.0f, fabsf(sz), fabsf(oz)) * 4.76837158203125e-7f);
+	const float bx = fmaf(-CUPT_QBIAS, sx, ox), by = fmaf(-CUPT_QBIAS, sy, oy), bz = fmaf(-CUPT_QBIAS, sz, oz);
+	const float onx = bx - kx, ony = by - ky, onz = bz - kz;
+	const float ofx = bx + kx, ofy = by + ky, ofz = bz + kz;
+	const uint32_t imask = n0.w >> 24;
+	uint32_t hitmask = 0u;
+#pragma unroll
+	for (int h = 0; h < 2; ++h) {
+		const uint32_t meta4 = h ? n1.w : n1.z;
+		const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+		const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+		const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
+		const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+		const uint32_t qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
+		const uint32_t qhx = h ? n3.w : n3.z, qhy = h ? n4.y : n4.x, qhz = h ? n4.w : n4.z;
+		const uint32_t nx = negx ? qhx : qlx, fx = negx ? qlx : qhx;
+		const uint32_t ny = negy ? qhy : qly, fy = negy ? qly : qhy;
+		const uint32_t nz = negz ? qhz : qlz, fz = negz ? qlz : qhz;
+#pragma unroll
+		for (int j = 0; j < 4; ++j) {
+			const float tnx = fmaf(u8f_biased(nx, j), sx, onx), tny = fmaf(u8f_biased(ny, j), sy, ony), tnz = fmaf(u8f_biased(nz, j), sz, onz);
+			const float tfx = fmaf(u8f_biased(fx, j), sx, ofx), tfy = fmaf(u8f_biased(fy, j), sy, ofy), tfz = fmaf(u8f_biased(fz, j), sz, ofz);
+			const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+			const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, r.best));
+			if (tmin <= tmax) {
+				const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu, bi = (bit_index4 >> (8 * j)) & 0xffu;
+				hitmask |= cb << bi;
+			}
+		}
+	}
+	ngroup = make_uint2(n1.x, (hitmask & 0xff000000u) | imask);
+	tgroup = make_uint2(n1.y, hitmask & 0x00ffffffu);
+}
+
+// Tests the lowest-numbered pending record of `tgroup` (three 128-bit fetches) and updates the closest hit with the
+// reference's acceptance rule `0 < t && t < closestT` (kernel.cu:127), equal t resolved by rank.
+__device__ __forceinline__ void wide_prim_step(const float4* __restrict__ prims, WideRay& r, uint2& tgroup)
+{
+	const uint32_t k = __ffs(tgroup.y) - 1u;
+	tgroup.y &= tgroup.y - 1u;
+	const float4* pp = prims + (size_t)(tgroup.x + k) * 3u;
+	const float4 r0 = ldg_nc_f4(pp + 0), r1 = ldg_nc_f4(pp + 1), r2 = ldg_nc_f4(pp + 2);
+	const uint32_t kind = __float_as_uint(r2.w);
+	float t;
+	if (kind == 0u) t = tri_refexact(r.o, r.d, r0, r1, r2);
+	else t = sphere_nearest(r.o, r.d, r0, r1);
+	const uint32_t rank = __float_as_uint(r2.z);
+	if (0.0f < t && (t < r.best || (t == r.best && rank < r.best_rank))) {
+		r.best = t; r.best_rank = rank;
+		r.best_id = (int32_t)(__float_as_uint(r2.y) | (kind << 31));
+	}
+}
+
+// One ray, start to end (host emulation harness, and the definition the warp-synchronous kernel loop in kernels.cuh
+// must agree with).  Stack entry i of this thread lives at stack[i * stride].
 template <bool STATS>
 __device__ __forceinline__ void traverse_wide(const uint4* __restrict__ nodes, const float4* __restrict__ prims,
                                               const f3 o, const f3 d, Hit& hit, uint2* stack, const int stride,
                                               const int stack_cap, uint32_t& n_nodes, uint32_t& n_tris)
 {
-	const float big = 1.0e30f;
-	const float ix = fabsf(d.x) > 1.0e-30f ? 1.0f / d.x : copysignf(big, d.x);
-	const float iy = fabsf(d.y) > 1.0e-30f ? 1.0f / d.y : copysignf(big, d.y);
-	const float iz = fabsf(d.z) > 1.0e-30f ? 1.0f / d.z : copysignf(big, d.z);
-	const bool negx = ix < 0.0f, negy = iy < 0.0f, negz = iz < 0.0f;
-	const uint32_t oct_inv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
-	const uint32_t oct_inv4 = oct_inv * 0x01010101u;
-
-	float best = CUPT_MAX_FLOAT;
-	int32_t best_id = -1;
-	uint32_t best_rank = 0u;   // rank < 0 never holds: a tie can only replace an existing hit
-
+	WideRay r;
+	wide_ray_init(r, o, d);
 	uint2 ngroup = make_uint2(0u, 0x80000000u);
 	uint2 tgroup = make_uint2(0u, 0u);
 	int sp = 0;
-
 	for (;;) {
-		if (ngroup.y > 0x00ffffffu) {
-			const uint32_t hits = ngroup.y;
-			const uint32_t bit = 31u - __clz(hits);
-			ngroup.y &= ~(1u << bit);
-			if (ngroup.y > 0x00ffffffu) {
-				if (sp < stack_cap) stack[sp * stride] = ngroup;
+		if (group_has_node(ngroup)) {
+			uint2 rest;
+			wide_node_step(nodes, r, ngroup, rest, tgroup);
+			if (group_has_node(rest)) {
+				if (sp < stack_cap) stack[sp * stride] = rest;
 				++sp;   // entries beyond the capacity are dropped only if the builder's depth bound is violated (checked on upload)
 			}
-			const uint32_t slot = (bit - 24u) ^ oct_inv;
-			const uint32_t rel = __popc(hits & 0xffu & ~(0xffffffffu << slot));
-			const uint4* np = nodes + (size_t)(ngroup.x + rel) * 5u;
-			const uint4 n0 = ldg_nc_u4(np + 0), n1 = ldg_nc_u4(np + 1), n2 = ldg_nc_u4(np + 2), n3 = ldg_nc_u4(np + 3),
-			            n4 = ldg_nc_u4(np + 4);
 			if (STATS) ++n_nodes;
-			const float sx = __uint_as_float((n0.w & 0xffu) << 23) * ix;
-			const float sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * iy;
-			const float sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * iz;
-			const float ox = (__uint_as_float(n0.x) - o.x) * ix;
-			const float oy = (__uint_as_float(n0.y) - o.y) * iy;
-			const float oz = (__uint_as_float(n0.z) - o.z) * iz;
-			// rounding slack of t = q * s + o', both sides (2 * 2^-21 relative to the magnitudes involved)
-			const float slack = fmaxf(fmaxf(fmaf(255.0f, fabsf(sx), fabsf(ox)), fmaf(255.0f, fabsf(sy), fabsf(oy))),
-			                          fmaf(255.0f, fabsf(sz), fabsf(oz))) * 9.5367431640625e-7f;
-			const uint32_t imask = n0.w >> 24;
-			uint32_t hitmask = 0u;
-#pragma unroll
-			for (int h = 0; h < 2; ++h) {
-				const uint32_t meta4 = h ? n1.w : n1.z;
-				const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-				const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-				const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
-				const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-				const uint32_t qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
-				const uint32_t qhx = h ? n3.w : n3.z, qhy = h ? n4.y : n4.x, qhz = h ? n4.w : n4.z;
-				const uint32_t nx = negx ? qhx : qlx, fx = negx ? qlx : qhx;
-				const uint32_t ny = negy ? qhy : qly, fy = negy ? qly : qhy;
-				const uint32_t nz = negz ? qhz : qlz, fz = negz ? qlz : qhz;
-#pragma unroll
-				for (int j = 0; j < 4; ++j) {
-					const float tnx = fmaf(u8f(nx, j), sx, ox), tny = fmaf(u8f(ny, j), sy, oy), tnz = fmaf(u8f(nz, j), sz, oz);
-					const float tfx = fmaf(u8f(fx, j), sx, ox), tfy = fmaf(u8f(fy, j), sy, oy), tfz = fmaf(u8f(fz, j), sz, oz);
-					const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
-					const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, best));
-					if (tmin <= tmax + slack) {
-						const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu, bi = (bit_index4 >> (8 * j)) & 0xffu;
-						hitmask |= cb << bi;
-					}
-				}
-			}
-			ngroup = make_uint2(n1.x, (hitmask & 0xff000000u) | imask);
-			tgroup = make_uint2(n1.y, hitmask & 0x00ffffffu);
 		} else {
 			tgroup = ngroup;
 			ngroup = make_uint2(0u, 0u);
 		}
-
 		while (tgroup.y != 0u) {
-			const uint32_t k = __ffs(tgroup.y) - 1u;
-			tgroup.y &= tgroup.y - 1u;
-			const float4* pp = prims + (size_t)(tgroup.x + k) * 3u;
-			const float4 r0 = ldg_nc_f4(pp + 0), r1 = ldg_nc_f4(pp + 1), r2 = ldg_nc_f4(pp + 2);
+			wide_prim_step(prims, r, tgroup);
 			if (STATS) ++n_tris;
-			const uint32_t kind = __float_as_uint(r2.w);
-			float t;
-			if (kind == 0u) t = tri_refexact(o, d, r0, r1, r2);
-			else t = sphere_nearest(o, d, r0, r1);
-			const uint32_t rank = __float_as_uint(r2.z);
-			if (0.0f < t && (t < best || (t == best && rank < best_rank))) {
-				best = t; best_rank = rank;
-				best_id = (int32_t)(__float_as_uint(r2.y) | (kind << 31));
-			}
 		}
-
-		if (ngroup.y <= 0x00ffffffu) {
+		if (!group_has_node(ngroup)) {
 			if (sp == 0) break;
 			--sp;
 			ngroup = stack[sp * stride];
 		}
 	}
-	hit.t = best; hit.id = best_id; hit.rank = best_rank;
+	hit.t = r.best; hit.id = r.best_id; hit.rank = r.best_rank;
 }
 
 // trace(), kernel.cu:112-161, with rayAABBIntersect (BVH.h:51-83) and triIntersect (modelLoader.h:49-82) in the
