@@ -153,7 +153,7 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
 {
 	const int mode = c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 ? 1 : 0;
 	const bool stats = c->opts.collect_stats != 0;
-	const size_t smem = mode == 0 ? (size_t)sc.stack_cap * 128 * sizeof(uint2) : 0;
+	const size_t smem = mode == 0 ? (size_t)sc.stack_cap * 128 * sizeof(uint2) + 128 * 16 : 0;   // stacks + per-warp keys/list/ids
 	ExtendTuning tune;
 	tune.fetch_thresh = c->opts.fetch_threshold > 0 ? std::min(c->opts.fetch_threshold, 31) : 24;
 	tune.tri_thresh = c->opts.postpone_threshold > 0 ? std::min(c->opts.postpone_threshold, 32) : 1;
@@ -312,6 +312,8 @@ int cupt_set_bvh(cupt_context* c, const cupt_bvh* b)
 {
 	if (!c || !b) return set_error(CUPT_ERR_INVALID, "bad arguments");
 	if (b->depth > 64) return set_error(CUPT_ERR_LIMIT, "wide BVH depth %d exceeds the traversal stack (64)", b->depth);
+	if (b->prims.size() >= ((size_t)1 << 27))
+		return set_error(CUPT_ERR_LIMIT, "more than 2^27 primitive records (the extend kernel packs record index and lane into 32 bits)");
 	CK(cudaSetDevice(c->device));
 	int rc;
 	if ((rc = upload(&c->d_nodes, b->nodes.data(), b->nodes.size() * sizeof(Node8), c->stream))) return rc;

@@ -136,11 +136,14 @@ struct ExtendTuning {
 };
 #define CUPT_TRI_SLOTS 4      // stack entries reserved for postponed primitive groups
 #define CUPT_QUEUE_CHUNK 64u
+#ifndef CUPT_EXTEND_MIN_BLOCKS
+#define CUPT_EXTEND_MIN_BLOCKS 7
+#endif
 
 template <bool STATS>
 __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffers& pb, const uint32_t count, uint32_t* cursor,
                                             const uint32_t* __restrict__ queue, uint2* stack, const int stride,
-                                            const ExtendTuning tune, uint32_t& n_nodes, uint32_t& n_tris, uint32_t& n_rays)
+                                            uint32_t* wlist, unsigned long long* wkeys, uint32_t* wids, const ExtendTuning tune, uint32_t& n_nodes, uint32_t& n_tris, uint32_t& n_rays)
 {
 	const uint32_t FULL = 0xffffffffu;
 	const uint32_t lane = threadIdx.x & 31u;
@@ -195,31 +198,79 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 				ngroup = make_uint2(0u, 0u);
 			}
 		}
-		// ---- primitive steps, warp-synchronous, with postponing ----------------------------------------------------
-		for (;;) {
+		// ---- primitive tests, shared across the warp ----------------------------------------------------------------
+		// Lanes with pending primitives are few (3.2 of 32 in profiles/r1c, where this phase took 40 % of the issue
+		// slots), so the (ray, primitive) pairs of the whole warp are listed in shared memory and every lane tests
+		// one pair: lane i fetches the owner's ray by shuffle, runs the exact test and merges its hit into the
+		// owner's 64-bit key (t bits << 32 | rank) with a shared-memory atomicMin, which is the acceptance rule
+		// `t < best || (t == best && rank < best_rank)` because positive floats order like their bit patterns.
+		if (tune.tri_thresh > 1) {
+			// (optional) postponing while few lanes have primitives; see the header comment
 			const bool has = active && tgroup.y != 0u;
 			const uint32_t m = __ballot_sync(FULL, has);
-			if (m == 0u) break;
-			bool test = has;
-			if (__popc(m) < tune.tri_thresh) {
-				if (has && tpushed < CUPT_TRI_SLOTS) {
-					if (group_has_node(ngroup)) {                       // node work in hand: primitives go to the stack
-						stack[sp * stride] = tgroup; ++sp; ++tpushed;
-						tgroup.y = 0u; test = false;
-					} else if (sp > 0) {
-						const uint2 top = stack[(sp - 1) * stride];
-						if (group_has_node(top)) {                       // swap with the node group on top of the stack
-							stack[(sp - 1) * stride] = tgroup; ++tpushed;
-							ngroup = top; tgroup.y = 0u; test = false;
-						}
+			if (m != 0u && __popc(m) < tune.tri_thresh && has && tpushed < CUPT_TRI_SLOTS) {
+				if (group_has_node(ngroup)) {                       // node work in hand: primitives go to the stack
+					stack[sp * stride] = tgroup; ++sp; ++tpushed;
+					tgroup.y = 0u;
+				} else if (sp > 0) {
+					const uint2 top = stack[(sp - 1) * stride];
+					if (group_has_node(top)) {                       // swap with the node group on top of the stack
+						stack[(sp - 1) * stride] = tgroup; ++tpushed;
+						ngroup = top; tgroup.y = 0u;
 					}
 				}
-				if (__ballot_sync(FULL, test) == 0u) break;
 			}
-			if (test) {
-				wide_prim_step(sc.prims, r, tgroup);
+		}
+		for (;;) {
+			const uint32_t cnt = active ? (uint32_t)__popc(tgroup.y) : 0u;
+			uint32_t incl = cnt;
+#pragma unroll
+			for (int ofs = 1; ofs < 32; ofs <<= 1) {
+				const uint32_t v = __shfl_up_sync(FULL, incl, ofs);
+				if (lane >= (uint32_t)ofs) incl += v;
+			}
+			const uint32_t total = __shfl_sync(FULL, incl, 31);
+			if (total == 0u) break;
+			uint32_t pos = incl - cnt;
+			while (tgroup.y != 0u && pos < 32u) {
+				const uint32_t k = __ffs(tgroup.y) - 1u;
+				tgroup.y &= tgroup.y - 1u;
+				wlist[pos++] = ((tgroup.x + k) << 5) | lane;
+			}
+			const unsigned long long mykey = ((unsigned long long)__float_as_uint(r.best) << 32) | r.best_rank;
+			wkeys[lane] = mykey;
+			__syncwarp();
+			const bool work = lane < total;
+			const uint32_t e = work ? wlist[lane] : 0u;
+			const uint32_t owner = e & 31u;
+			f3 po, pd;
+			po.x = __shfl_sync(FULL, r.o.x, owner); po.y = __shfl_sync(FULL, r.o.y, owner); po.z = __shfl_sync(FULL, r.o.z, owner);
+			pd.x = __shfl_sync(FULL, r.d.x, owner); pd.y = __shfl_sync(FULL, r.d.y, owner); pd.z = __shfl_sync(FULL, r.d.z, owner);
+			unsigned long long hkey = ~0ull;
+			uint32_t hid = 0u;
+			if (work) {
+				const float4* pp = sc.prims + (size_t)(e >> 5) * 3u;
+				const float4 r0 = ldg_nc_f4(pp + 0), r1 = ldg_nc_f4(pp + 1), r2 = ldg_nc_f4(pp + 2);
+				const uint32_t kind = __float_as_uint(r2.w);
+				float t;
+				if (kind == 0u) t = tri_refexact(po, pd, r0, r1, r2);
+				else t = sphere_nearest(po, pd, r0, r1);
+				if (0.0f < t) {
+					hkey = ((unsigned long long)__float_as_uint(t) << 32) | __float_as_uint(r2.z);
+					hid = __float_as_uint(r2.y) | (kind << 31);
+					atomicMin(&wkeys[owner], hkey);
+				}
 				if (STATS) ++n_tris;
 			}
+			__syncwarp();
+			if (hkey != ~0ull && wkeys[owner] == hkey) wids[owner] = hid;
+			__syncwarp();
+			const unsigned long long nk = wkeys[lane];
+			if (nk != mykey) {
+				r.best = __uint_as_float((uint32_t)(nk >> 32)); r.best_rank = (uint32_t)nk; r.best_id = (int32_t)wids[lane];
+			}
+			if (total <= 32u) break;   // everything listed in this round
+			__syncwarp();
 		}
 		// ---- pop / finish -------------------------------------------------------------------------------------------
 		if (active && !group_has_node(ngroup) && tgroup.y == 0u) {
@@ -237,7 +288,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 }
 
 template <int MODE, bool STATS>
-__global__ void __launch_bounds__(128) k_extend(DevScene sc, PathBuffers pb, int depth, int qsel, ExtendTuning tune)
+__global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene sc, PathBuffers pb, int depth, int qsel, ExtendTuning tune)
 {
 	extern __shared__ uint2 smem_stack[];
 	const uint32_t lane = threadIdx.x & 31u;
@@ -246,7 +297,12 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathBuffers pb, int
 	const uint32_t* __restrict__ queue = pb.queue[qsel];
 	uint32_t n_nodes = 0, n_tris = 0, n_rays = 0;
 	if (MODE == 0) {
-		extend_wide<STATS>(sc, pb, count, cursor, queue, smem_stack + threadIdx.x, blockDim.x, tune, n_nodes, n_tris, n_rays);
+		// shared memory: per-thread stacks [stack_cap][128] uint2, then per warp: 32 keys (u64), 32 list entries, 32 ids
+		unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_stack + (size_t)sc.stack_cap * blockDim.x);
+		uint32_t* lists = reinterpret_cast<uint32_t*>(keys + blockDim.x);
+		const uint32_t w = threadIdx.x >> 5;
+		extend_wide<STATS>(sc, pb, count, cursor, queue, smem_stack + threadIdx.x, blockDim.x, lists + 64u * w, keys + 32u * w,
+		                   lists + 64u * w + 32u, tune, n_nodes, n_tris, n_rays);
 	} else {
 		for (;;) {
 			uint32_t base = 0;

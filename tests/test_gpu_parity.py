@@ -179,14 +179,17 @@ def test_full_size_properties(ctx, lib):
     ri, rt = ctx.primary_hits()
     differ = (wi != ri) | (wt.view(np.uint32) != rt.view(np.uint32))
     assert differ.sum() <= 64 and np.all(wt[differ] <= rt[differ])            # closed room: wide never finds a farther hit
-    assert np.all(wi >= 0) and np.all(wt < 60)                                 # closed hall: the wide traversal loses no primary ray
+    # closed hall: apart from a handful of rays that slip between two triangles of the non-watertight test
+    # (modelLoader.h:74-79; the brute force misses them too), every primary ray hits within the hall's diagonal
+    assert (wi < 0).sum() <= 16 and np.all(wt[wi >= 0] < 60)
     assert (ri < 0).sum() <= 64                                                # (the reference's slab test may, BVH.h:65,79)
     # hit point lies on the reported triangle's plane
     rays = ctx.camera_rays()
     v, t, m, l = s.arrays()
     pos = v.view(np.float32).reshape(-1, 3).astype(np.float64)
-    p = rays[:, :3] + rays[:, 3:] * wt[:, None].astype(np.float64)
-    tr = t[wi]
+    ok = wi >= 0
+    p = rays[ok, :3] + rays[ok, 3:] * wt[ok, None].astype(np.float64)
+    tr = t[wi[ok]]
     dist = np.einsum("ij,ij->i", p - pos[tr["v0"]], tr["norm"].astype(np.float64))
     assert np.abs(dist).max() < 1e-3
     # linearity of the accumulator: 2 x render(1 spp ranges) sums; normalised mean is bounded by the emission

@@ -9,7 +9,8 @@ def main():
     W = 1024; SPP = int(os.environ.get("SPP", "32"))
     sc = scenes.atrium(262144)
     s = api.SceneHandle(); s.add_scene(sc)
-    b = s.build_bvh()
+    b = s.build_bvh(sah_bins=int(os.environ.get("BINS", "0")), max_leaf_tris=int(os.environ.get("LEAF", "0")))
+    print("bvh", b.info(), flush=True)
     cam = api.make_camera(W, W, **sc.camera)
     ctx = api.Context(0)
     ctx.set_scene(s); ctx.set_bvh(b); ctx.set_camera(cam)
