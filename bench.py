@@ -129,6 +129,22 @@ def cpu_reference(scene_handle, cam, spp, threads):
     return rays, time.perf_counter() - t0, "port", 0.0
 
 
+def legacy_gpu(scene_handle, cam, spp=16):
+    """reported baseline: the reference's own kernel.cu rebuilt for sm_100a (oracle/_ref/libcupt_legacy.so), its live
+    integrator (fixed-length BDPT, kernel.cu:217-415), 512-thread blocks, one launch + device sync per sample"""
+    try:
+        import legacybind
+        if not legacybind.available() or legacybind.image_dim() != W:
+            return {"unavailable": "oracle/_ref/libcupt_legacy.so not built for this image size"}
+        v, t, m, l = scene_handle.arrays()
+        r = legacybind.render(v, t, m, l, scene_handle.total_light_area, cam, spp)
+        return {"value": r["rays"] / (r["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "msamples_per_s": W * H * spp / (r["ms"] * 1e-3) / 1e6,
+                "ms": r["ms"], "spp": spp, "rays_per_sample": r["rays"] / (W * H * spp), "bvh_depth": r["depth"], "bvh_build_s": r["build_s"],
+                "what": "original kernel.cu, compile patches only, -arch=sm_100a, drawPixel (BDPT) per sample with cudaDeviceSynchronize; rays counted in a second, untimed run of the same length"}
+    except Exception as e:   # a reported baseline must not take the bench line down
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -294,6 +310,8 @@ def main():
             rays, dt, kind, tb = cpu_reference(s, cam, spp_cpu, threads)
             line["cpu_baseline"] = {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
                                     "sample": f"{W}x{H} x {spp_cpu} spp of the same frame ({rays} rays in {dt:.1f} s; reference BVH build {tb:.1f} s not included)"}
+        if world == 1 and not args.no_cpu_baseline:
+            line["legacy_gpu"] = legacy_gpu(s, cam)
         print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:

@@ -75,3 +75,31 @@ g++ -O2 -fPIC -ffp-contract=off -c "$REF/tiny_obj_loader.cc" -o "$TMP/tiny_obj_l
   -c "$TMP/ref_tu.cu" -o "$TMP/ref_tu.o"
 "$NVCC" -shared -Xcompiler -pthread "$TMP/ref_tu.o" "$TMP/tiny_obj_loader.o" -o "$OUT/libcupt_ref.so"
 echo "built $OUT/libcupt_ref.so"
+
+# ---- legacy GPU baseline: the original kernel.cu rebuilt for sm_100a (SURVEY.md §8d "Legacy GPU baseline") ----
+# Compile patches only: 1 (windows.h), 2 (triple.h), 3 (nvml.h, getGPUTemp/main cut), the ray counter hook (9) and
+# the image size (kernel.cu:28-29: 512 -> LEGACY_IMAGE_DIM, default 1024 = BASELINE config 2).  Device code is the
+# reference's: cuRAND XORWOW, NUM_BOUNCES 3, radianceAlongSingleStep, 512-thread blocks, default nvcc flags
+# (FMA contraction on, as compile.bat:4 had it).  Output: oracle/_ref/libcupt_legacy.so (runs only on a GPU box).
+chk kernel.cu 28 '#define IMAGE_WIDTH 512'
+chk kernel.cu 29 '#define IMAGE_HEIGHT 512'
+mkdir -p "$TMP/legacy"
+for h in vec3.h AABBvec3.h ivec3.h color.h camera.h BVH.h modelLoader.h SIUnits.h sphere.h tiny_obj_loader.h limits.h; do
+  cp "$REF/$h" "$TMP/legacy/$h"
+done
+sed -E \
+  -e '555,$d' \
+  -e '114s/$/ ORACLE_COUNT_RAY();/' \
+  -e '28s/512/LEGACY_IMAGE_DIM/' -e '29s/512/LEGACY_IMAGE_DIM/' \
+  -e '23d' -e '14d' -e '9d' \
+  "$REF/kernel.cu" > "$TMP/legacy/kernel_legacy.cu"
+cat > "$TMP/legacy/legacy_tu.cu" <<EOF2
+#include "$HERE/legacy_prelude.h"
+#include "kernel_legacy.cu"
+#include "$HERE/legacy_driver.inc"
+EOF2
+"$NVCC" -std=c++17 -w -gencode arch=compute_100a,code=sm_100a -DLEGACY_IMAGE_DIM=${LEGACY_IMAGE_DIM:-1024} -Xptxas -v \
+  -Xcompiler -fPIC -c "$TMP/legacy/legacy_tu.cu" -o "$TMP/legacy/legacy_tu.o" 2> "$OUT/legacy_ptxas.log" || { cat "$OUT/legacy_ptxas.log"; exit 1; }
+"$NVCC" -shared -gencode arch=compute_100a,code=sm_100a "$TMP/legacy/legacy_tu.o" "$TMP/tiny_obj_loader.o" -o "$OUT/libcupt_legacy.so"
+grep -A1 "drawPixel" "$OUT/legacy_ptxas.log" | grep -E "Used|stack" || true
+echo "built $OUT/libcupt_legacy.so"
