@@ -208,14 +208,15 @@ def main():
     ctx.set_options(max_depth=DEPTH, seed=SEED, traversal=api.TRAVERSAL_WIDE, time_stages=1, collect_stats=0)
     accum_t = torch.zeros(W * H * 3, dtype=torch.float32, device="cuda")
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
-    first = rank * SPP
+    from cudapathtracer_b200 import sharding
+    first, _ = sharding.weak_sample_range(rank, SPP)
 
     def step():
         ctx.reset_accum()
         ctx.render(first, SPP)
         if world > 1:
             ctx.copy_accum_device(accum_t.data_ptr())
-            dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+            sharding.reduce_accumulators(accum_t, dst=0)
 
     def barrier():
         if world > 1:
