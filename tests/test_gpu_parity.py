@@ -192,9 +192,10 @@ def test_full_size_properties(ctx, lib):
     tr = t[wi[ok]]
     dist = np.einsum("ij,ij->i", p - pos[tr["v0"]], tr["norm"].astype(np.float64))
     assert np.abs(dist).max() < 1e-3
-    # linearity of the accumulator: 2 x render(1 spp ranges) sums; normalised mean is bounded by the emission
+    # linearity of the accumulator: 2 x render(1 spp ranges) sums
     ctx.set_options(traversal=api.TRAVERSAL_WIDE)
     ctx.reset_accum(); ctx.render(0, 2); a = ctx.read_accum(False)
     ctx.reset_accum(); ctx.render(0, 1); ctx.render(1, 1); b2 = ctx.read_accum(False)
     assert np.allclose(a, b2, rtol=1e-6, atol=1e-6)
-    assert np.isfinite(a).all() and a.min() >= 0 and a.max() / 2 <= 6.0 * 1.0001
+    # (the estimator is unbounded above: kernel.cu:504-506 multiplies by G = cos*cos/d^2 times the total light area)
+    assert np.isfinite(a).all() and a.min() >= 0 and a.mean() > 0.1
