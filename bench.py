@@ -49,11 +49,17 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.t0, self.t1 = index, [], None, None, None
+
+    def mark_begin(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "25",
                                           "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
@@ -61,7 +67,8 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            if self.t0 is not None and self.t1 is None:   # keep only what was sampled inside the timed region
+                self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
         if self.proc:
@@ -229,19 +236,21 @@ def main():
     st = ctx.stats()
     rays_step, nodes_step, tris_step = st["rays"], st["nodes_visited"], st["tris_tested"]
     ctx.set_options(collect_stats=0)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()          # nvidia-smi takes a moment to come up: started before the warm-up, rows kept only inside the timed region
     for _ in range(args.warmup):
         step()
     barrier()
     ctx.reset_stats()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
+    sampler.mark_begin()
     for a, b in ev:
         flush_buf.fill_(1)          # L2 flush between timed iterations (outside the event pair)
         a.record(stream); step(); b.record(stream)
     barrier()
+    sampler.mark_end()
     clocks = sampler.stop() if rank == 0 else None
     ms = sum(a.elapsed_time(b) for a, b in ev)
     st = ctx.stats()
@@ -249,7 +258,11 @@ def main():
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     ms_total = float(tms.item())
-    rays_all = rays_step * world * args.steps       # every rank traces a different sample range of the same frame
+    # every rank traces a different sample range of the same frame: sum the rays each rank actually counted
+    trays = torch.tensor([float(st["rays"])], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(trays, op=dist.ReduceOp.SUM)
+    rays_all = float(trays.item())
     value = rays_all / (ms_total * 1e-3) / 1e6
 
     # e2e through the C-ABI with host buffers (scene + BVH H2D, render, image D2H), same step

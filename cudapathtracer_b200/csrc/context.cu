@@ -157,6 +157,7 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
 	ExtendTuning tune;
 	tune.fetch_thresh = c->opts.fetch_threshold > 0 ? std::min(c->opts.fetch_threshold, 31) : 24;
 	tune.tri_thresh = c->opts.postpone_threshold > 0 ? std::min(c->opts.postpone_threshold, 32) : 1;
+	tune.qbias_bits = CUPT_QBIAS_BITS;
 	void (*kern)(DevScene, PathBuffers, int, int, ExtendTuning) =
 		mode == 0 ? (stats ? k_extend<0, true> : k_extend<0, false>) : (stats ? k_extend<1, true> : k_extend<1, false>);
 	if (c->extend_blocks[mode] == 0 || mode == 0) {

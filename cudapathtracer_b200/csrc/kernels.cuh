@@ -133,6 +133,7 @@ __global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb)
 struct ExtendTuning {
 	int32_t fetch_thresh;   // refill idle lanes when active lanes <= this
 	int32_t tri_thresh;     // postpone primitive tests when lanes with primitives < this
+	uint32_t qbias_bits;    // CUPT_QBIAS_BITS, passed as a parameter on purpose (see u8f_biased)
 };
 #define CUPT_TRI_SLOTS 4      // stack entries reserved for postponed primitive groups
 #define CUPT_QUEUE_CHUNK 64u
@@ -190,7 +191,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 		if (active) {
 			if (group_has_node(ngroup)) {
 				uint2 rest;
-				wide_node_step(sc.nodes, r, ngroup, rest, tgroup);
+				wide_node_step(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits);
 				if (group_has_node(rest)) { stack[sp * stride] = rest; ++sp; }
 				if (STATS) ++n_nodes;
 			} else {

@@ -68,12 +68,17 @@ __device__ __forceinline__ float sphere_nearest(const f3 o, const f3 d, const fl
 // The constant 2^15 is folded into the per-node offset (o' = o - 2^15 s), which costs 2^-9 of a grid cell of
 // accuracy and is covered by the per-axis slack below.
 #define CUPT_QBIAS 32768.0f
-__device__ __forceinline__ float u8f_biased(uint32_t w, int j)
+// `bias_bits` must hold 0x47000000 (the bits of 2^15) but come from a kernel parameter, not a literal: with a literal
+// ptxas keeps the constant as PRMT's immediate and re-materialises the SELECTOR in a register before almost every
+// PRMT (60 extra IMAD/MOV per node step in profiles/r1d); with an opaque register the selector is the immediate.
+#define CUPT_QBIAS_BITS 0x47000000u
+__device__ __forceinline__ float u8f_biased(uint32_t w, int j, uint32_t bias_bits)
 {
 #ifdef CUPT_HOST_EMUL
+	(void)bias_bits;
 	return CUPT_QBIAS + (float)((w >> (8 * j)) & 0xffu);
 #else
-	return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7604u + ((uint32_t)j << 4)));
+	return __uint_as_float(__byte_perm(w, bias_bits, 0x7604u + ((uint32_t)j << 4)));
 #endif
 }
 
@@ -106,7 +111,8 @@ __device__ __forceinline__ bool group_has_node(const uint2 g) { return g.y > 0x0
 // Takes the nearest untested child out of `ngroup` (the caller pushes what is left), fetches its 80-byte node with
 // five 128-bit ld.global.nc and tests the eight quantised child boxes against [0, best]; returns the children hit
 // as a new node group and a primitive group.
-__device__ __forceinline__ void wide_node_step(const uint4* __restrict__ nodes, const WideRay& r, uint2& ngroup, uint2& rest, uint2& tgroup)
+__device__ __forceinline__ void wide_node_step(const uint4* __restrict__ nodes, const WideRay& r, uint2& ngroup, uint2& rest, uint2& tgroup,
+                                               const uint32_t bias_bits = CUPT_QBIAS_BITS)
 {
 	const uint32_t hits = ngroup.y;
 	const uint32_t bit = 31u - __clz(hits);
@@ -149,8 +155,8 @@ __device__ __forceinline__ void wide_node_step(const uint4* __restrict__ nodes, 
 		const uint32_t nz = negz ? qhz : qlz, fz = negz ? qlz : qhz;
 #pragma unroll
 		for (int j = 0; j < 4; ++j) {
-			const float tnx = fmaf(u8f_biased(nx, j), sx, onx), tny = fmaf(u8f_biased(ny, j), sy, ony), tnz = fmaf(u8f_biased(nz, j), sz, onz);
-			const float tfx = fmaf(u8f_biased(fx, j), sx, ofx), tfy = fmaf(u8f_biased(fy, j), sy, ofy), tfz = fmaf(u8f_biased(fz, j), sz, ofz);
+			const float tnx = fmaf(u8f_biased(nx, j, bias_bits), sx, onx), tny = fmaf(u8f_biased(ny, j, bias_bits), sy, ony), tnz = fmaf(u8f_biased(nz, j, bias_bits), sz, onz);
+			const float tfx = fmaf(u8f_biased(fx, j, bias_bits), sx, ofx), tfy = fmaf(u8f_biased(fy, j, bias_bits), sy, ofy), tfz = fmaf(u8f_biased(fz, j, bias_bits), sz, ofz);
 			const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
 			const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, r.best));
 			if (tmin <= tmax) {
