@@ -346,7 +346,7 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 	const DevScene sc = make_scene(c);
 	PassParams probe = make_pass(c, 0, 1, 0);
 	int S = c->opts.samples_per_pass;
-	if (S <= 0) S = (int)std::max<int64_t>(1, (int64_t)(4 << 20) / probe.p_pad);
+	if (S <= 0) S = (int)std::max<int64_t>(1, (int64_t)(64 << 20) / probe.p_pad);   // 64 Mi paths x 72 B = 4.8 GB of path state: long passes amortise the tail of every extend launch
 	S = std::min(S, std::max(1, num_samples));
 	if ((int64_t)probe.p_pad * S > 0x7fffffff) S = (int)(0x7fffffff / probe.p_pad);
 	if ((rc = ensure_paths(c, (size_t)probe.p_pad * S))) return rc;

@@ -41,21 +41,24 @@ __device__ __forceinline__ float tri_refexact(const f3 o, const f3 d, const floa
 	return rdot(e2, r);
 }
 
-// analytic ray-sphere (no reference code exists, sphere.h:7-13 is a POD only: parity unpinned)
+// analytic ray-sphere, nearest root with 0 < t (no reference code exists, sphere.h:7-13 is a POD only: PARITY
+// UNPINNED; oracle/oracle.c restates exactly this arithmetic).  Every operation is individually rounded.
+//   c = centre - o, dd = d.d, b = c.d, p = c - (b/dd) d (closest approach), disc = r^2 - p.p,
+//   q = b + sign(b) sqrt(disc dd), roots (c.c - r^2)/q and q/dd
 __device__ __forceinline__ float sphere_nearest(const f3 o, const f3 d, const float4 r0, const float4 r1)
 {
-	const float cx = r0.x - o.x, cy = r0.y - o.y, cz = r0.z - o.z, rad = r0.w;
-	const float dd = d.x * d.x + d.y * d.y + d.z * d.z;
-	const float b = cx * d.x + cy * d.y + cz * d.z;
-	// numerically robust discriminant (distance from the centre to the ray, squared)
-	const float px = cx - (b / dd) * d.x, py = cy - (b / dd) * d.y, pz = cz - (b / dd) * d.z;
-	const float disc = rad * rad - (px * px + py * py + pz * pz);
+	const f3 c = rsub3(mk3(r0.x, r0.y, r0.z), o);
+	const float rad = r0.w;
+	const float dd = rdot(d, d), b = rdot(c, d);
+	const float k = rdiv(b, dd);
+	const f3 p = rsub3(c, rmul3(d, k));
+	const float disc = rsub(rmul(rad, rad), rdot(p, p));
 	if (!(disc >= 0.0f))
 		return CUPT_MAX_FLOAT;
-	const float root = sqrtf(disc * dd);
-	const float qv = b + copysignf(root, b);
-	const float cc = cx * cx + cy * cy + cz * cz - rad * rad;
-	float t0 = cc / qv, t1 = qv / dd;
+	const float root = __fsqrt_rn(rmul(disc, dd));
+	const float qv = radd(b, copysignf(root, b));
+	const float cc = rsub(rdot(c, c), rmul(rad, rad));
+	float t0 = rdiv(cc, qv), t1 = rdiv(qv, dd);
 	if (t0 > t1) { const float tt = t0; t0 = t1; t1 = tt; }
 	(void)r1;
 	if (t0 > 0.0f) return t0;
