@@ -102,6 +102,17 @@ def make_camera(width: int, height: int, pos=(0.0, 1.0, 3.0), distFromFilm=1.0, 
     return cam
 
 
+def spheres_array(spheres) -> np.ndarray:
+    """[(centre, radius, diffuse, emm)] -> SPHERE records; colours pass through float like MTL values do"""
+    out = np.zeros(len(spheres), dtype=SPHERE)
+    for i, (c, r, kd, ke) in enumerate(spheres):
+        out["pos"][i] = c
+        out["rad"][i] = r
+        out["diffuse"][i] = np.asarray(kd, dtype=np.float32)
+        out["emm"][i] = np.asarray(ke, dtype=np.float32)
+    return out
+
+
 class SceneHandle:
     """cupt_scene: the reference's globals verts/tris/mats/lights/totalLightArea (modelLoader.h:43-47)."""
 
@@ -150,6 +161,8 @@ class SceneHandle:
         first = self.add_materials(mats, duplicate_table)
         for sh in scene.shapes:
             self.add_shape(sh.positions, sh.indices, sh.material + first, origin, scale, flip)
+        if getattr(scene, "spheres", None):
+            self.add_spheres(spheres_array(scene.spheres))
 
     def add_spheres(self, spheres: np.ndarray):
         spheres = np.ascontiguousarray(spheres, dtype=SPHERE)

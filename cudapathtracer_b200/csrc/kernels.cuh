@@ -26,6 +26,7 @@ struct DevScene {
 	const float4* trishade;        // TriShade
 	const float4* mats;            // MatF x2 float4
 	const float4* lights;          // LightTri x3 float4, numLights + 1 entries (last = triangle 0 fallback)
+	const float4* spheres;         // SphereShade x3 float4: {centre, radius}, {diffuse, emissive flag}, {emission, 0}
 	int32_t numLights;
 	float totalLightArea;
 	int32_t stack_cap;             // shared-memory stack entries per thread
@@ -372,11 +373,23 @@ __global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathB
 			float closestT = (float)((double)rb.z - 0.001);                        // kernel.cu:431
 			if ((double)closestT < 0.001) { wr = wg = wb = 0.f; }                   // kernel.cu:432-435
 			if (closestT > CUPT_MAX_FLOAT - 1) { wr = wg = wb = 0.f; id = 0; closestT = 0.f; }  // kernel.cu:436-441
-			const float4 tsh = sc.trishade[id];
-			const f3 normal = mk3(tsh.x, tsh.y, tsh.z);
-			const int mat = __float_as_int(tsh.w);
-			const float4 m0 = sc.mats[2 * mat], m1 = sc.mats[2 * mat + 1];
 			const f3 pos = radd3(o, rmul3(d, closestT));                            // kernel.cu:449
+			f3 normal;
+			float4 m0, m1;
+			if (id >= 0) {
+				const float4 tsh = sc.trishade[id];
+				normal = mk3(tsh.x, tsh.y, tsh.z);
+				const int mat = __float_as_int(tsh.w);
+				m0 = sc.mats[2 * mat]; m1 = sc.mats[2 * mat + 1];
+			} else {
+				// sphere (sphere.h:7-13 is a POD without an intersector or shading code: parity unpinned).  Normal =
+				// (hit point - centre) / radius at the UNSHORTENED hit distance; diffuse / emm play albedo / emission.
+				const uint32_t si = (uint32_t)id & 0x7fffffffu;
+				const float4 sp0 = sc.spheres[3 * si];
+				const f3 hp = radd3(o, rmul3(d, rb.z));
+				normal = rdiv3(rsub3(hp, mk3(sp0.x, sp0.y, sp0.z)), sp0.w);
+				m0 = sc.spheres[3 * si + 1]; m1 = sc.spheres[3 * si + 2];
+			}
 			if (m0.w != 0.f) {                                                      // kernel.cu:453-457
 				s1.x += wr * m1.x; s1.y += wg * m1.y; s1.z += wb * m1.z;
 				wr = wg = wb = 0.f;

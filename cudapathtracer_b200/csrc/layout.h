@@ -71,6 +71,15 @@ struct alignas(16) LightTri {   // per light triangle (+ one fallback entry for 
 	float pad1;
 };
 
+struct alignas(16) SphereShade {   // per sphere (sphere.h:7-13), f32
+	float centre[3];
+	float radius;
+	float diffuse[3];
+	float emissive_flag;          // 1 when emm.r != 0 in f64 (same rule as materials, kernel.cu:453)
+	float emm[3];
+	float pad;
+};
+
 }  // namespace cupt
 
 // host image of the wide BVH

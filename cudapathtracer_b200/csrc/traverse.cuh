@@ -42,7 +42,7 @@ __device__ __forceinline__ float tri_refexact(const f3 o, const f3 d, const floa
 }
 
 // analytic ray-sphere, nearest root with 0 < t (no reference code exists, sphere.h:7-13 is a POD only: PARITY
-// UNPINNED; oracle/oracle.c restates exactly this arithmetic).  Every operation is individually rounded.
+// UNPINNED; the test-side CPU restatement repeats exactly this arithmetic).  Every operation is individually rounded.
 //   c = centre - o, dd = d.d, b = c.d, p = c - (b/dd) d (closest approach), disc = r^2 - p.p,
 //   q = b + sign(b) sqrt(disc dd), roots (c.c - r^2)/q and q/dd
 __device__ __forceinline__ float sphere_nearest(const f3 o, const f3 d, const float4 r0, const float4 r1)

@@ -7,7 +7,7 @@ import os
 
 import numpy as np
 
-from cudapathtracer_b200.api import BVH2_NODE, CAMERA, MATERIAL, TRIANGLE, VEC3
+from cudapathtracer_b200.api import BVH2_NODE, CAMERA, MATERIAL, SPHERE, TRIANGLE, VEC3
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
@@ -16,7 +16,8 @@ ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
 class _Scene(C.Structure):
     _fields_ = [("verts", C.c_void_p), ("tris", C.c_void_p), ("mats", C.c_void_p), ("lights", C.c_void_p),
                 ("numVerts", C.c_int32), ("numTris", C.c_int32), ("numMats", C.c_int32), ("numLights", C.c_int32),
-                ("totalLightArea", C.c_float), ("nodes", C.c_void_p), ("numNodes", C.c_int32)]
+                ("totalLightArea", C.c_float), ("nodes", C.c_void_p), ("numNodes", C.c_int32),
+                ("spheres", C.c_void_p), ("numSpheres", C.c_int32)]
 
 
 _lib = None
@@ -42,7 +43,7 @@ def _p(a):
 class OracleScene:
     """scene arrays in reference layout + a reference-layout BVH2 node array"""
 
-    def __init__(self, verts, tris, mats, lights, total_light_area, nodes):
+    def __init__(self, verts, tris, mats, lights, total_light_area, nodes, spheres=None):
         self.verts = np.ascontiguousarray(verts, dtype=VEC3)
         self.tris = np.ascontiguousarray(tris, dtype=TRIANGLE)
         self.mats = np.ascontiguousarray(mats, dtype=MATERIAL)
@@ -50,7 +51,10 @@ class OracleScene:
         self.nodes = np.ascontiguousarray(nodes, dtype=BVH2_NODE)
         self.c = _Scene(self.verts.ctypes.data, self.tris.ctypes.data, self.mats.ctypes.data, self.lights.ctypes.data,
                         len(self.verts), len(self.tris), len(self.mats), len(self.lights),
-                        float(total_light_area), self.nodes.ctypes.data, len(self.nodes))
+                        float(total_light_area), self.nodes.ctypes.data, len(self.nodes), None, 0)
+        if spheres is not None and len(spheres):
+            self.spheres = np.ascontiguousarray(spheres, dtype=SPHERE)
+            self.c.spheres, self.c.numSpheres = self.spheres.ctypes.data, len(self.spheres)
 
     def camera_rays(self, cam, u1=0.5, u2=0.5):
         cam = np.ascontiguousarray(cam, dtype=CAMERA)
