@@ -28,7 +28,7 @@ struct cupt_context {
 	bool own_stream = false;
 	// scene
 	float* d_verts = nullptr; cupt_triangle* d_tris = nullptr; float4* d_trishade = nullptr; float4* d_mats = nullptr;
-	float4* d_lights = nullptr; float4* d_spheres = nullptr; int num_spheres = 0;
+	float4* d_lights = nullptr; float* d_light_cdf = nullptr; float4* d_spheres = nullptr; int num_spheres = 0;
 	int64_t num_tris = 0; int num_lights = 0; float total_light_area = 0.f;
 	// acceleration structures
 	uint4* d_nodes = nullptr; float4* d_prims = nullptr; int bvh_depth = 0; int64_t num_nodes = 0, num_prims = 0;
@@ -132,7 +132,7 @@ DevScene make_scene(const cupt_context* c)
 {
 	DevScene sc;
 	sc.nodes = c->d_nodes; sc.prims = c->d_prims; sc.bvh2 = c->d_bvh2; sc.verts = c->d_verts; sc.tris = c->d_tris;
-	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.lights = c->d_lights; sc.spheres = c->d_spheres;
+	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.lights = c->d_lights; sc.light_cdf = c->d_light_cdf; sc.spheres = c->d_spheres;
 	sc.numLights = c->num_lights; sc.totalLightArea = c->total_light_area;
 	sc.stack_cap = std::max(c->bvh_depth, 1) + CUPT_TRI_SLOTS;
 	return sc;
@@ -218,7 +218,7 @@ void cupt_destroy(cupt_context* c)
 	cudaStreamSynchronize(c->stream);
 	drain_events(c);
 	for (StageEvent& ev : c->pool) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
-	cudaFree(c->d_verts); cudaFree(c->d_tris); cudaFree(c->d_trishade); cudaFree(c->d_mats); cudaFree(c->d_lights); cudaFree(c->d_spheres);
+	cudaFree(c->d_verts); cudaFree(c->d_tris); cudaFree(c->d_trishade); cudaFree(c->d_mats); cudaFree(c->d_lights); cudaFree(c->d_light_cdf); cudaFree(c->d_spheres);
 	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2);
 	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
 	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats);
@@ -305,6 +305,10 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 		lt[j].area = length3(cross3(a1, a2)) / 2;
 	}
 	if ((rc = upload(&c->d_lights, lt.data(), lt.size() * sizeof(LightTri), c->stream))) return rc;
+	std::vector<float> cdf(nl);
+	double run = 0;
+	for (size_t j = 0; j < nl; ++j) { run += (double)lt[j].area; cdf[j] = (float)run; }
+	if ((rc = upload(&c->d_light_cdf, cdf.data(), nl * sizeof(float), c->stream))) return rc;
 	std::vector<SphereShade> ss(s->spheres.size());
 	for (size_t i = 0; i < ss.size(); ++i) {
 		const cupt_sphere& sp = s->spheres[i];

@@ -26,6 +26,7 @@ struct DevScene {
 	const float4* trishade;        // TriShade
 	const float4* mats;            // MatF x2 float4
 	const float4* lights;          // LightTri x3 float4, numLights + 1 entries (last = triangle 0 fallback)
+	const float* light_cdf;        // inclusive prefix sums of the light areas (only used above CUPT_LIGHT_SCAN_MAX lights)
 	const float4* spheres;         // SphereShade x3 float4: {centre, radius}, {diffuse, emissive flag}, {emission, 0}
 	int32_t numLights;
 	float totalLightArea;
@@ -136,6 +137,7 @@ struct ExtendTuning {
 	int32_t tri_thresh;     // postpone primitive tests when lanes with primitives < this
 	uint32_t qbias_bits;    // CUPT_QBIAS_BITS, passed as a parameter on purpose (see u8f_biased)
 };
+#define CUPT_LIGHT_SCAN_MAX 64   // up to this many lights k_shade repeats the reference's linear scan exactly
 #define CUPT_TRI_SLOTS 4      // stack entries reserved for postponed primitive groups
 #define CUPT_QUEUE_CHUNK 64u
 #ifndef CUPT_EXTEND_MIN_BLOCKS
@@ -419,10 +421,23 @@ __global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathB
 					// light-point sample, kernel.cu:468-507
 					float randArea = rmul(sc.totalLightArea, rng.draw(draw++));
 					int sel = sc.numLights;   // fallback entry = triangle 0 (`selectedTri = 0`, kernel.cu:469)
-					for (int j = 0; j < sc.numLights; ++j) {
-						const float area = sc.lights[3 * j].w;
-						if (randArea < area && randArea > 0.f) sel = j;
-						randArea = rsub(randArea, area);
+					if (sc.numLights <= CUPT_LIGHT_SCAN_MAX) {
+						for (int j = 0; j < sc.numLights; ++j) {   // the reference's linear scan, kernel.cu:470-481, op for op
+							const float area = sc.lights[3 * j].w;
+							if (randArea < area && randArea > 0.f) sel = j;
+							randArea = rsub(randArea, area);
+						}
+					} else {
+						// The scan is O(numLights) per sample (58 k lights on the 30 M-triangle soup: 95 % of the frame time).
+						// Above CUPT_LIGHT_SCAN_MAX lights the same selection is made by binary search in the prefix sums:
+						// first j with randArea < cdf[j].  It differs from the sequential f32 subtraction only when randArea
+						// lies within rounding of a light boundary (probability ~ numLights * 1e-7 per draw).
+						int lo = 0, hi = sc.numLights;
+						while (lo < hi) {
+							const int mid = (lo + hi) >> 1;
+							if (randArea < sc.light_cdf[mid]) hi = mid; else lo = mid + 1;
+						}
+						sel = lo;   // == numLights (fallback) when randArea >= cdf[last]
 					}
 					float u = rng.draw(draw++), v = rng.draw(draw++);
 					const float4 l0 = sc.lights[3 * sel], l1 = sc.lights[3 * sel + 1], l2 = sc.lights[3 * sel + 2];
