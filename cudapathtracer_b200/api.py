@@ -49,7 +49,7 @@ class BvhInfo(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("max_depth", C.c_int32), ("integrator", C.c_int32), ("traversal", C.c_int32), ("tri_test", C.c_int32),
                 ("seed", C.c_uint64), ("samples_per_pass", C.c_int32), ("collect_stats", C.c_int32),
-                ("time_stages", C.c_int32), ("fetch_threshold", C.c_int32), ("postpone_threshold", C.c_int32),
+                ("time_stages", C.c_int32), ("fetch_threshold", C.c_int32), ("defer_pairs", C.c_int32),
                 ("reserved", C.c_int32)]
 
 

@@ -134,7 +134,7 @@ DevScene make_scene(const cupt_context* c)
 	sc.nodes = c->d_nodes; sc.prims = c->d_prims; sc.bvh2 = c->d_bvh2; sc.verts = c->d_verts; sc.tris = c->d_tris;
 	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.lights = c->d_lights; sc.light_cdf = c->d_light_cdf; sc.spheres = c->d_spheres;
 	sc.numLights = c->num_lights; sc.totalLightArea = c->total_light_area;
-	sc.stack_cap = std::max(c->bvh_depth, 1) + CUPT_TRI_SLOTS;
+	sc.stack_cap = std::max(c->bvh_depth, 1);
 	return sc;
 }
 
@@ -156,7 +156,7 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
 	const size_t smem = mode == 0 ? (size_t)sc.stack_cap * 128 * sizeof(uint2) + 128 * 16 : 0;   // stacks + per-warp keys/list/ids
 	ExtendTuning tune;
 	tune.fetch_thresh = c->opts.fetch_threshold > 0 ? std::min(c->opts.fetch_threshold, 31) : 24;
-	tune.tri_thresh = c->opts.postpone_threshold > 0 ? std::min(c->opts.postpone_threshold, 32) : 1;
+	tune.defer_pairs = c->opts.defer_pairs > 0 ? std::min(c->opts.defer_pairs, 64) : 16;
 	tune.qbias_bits = CUPT_QBIAS_BITS;
 	void (*kern)(DevScene, PathBuffers, int, int, ExtendTuning) =
 		mode == 0 ? (stats ? k_extend<0, true> : k_extend<0, false>) : (stats ? k_extend<1, true> : k_extend<1, false>);

@@ -126,19 +126,15 @@ __global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb)
 //   * a lane whose ray has ended is refilled from the queue as soon as fewer than `fetch_thresh` lanes are busy
 //     (the first version traced 32 rays to the end per fetch and ran at 7 of 32 threads per instruction on
 //     diffuse bounces, profiles/r1a_extend_metrics.md),
-//   * when fewer than `tri_thresh` lanes have primitives to test, lanes that can go on with node work put their
-//     primitive group on the stack and come back to it later, so that primitive tests run with fuller warps
-//     (postponing after Ylitie, Karras, Laine, HPG 2017; the bookkeeping below is ours and bounds the stack:
-//     at most TRI_SLOTS postponed groups per ray, and a lane only postpones when it does a node step next, which
-//     guarantees progress).
+//   * primitive tests are shared: the (ray, primitive) pairs of the whole warp are listed in shared memory and
+//     every lane tests one pair, whoever owns the ray (see the primitive phase below).
 // Queue entries are handed out from warp-private chunks of CHUNK entries (one atomic per chunk).
 struct ExtendTuning {
 	int32_t fetch_thresh;   // refill idle lanes when active lanes <= this
-	int32_t tri_thresh;     // postpone primitive tests when lanes with primitives < this
+	int32_t defer_pairs;    // hold primitive tests one iteration while the warp has fewer (ray, primitive) pairs than this
 	uint32_t qbias_bits;    // CUPT_QBIAS_BITS, passed as a parameter on purpose (see u8f_biased)
 };
 #define CUPT_LIGHT_SCAN_MAX 64   // up to this many lights k_shade repeats the reference's linear scan exactly
-#define CUPT_TRI_SLOTS 4      // stack entries reserved for postponed primitive groups
 #define CUPT_QUEUE_CHUNK 64u
 #ifndef CUPT_EXTEND_MIN_BLOCKS
 #define CUPT_EXTEND_MIN_BLOCKS 7
@@ -152,12 +148,11 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 	const uint32_t FULL = 0xffffffffu;
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t lt_mask = (1u << lane) - 1u;
-	const int node_cap = sc.stack_cap - CUPT_TRI_SLOTS;
 	bool active = false, exhausted = false;
 	uint32_t chunk_next = 0u, chunk_end = 0u;
 	WideRay r;
-	uint2 ngroup = make_uint2(0u, 0u), tgroup = make_uint2(0u, 0u);
-	int sp = 0, tpushed = 0;
+	uint2 ngroup = make_uint2(0u, 0u), tgroup = make_uint2(0u, 0u), pgroup = make_uint2(0u, 0u);
+	int sp = 0;
 	uint32_t slot = 0u;
 	for (;;) {
 		uint32_t act = __ballot_sync(FULL, active);
@@ -179,7 +174,8 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 					const float4 b = pb.rayB[slot];
 					wide_ray_init(r, mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y));
 					ngroup = make_uint2(0u, 0x80000000u); tgroup = make_uint2(0u, 0u);
-					sp = 0; tpushed = 0;
+					pgroup = make_uint2(0u, 0u);
+					sp = 0;
 					active = true;
 					++n_rays;
 				}
@@ -191,16 +187,11 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 		if (act == 0u) break;
 
 		// ---- node step ------------------------------------------------------------------------------------------
-		if (active) {
-			if (group_has_node(ngroup)) {
-				uint2 rest;
-				wide_node_step(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits);
-				if (group_has_node(rest)) { stack[sp * stride] = rest; ++sp; }
-				if (STATS) ++n_nodes;
-			} else {
-				tgroup = ngroup;
-				ngroup = make_uint2(0u, 0u);
-			}
+		if (active && group_has_node(ngroup)) {   // (only node groups are ever pushed, so a popped group always has one)
+			uint2 rest;
+			wide_node_step(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits);
+			if (group_has_node(rest)) { stack[sp * stride] = rest; ++sp; }
+			if (STATS) ++n_nodes;
 		}
 		// ---- primitive tests, shared across the warp ----------------------------------------------------------------
 		// Lanes with pending primitives are few (3.2 of 32 in profiles/r1c, where this phase took 40 % of the issue
@@ -208,87 +199,89 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 		// one pair: lane i fetches the owner's ray by shuffle, runs the exact test and merges its hit into the
 		// owner's 64-bit key (t bits << 32 | rank) with a shared-memory atomicMin, which is the acceptance rule
 		// `t < best || (t == best && rank < best_rank)` because positive floats order like their bit patterns.
-		if (tune.tri_thresh > 1) {
-			// (optional) postponing while few lanes have primitives; see the header comment
-			const bool has = active && tgroup.y != 0u;
-			const uint32_t m = __ballot_sync(FULL, has);
-			if (m != 0u && __popc(m) < tune.tri_thresh && has && tpushed < CUPT_TRI_SLOTS) {
-				if (group_has_node(ngroup)) {                       // node work in hand: primitives go to the stack
-					stack[sp * stride] = tgroup; ++sp; ++tpushed;
-					tgroup.y = 0u;
-				} else if (sp > 0) {
-					const uint2 top = stack[(sp - 1) * stride];
-					if (group_has_node(top)) {                       // swap with the node group on top of the stack
-						stack[(sp - 1) * stride] = tgroup; ++tpushed;
-						ngroup = top; tgroup.y = 0u;
+		// A warp that holds fewer than `defer_pairs` pairs keeps them one iteration (tgroup -> pgroup) unless a ray
+		// would end or a lane would need a third group, so that a round runs with more lanes (10.7 in profiles/r1e).
+		{
+			const uint32_t cnt0 = active ? (uint32_t)(__popc(tgroup.y) + __popc(pgroup.y)) : 0u;
+			const uint32_t total0 = __reduce_add_sync(FULL, cnt0);
+			if (total0 != 0u) {
+				const bool last = !group_has_node(ngroup) && sp == 0;        // this ray ends after the iteration
+				const bool clash = tgroup.y != 0u && pgroup.y != 0u;         // both slots taken
+				const bool flush = total0 >= (uint32_t)tune.defer_pairs || __any_sync(FULL, cnt0 != 0u && (last || clash));
+				if (!flush) {
+					if (active && tgroup.y != 0u) { pgroup = tgroup; tgroup.y = 0u; }
+				} else {
+					for (;;) {
+						const uint32_t cnt = active ? (uint32_t)(__popc(tgroup.y) + __popc(pgroup.y)) : 0u;
+						uint32_t incl = cnt;
+#pragma unroll
+						for (int ofs = 1; ofs < 32; ofs <<= 1) {
+							const uint32_t v = __shfl_up_sync(FULL, incl, ofs);
+							if (lane >= (uint32_t)ofs) incl += v;
+						}
+						const uint32_t total = __shfl_sync(FULL, incl, 31);
+						uint32_t pos = incl - cnt;
+						if (cnt != 0u) {
+							while (pgroup.y != 0u && pos < 32u) {
+								const uint32_t k = __ffs(pgroup.y) - 1u;
+								pgroup.y &= pgroup.y - 1u;
+								wlist[pos++] = ((pgroup.x + k) << 5) | lane;
+							}
+							while (tgroup.y != 0u && pos < 32u) {
+								const uint32_t k = __ffs(tgroup.y) - 1u;
+								tgroup.y &= tgroup.y - 1u;
+								wlist[pos++] = ((tgroup.x + k) << 5) | lane;
+							}
+						}
+						const unsigned long long mykey = ((unsigned long long)__float_as_uint(r.best) << 32) | r.best_rank;
+						wkeys[lane] = mykey;
+						__syncwarp();
+						const bool work = lane < total;
+						const uint32_t e = work ? wlist[lane] : 0u;
+						const uint32_t owner = e & 31u;
+						f3 po, pd;
+						po.x = __shfl_sync(FULL, r.o.x, owner); po.y = __shfl_sync(FULL, r.o.y, owner); po.z = __shfl_sync(FULL, r.o.z, owner);
+						pd.x = __shfl_sync(FULL, r.d.x, owner); pd.y = __shfl_sync(FULL, r.d.y, owner); pd.z = __shfl_sync(FULL, r.d.z, owner);
+						unsigned long long hkey = ~0ull;
+						uint32_t hid = 0u;
+						if (work) {
+							const float4* pp = sc.prims + (size_t)(e >> 5) * 3u;
+							const float4 r0 = ldg_nc_f4(pp + 0), r1 = ldg_nc_f4(pp + 1), r2 = ldg_nc_f4(pp + 2);
+							const uint32_t kind = __float_as_uint(r2.w);
+							float t;
+							if (kind == 0u) t = tri_refexact(po, pd, r0, r1, r2);
+							else t = sphere_nearest(po, pd, r0, r1);
+							if (0.0f < t) {
+								hkey = ((unsigned long long)__float_as_uint(t) << 32) | __float_as_uint(r2.z);
+								hid = __float_as_uint(r2.y) | (kind << 31);
+								atomicMin(&wkeys[owner], hkey);
+							}
+							if (STATS) ++n_tris;
+						}
+						__syncwarp();
+						if (hkey != ~0ull && wkeys[owner] == hkey) wids[owner] = hid;
+						__syncwarp();
+						const unsigned long long nk = wkeys[lane];
+						if (nk != mykey) {
+							r.best = __uint_as_float((uint32_t)(nk >> 32)); r.best_rank = (uint32_t)nk; r.best_id = (int32_t)wids[lane];
+						}
+						if (total <= 32u) break;   // everything was listed in this round
+						__syncwarp();
 					}
 				}
 			}
 		}
-		for (;;) {
-			const uint32_t cnt = active ? (uint32_t)__popc(tgroup.y) : 0u;
-			uint32_t incl = cnt;
-#pragma unroll
-			for (int ofs = 1; ofs < 32; ofs <<= 1) {
-				const uint32_t v = __shfl_up_sync(FULL, incl, ofs);
-				if (lane >= (uint32_t)ofs) incl += v;
-			}
-			const uint32_t total = __shfl_sync(FULL, incl, 31);
-			if (total == 0u) break;
-			uint32_t pos = incl - cnt;
-			while (tgroup.y != 0u && pos < 32u) {
-				const uint32_t k = __ffs(tgroup.y) - 1u;
-				tgroup.y &= tgroup.y - 1u;
-				wlist[pos++] = ((tgroup.x + k) << 5) | lane;
-			}
-			const unsigned long long mykey = ((unsigned long long)__float_as_uint(r.best) << 32) | r.best_rank;
-			wkeys[lane] = mykey;
-			__syncwarp();
-			const bool work = lane < total;
-			const uint32_t e = work ? wlist[lane] : 0u;
-			const uint32_t owner = e & 31u;
-			f3 po, pd;
-			po.x = __shfl_sync(FULL, r.o.x, owner); po.y = __shfl_sync(FULL, r.o.y, owner); po.z = __shfl_sync(FULL, r.o.z, owner);
-			pd.x = __shfl_sync(FULL, r.d.x, owner); pd.y = __shfl_sync(FULL, r.d.y, owner); pd.z = __shfl_sync(FULL, r.d.z, owner);
-			unsigned long long hkey = ~0ull;
-			uint32_t hid = 0u;
-			if (work) {
-				const float4* pp = sc.prims + (size_t)(e >> 5) * 3u;
-				const float4 r0 = ldg_nc_f4(pp + 0), r1 = ldg_nc_f4(pp + 1), r2 = ldg_nc_f4(pp + 2);
-				const uint32_t kind = __float_as_uint(r2.w);
-				float t;
-				if (kind == 0u) t = tri_refexact(po, pd, r0, r1, r2);
-				else t = sphere_nearest(po, pd, r0, r1);
-				if (0.0f < t) {
-					hkey = ((unsigned long long)__float_as_uint(t) << 32) | __float_as_uint(r2.z);
-					hid = __float_as_uint(r2.y) | (kind << 31);
-					atomicMin(&wkeys[owner], hkey);
-				}
-				if (STATS) ++n_tris;
-			}
-			__syncwarp();
-			if (hkey != ~0ull && wkeys[owner] == hkey) wids[owner] = hid;
-			__syncwarp();
-			const unsigned long long nk = wkeys[lane];
-			if (nk != mykey) {
-				r.best = __uint_as_float((uint32_t)(nk >> 32)); r.best_rank = (uint32_t)nk; r.best_id = (int32_t)wids[lane];
-			}
-			if (total <= 32u) break;   // everything listed in this round
-			__syncwarp();
-		}
 		// ---- pop / finish -------------------------------------------------------------------------------------------
-		if (active && !group_has_node(ngroup) && tgroup.y == 0u) {
-			if (sp == 0) {
+		if (active && !group_has_node(ngroup)) {
+			if (sp == 0) {     // (a ray that ends has had its pending primitives flushed above)
 				reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(r.best, __int_as_float(r.best_id));
 				active = false;
 			} else {
 				--sp;
 				ngroup = stack[sp * stride];
-				if (!group_has_node(ngroup)) --tpushed;
 			}
 		}
 	}
-	(void)node_cap;
 }
 
 template <int MODE, bool STATS>
@@ -365,7 +358,6 @@ __global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathB
 		if (qi < count) {
 			slot = qin[qi];
 			const float4 ra = pb.rayA[slot], rb = pb.rayB[slot], s0 = pb.st0[slot];
-			float4 s1 = pb.st1[slot];
 			const f3 o = mk3(ra.x, ra.y, ra.z), d = mk3(ra.w, rb.x, rb.y);
 			float wr = s0.x, wg = s0.y, wb = s0.z;
 			const uint32_t packed = __float_as_uint(s0.w);
@@ -393,13 +385,14 @@ __global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathB
 				m0 = sc.spheres[3 * si + 1]; m1 = sc.spheres[3 * si + 2];
 			}
 			if (m0.w != 0.f) {                                                      // kernel.cu:453-457
+				// the radiance record is touched only here: a path meets an emitter at most once (its weight is zero after)
+				float4 s1 = pb.st1[slot];
 				s1.x += wr * m1.x; s1.y += wg * m1.y; s1.z += wb * m1.z;
+				pb.st1[slot] = s1;
 				wr = wg = wb = 0.f;
 			}
 			const bool dead = !(wr != 0.f || wg != 0.f || wb != 0.f);
-			if (dead || iter >= pp.max_depth - 1) {
-				pb.st1[slot] = s1;
-			} else {
+			if (!(dead || iter >= pp.max_depth - 1)) {
 				int x, y, sl;
 				slot_to_pixel(pp, slot, x, y, sl);
 				PhiloxStream rng;
@@ -457,7 +450,6 @@ __global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathB
 				}
 				++iter;
 				push = (wr != 0.f || wg != 0.f || wb != 0.f);
-				pb.st1[slot] = s1;
 				if (push) {
 					pb.rayA[slot] = make_float4(pos.x, pos.y, pos.z, lDir.x);
 					pb.rayB[slot] = make_float4(lDir.y, lDir.z, CUPT_MAX_FLOAT, __int_as_float(-1));

@@ -156,7 +156,7 @@ typedef struct cupt_render_opts {
 	int32_t collect_stats;    /* 1: count node visits / triangle tests (slower; for the roofline's bytes/ray) */
 	int32_t time_stages;      /* 1: CUDA events around every stage launch */
 	int32_t fetch_threshold;  /* extend: refill idle lanes of a warp from the ray queue when <= this many are busy (0 = default 24) */
-	int32_t postpone_threshold; /* extend: postpone primitive tests while fewer lanes than this have any (0 = default 1 = never) */
+	int32_t defer_pairs;      /* extend: hold primitive tests one traversal step while a warp has fewer (ray, primitive) pairs than this (0 = default 16, 1 = never) */
 	int32_t reserved;
 } cupt_render_opts;
 int cupt_default_render_opts(cupt_render_opts* o);

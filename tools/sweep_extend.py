@@ -17,7 +17,7 @@ def main():
     combos = [tuple(int(x) for x in c.split(":")) for c in os.environ.get("COMBOS", "24:8,24:1,16:8,28:8,24:4,24:12,24:16,20:6,31:8,12:1").split(",")]
     ref_img = None
     for ft, tt in combos:
-        ctx.set_options(max_depth=5, seed=1234, traversal=api.TRAVERSAL_WIDE, time_stages=1, collect_stats=0, fetch_threshold=ft, postpone_threshold=tt, samples_per_pass=int(os.environ.get("SPASS", "0")))
+        ctx.set_options(max_depth=5, seed=1234, traversal=api.TRAVERSAL_WIDE, time_stages=1, collect_stats=0, fetch_threshold=ft, defer_pairs=tt, samples_per_pass=int(os.environ.get("SPASS", "0")))
         ctx.reset_accum(); ctx.render(0, 4); ctx.sync()
         best = 1e9
         for rep in range(3):
