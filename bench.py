@@ -304,7 +304,7 @@ def main():
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "parallelism": f"sample ranges x{world}, replicated BVH, NCCL reduce of f32 accumulators",
-                       "l2": "L2 flushed (256 MiB write) between timed steps; per-step path state (4 Mi paths x 72 B) exceeds the 126 MB L2, the 16 MB BVH is L2-resident within a step by design",
+                       "l2": "L2 flushed (256 MiB write) between timed steps; per-step path state (64 Mi paths x 72 B = 4.8 GB) exceeds the 126 MB L2, the 16 MB BVH is L2-resident within a step by design",
                        "bvh": {"nodes": info["num_nodes"], "prims": info["num_tri_records"], "depth": info["depth"], "build_s_host": build_s}},
             "msamples_per_s": W * H * SPP * world * args.steps / (ms_total * 1e-3) / 1e6,
             "rays_per_step_per_gpu": rays_step, "rays_per_sample": rays_step / (W * H * SPP),
