@@ -79,9 +79,30 @@ __device__ __forceinline__ void camera_ray(const cupt_camera& c, int px, int py,
 	d_out = rnormalized(rsub3(prf, o));
 }
 
+// Queue compaction for a 256-thread block inside a block-uniform loop: warp ballots, one shared-memory exchange and
+// ONE global atomic per block (a single L2 address retires about one atomic per clock, so one per warp — 5 M per
+// frame on config 2 — cost milliseconds).  Returns the queue position of this thread's entry (valid only if `push`).
+__device__ __forceinline__ uint32_t block_queue_reserve(bool push, uint32_t* counter, uint32_t* s_warp /* [9] */)
+{
+	const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+	const uint32_t m = __ballot_sync(0xffffffffu, push);
+	if (lane == 0u) s_warp[w] = (uint32_t)__popc(m);
+	__syncthreads();
+	if (threadIdx.x == 0u) {
+		uint32_t run = 0u;
+		for (uint32_t i = 0; i < (blockDim.x >> 5); ++i) { const uint32_t c = s_warp[i]; s_warp[i] = run; run += c; }
+		s_warp[8] = run ? atomicAdd(counter, run) : 0u;
+	}
+	__syncthreads();
+	const uint32_t pos = s_warp[8] + s_warp[w] + (uint32_t)__popc(m & ((1u << lane) - 1u));
+	__syncthreads();   // s_warp is reused by the next loop iteration
+	return pos;
+}
+
 // ---- raygen --------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb)
 {
+	__shared__ uint32_t s_warp[9];
 	const uint32_t total = (uint32_t)pp.p_pad * (uint32_t)pp.samples;
 	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += gridDim.x * blockDim.x) {
 		const uint32_t slot = base + threadIdx.x;
@@ -105,14 +126,8 @@ __global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb)
 				pb.st1[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 			}
 		}
-		const uint32_t m = __ballot_sync(0xffffffffu, valid);
-		if (m) {
-			uint32_t wbase = 0;
-			const uint32_t lane = threadIdx.x & 31u;
-			if (lane == (uint32_t)(__ffs(m) - 1)) wbase = atomicAdd(&pb.counters[0], (uint32_t)__popc(m));
-			wbase = __shfl_sync(0xffffffffu, wbase, __ffs(m) - 1);
-			if (valid) pb.queue[0][wbase + __popc(m & ((1u << lane) - 1u))] = slot;
-		}
+		const uint32_t pos = block_queue_reserve(valid, &pb.counters[0], s_warp);
+		if (valid) pb.queue[0][pos] = slot;
 	}
 	if (blockIdx.x == 0 && threadIdx.x == 0)
 		atomicAdd(&pb.stats[3], (unsigned long long)pp.cam.pxlWidth * pp.cam.pxlHeight * pp.samples);
@@ -345,10 +360,10 @@ __device__ __forceinline__ f3 get_tangent(const f3 n)  // kernel.cu:44-54
 
 __global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathBuffers pb, int depth, int qsel)
 {
+	__shared__ uint32_t s_warp[9];
 	const uint32_t count = pb.counters[depth];
 	const uint32_t* __restrict__ qin = pb.queue[qsel];
 	uint32_t* __restrict__ qout = pb.queue[qsel ^ 1];
-	const uint32_t lane = threadIdx.x & 31u;
 	const float kBrdf = (float)(1 / 3.14159);   // BRDF(): mul(albedo, 1 / 3.14159) with a float parameter (kernel.cu:101-104)
 	const float kPi = (float)3.14159;            // color::operator*(const float&) (kernel.cu:463)
 	for (uint32_t base = blockIdx.x * blockDim.x; base < count; base += gridDim.x * blockDim.x) {
@@ -457,14 +472,8 @@ __global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathB
 				}
 			}
 		}
-		const uint32_t m = __ballot_sync(0xffffffffu, push);
-		if (m) {
-			uint32_t wbase = 0;
-			const int leader = __ffs(m) - 1;
-			if ((int)lane == leader) wbase = atomicAdd(&pb.counters[depth + 1], (uint32_t)__popc(m));
-			wbase = __shfl_sync(0xffffffffu, wbase, leader);
-			if (push) qout[wbase + __popc(m & ((1u << lane) - 1u))] = slot;
-		}
+		const uint32_t pos = block_queue_reserve(push, &pb.counters[depth + 1], s_warp);
+		if (push) qout[pos] = slot;
 	}
 }
 
