@@ -186,6 +186,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--traversal", default="wide", choices=["wide", "strict", "ref"], help="wide (default), strict = wide + reference-equality check, ref = the reference algorithm on its own BVH2")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -204,15 +205,21 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     sc, s, cam = build_scene()
+    mode = {"wide": api.TRAVERSAL_WIDE, "strict": api.TRAVERSAL_WIDE_STRICT, "ref": api.TRAVERSAL_REF_BVH2}[args.traversal]
+    n2 = None
+    if mode != api.TRAVERSAL_WIDE:   # reference-layout tree: the parity mode's structure and the tie-break ranks
+        n2, d2 = s.build_bvh2()
     t0 = time.perf_counter()
-    bvh = s.build_bvh()
+    bvh = s.build_bvh(tie_rank=None if n2 is None else api.bvh2_leaf_order(n2, s.counts()[1]))
     build_s = time.perf_counter() - t0
     info = bvh.info()
     ctx = api.Context(local)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
     ctx.set_scene(s); ctx.set_bvh(bvh); ctx.set_camera(cam)
-    ctx.set_options(max_depth=DEPTH, seed=SEED, traversal=api.TRAVERSAL_WIDE, time_stages=1, collect_stats=0)
+    if n2 is not None:
+        ctx.set_bvh2(n2, d2)
+    ctx.set_options(max_depth=DEPTH, seed=SEED, traversal=mode, time_stages=1, collect_stats=0)
     accum_t = torch.zeros(W * H * 3, dtype=torch.float32, device="cuda")
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
     from cudapathtracer_b200 import sharding
@@ -273,6 +280,8 @@ def main():
 
     def e2e_step():
         ctx.set_scene(s); ctx.set_bvh(bvh); ctx.set_camera(cam)
+        if n2 is not None:
+            ctx.set_bvh2(n2, d2)
         ctx.reset_accum(); ctx.render(first, SPP)
         if world > 1:
             ctx.copy_accum_device(accum_t.data_ptr())
@@ -303,7 +312,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "parallelism": f"sample ranges x{world}, replicated BVH, NCCL reduce of f32 accumulators",
+            "config": {"workload": WORKLOAD, "traversal": args.traversal, "parallelism": f"sample ranges x{world}, replicated BVH, NCCL reduce of f32 accumulators",
                        "l2": "L2 flushed (256 MiB write) between timed steps; per-step path state (64 Mi paths x 72 B = 4.8 GB) exceeds the 126 MB L2, the 16 MB BVH is L2-resident within a step by design",
                        "bvh": {"nodes": info["num_nodes"], "prims": info["num_tri_records"], "depth": info["depth"], "build_s_host": build_s}},
             "msamples_per_s": W * H * SPP * world * args.steps / (ms_total * 1e-3) / 1e6,

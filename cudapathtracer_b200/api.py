@@ -28,7 +28,7 @@ assert (VEC3.itemsize, TRIANGLE.itemsize, MATERIAL.itemsize, CAMERA.itemsize, BV
 LEAF_FLAG = 0x80000000
 MAX_FLOAT = np.float32(100000.0)
 INTEGRATOR_PT, INTEGRATOR_BDPT = 2, 1
-TRAVERSAL_WIDE, TRAVERSAL_REF_BVH2 = 0, 1
+TRAVERSAL_WIDE, TRAVERSAL_REF_BVH2, TRAVERSAL_WIDE_STRICT = 0, 1, 2
 TRI_REFEXACT, TRI_WATERTIGHT = 0, 1
 
 
@@ -56,7 +56,7 @@ class RenderOpts(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("samples", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("ms_raygen", C.c_double), ("ms_extend", C.c_double),
-                ("ms_shade", C.c_double), ("ms_accum", C.c_double), ("extend_launches", C.c_uint64)]
+                ("ms_shade", C.c_double), ("ms_accum", C.c_double), ("extend_launches", C.c_uint64), ("strict_retraces", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

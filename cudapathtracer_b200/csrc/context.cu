@@ -33,6 +33,7 @@ struct cupt_context {
 	// acceleration structures
 	uint4* d_nodes = nullptr; float4* d_prims = nullptr; int bvh_depth = 0; int64_t num_nodes = 0, num_prims = 0;
 	cupt_bvh2_node* d_bvh2 = nullptr; int bvh2_size = 0, bvh2_depth = 0;
+	uint32_t* d_bvh2_parent = nullptr; uint32_t* d_bvh2_leaf_parent = nullptr; int64_t bvh2_leaves = 0;
 	// camera / options
 	cupt_camera cam{}; bool have_cam = false;
 	cupt_render_opts opts{};
@@ -132,18 +133,21 @@ DevScene make_scene(const cupt_context* c)
 {
 	DevScene sc;
 	sc.nodes = c->d_nodes; sc.prims = c->d_prims; sc.bvh2 = c->d_bvh2; sc.verts = c->d_verts; sc.tris = c->d_tris;
-	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.lights = c->d_lights; sc.light_cdf = c->d_light_cdf; sc.spheres = c->d_spheres;
+	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.bvh2_parent = c->d_bvh2_parent; sc.bvh2_leaf_parent = c->d_bvh2_leaf_parent;
+	sc.lights = c->d_lights; sc.light_cdf = c->d_light_cdf; sc.spheres = c->d_spheres;
 	sc.numLights = c->num_lights; sc.totalLightArea = c->total_light_area;
 	sc.stack_cap = std::max(c->bvh_depth, 1);
 	return sc;
 }
 
-int check_ready(const cupt_context* c, bool need_shading)
+int check_ready(const cupt_context* c, bool need_shading, bool need_cam = true)
 {
 	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
-	if (!c->have_cam) return set_error(CUPT_ERR_INVALID, "no camera set (cupt_set_camera)");
-	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE && !c->d_nodes) return set_error(CUPT_ERR_INVALID, "no wide BVH set (cupt_set_bvh)");
-	if (c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 && (!c->d_bvh2 || !c->d_tris)) return set_error(CUPT_ERR_INVALID, "no reference BVH2 / scene set");
+	if (need_cam && !c->have_cam) return set_error(CUPT_ERR_INVALID, "no camera set (cupt_set_camera)");
+	if (c->opts.traversal != CUPT_TRAVERSAL_REF_BVH2 && !c->d_nodes) return set_error(CUPT_ERR_INVALID, "no wide BVH set (cupt_set_bvh)");
+	if (c->opts.traversal != CUPT_TRAVERSAL_WIDE && (!c->d_bvh2 || !c->d_tris)) return set_error(CUPT_ERR_INVALID, "no reference BVH2 / scene set");
+	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE_STRICT && (c->num_spheres > 0 || c->bvh2_leaves != c->num_tris))
+		return set_error(CUPT_ERR_INVALID, "strict mode needs a sphere-free scene and the reference BVH2 of the same scene");
 	if (need_shading && !c->d_trishade) return set_error(CUPT_ERR_INVALID, "no scene set (cupt_set_scene)");
 	return CUPT_OK;
 }
@@ -172,6 +176,14 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
 	stage_end(c, ev);
 	CK(cudaGetLastError());
 	c->launches++; c->extend_launches++;
+	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE_STRICT) {
+		StageEvent ev2;
+		stage_begin(c, 1, ev2);
+		k_verify_strict<<<c->num_sms * 8, 256, 0, c->stream>>>(sc, c->pb, depth, qsel);
+		stage_end(c, ev2);
+		CK(cudaGetLastError());
+		c->launches++;
+	}
 	return CUPT_OK;
 }
 
@@ -219,7 +231,7 @@ void cupt_destroy(cupt_context* c)
 	drain_events(c);
 	for (StageEvent& ev : c->pool) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
 	cudaFree(c->d_verts); cudaFree(c->d_tris); cudaFree(c->d_trishade); cudaFree(c->d_mats); cudaFree(c->d_lights); cudaFree(c->d_light_cdf); cudaFree(c->d_spheres);
-	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2);
+	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2); cudaFree(c->d_bvh2_parent); cudaFree(c->d_bvh2_leaf_parent);
 	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
 	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats);
 	cudaFree(c->d_accum);
@@ -254,7 +266,8 @@ int cupt_set_render_opts(cupt_context* c, const cupt_render_opts* o)
 	if (o->max_depth < 1 || o->max_depth > 62) return set_error(CUPT_ERR_INVALID, "max_depth must be in 1..62");
 	if (o->integrator != CUPT_INTEGRATOR_PT)
 		return set_error(CUPT_ERR_INVALID, "integrator %d is not implemented (only CUPT_INTEGRATOR_PT, kernel.cu:417-515)", o->integrator);
-	if (o->traversal != CUPT_TRAVERSAL_WIDE && o->traversal != CUPT_TRAVERSAL_REF_BVH2) return set_error(CUPT_ERR_INVALID, "bad traversal");
+	if (o->traversal != CUPT_TRAVERSAL_WIDE && o->traversal != CUPT_TRAVERSAL_REF_BVH2 && o->traversal != CUPT_TRAVERSAL_WIDE_STRICT)
+		return set_error(CUPT_ERR_INVALID, "bad traversal");
 	if (o->tri_test != CUPT_TRI_REFEXACT) return set_error(CUPT_ERR_INVALID, "tri_test %d is not implemented", o->tri_test);
 	c->opts = *o;
 	return CUPT_OK;
@@ -346,6 +359,20 @@ int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int de
 	CK(cudaSetDevice(c->device));
 	int rc;
 	if ((rc = upload(&c->d_bvh2, nodes, (size_t)size * sizeof(cupt_bvh2_node), c->stream))) return rc;
+	// parent links for the strict mode's ancestor walk (the reference stores child links only, BVH.h:111-115)
+	std::vector<uint32_t> parent((size_t)size, 0xffffffffu), leaf_parent;
+	for (int i = 0; i < size; ++i)
+		for (int k = 0; k < 2; ++k) {
+			const uint32_t ch = k ? nodes[i].right : nodes[i].left;
+			if (ch & CUPT_BVH_LEAF_FLAG) {
+				const uint32_t tri = ch ^ CUPT_BVH_LEAF_FLAG;
+				if (tri >= leaf_parent.size()) leaf_parent.resize((size_t)tri + 1, 0xffffffffu);
+				leaf_parent[tri] = (uint32_t)i;
+			} else if (ch < (uint32_t)size) parent[ch] = (uint32_t)i;
+		}
+	if ((rc = upload(&c->d_bvh2_parent, parent.data(), parent.size() * sizeof(uint32_t), c->stream))) return rc;
+	if ((rc = upload(&c->d_bvh2_leaf_parent, leaf_parent.data(), leaf_parent.size() * sizeof(uint32_t), c->stream))) return rc;
+	c->bvh2_leaves = (int64_t)leaf_parent.size();
 	c->bvh2_size = size; c->bvh2_depth = depth;
 	return CUPT_OK;
 }
@@ -511,8 +538,7 @@ int cupt_camera_rays(cupt_context* c, float* rays_host)
 int cupt_trace_rays(cupt_context* c, const float* rays_host, int64_t n, int32_t* tri_id, float* t)
 {
 	if (!c || !rays_host || !tri_id || !t || n < 0) return set_error(CUPT_ERR_INVALID, "bad arguments");
-	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE && !c->d_nodes) return set_error(CUPT_ERR_INVALID, "no wide BVH set (cupt_set_bvh)");
-	if (c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 && (!c->d_bvh2 || !c->d_tris)) return set_error(CUPT_ERR_INVALID, "no reference BVH2 / scene set");
+	{ const int rc0 = check_ready(c, false, false); if (rc0) return rc0; }
 	CK(cudaSetDevice(c->device));
 	const int64_t chunk = 8 << 20;
 	int rc;
@@ -552,7 +578,7 @@ int cupt_get_stats(cupt_context* c, cupt_stats* out)
 	unsigned long long h[8];
 	CK(cudaMemcpy(h, c->pb.stats, sizeof(h), cudaMemcpyDeviceToHost));
 	memset(out, 0, sizeof(*out));
-	out->rays = h[0]; out->nodes_visited = h[1]; out->tris_tested = h[2]; out->samples = h[3];
+	out->rays = h[0]; out->nodes_visited = h[1]; out->tris_tested = h[2]; out->samples = h[3]; out->strict_retraces = h[4];
 	out->kernel_launches = c->launches; out->extend_launches = c->extend_launches;
 	out->ms_raygen = c->ms[0]; out->ms_extend = c->ms[1]; out->ms_shade = c->ms[2]; out->ms_accum = c->ms[3];
 	return CUPT_OK;

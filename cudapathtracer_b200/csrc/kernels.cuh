@@ -26,6 +26,8 @@ struct DevScene {
 	const float4* trishade;        // TriShade
 	const float4* mats;            // MatF x2 float4
 	const float4* lights;          // LightTri x3 float4, numLights + 1 entries (last = triangle 0 fallback)
+	const uint32_t* bvh2_parent;   // strict mode: parent of every reference-layout inner node (root: 0xffffffff)
+	const uint32_t* bvh2_leaf_parent;  // strict mode: the inner node that holds each triangle's leaf link
 	const float* light_cdf;        // inclusive prefix sums of the light areas (only used above CUPT_LIGHT_SCAN_MAX lights)
 	const float4* spheres;         // SphereShade x3 float4: {centre, radius}, {diffuse, emissive flag}, {emission, 0}
 	int32_t numLights;
@@ -51,7 +53,7 @@ struct PathBuffers {
 	float4* st1;
 	uint32_t* queue[2];
 	uint32_t* counters;        // [0..63] queue sizes per depth, [64..127] extend fetch cursors per depth
-	unsigned long long* stats; // [0] rays, [1] nodes, [2] tris, [3] samples
+	unsigned long long* stats; // [0] rays, [1] nodes, [2] tris, [3] samples, [4] strict-mode re-traces
 };
 
 __device__ __forceinline__ void slot_to_pixel(const PassParams& pp, uint32_t slot, int& x, int& y, int& s_local)
@@ -343,6 +345,40 @@ __global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene
 		if (n_rays) atomicAdd(&pb.stats[0], (unsigned long long)n_rays);
 		if (STATS) { atomicAdd(&pb.stats[1], (unsigned long long)n_nodes); atomicAdd(&pb.stats[2], (unsigned long long)n_tris); }
 	}
+}
+
+// ---- strict mode: make the wide result equal the reference's on EVERY ray -----------------------------------------
+// The reference returns the argmin over the triangles its own traversal REACHES, and it reaches a triangle iff
+// every ancestor box passes rayAABBIntersect (kernel.cu:139-151, BVH.h:51-83), which is not conservative.  The wide
+// traversal returns the argmin over ALL triangles (ties by the reference's visiting order).  If that triangle is
+// reached by the reference, it is also the reference's answer; so this kernel walks the hit triangle's ancestor chain
+// in the reference tree with the reference's slab arithmetic, and only when an ancestor rejects the ray (about one
+// ray in 40 000 on config 2) re-traces that ray with the reference's algorithm.  A miss needs no check (reached is a
+// subset of all).  One thread per queued ray.
+__global__ void __launch_bounds__(256) k_verify_strict(DevScene sc, PathBuffers pb, int depth, int qsel)
+{
+	const uint32_t count = pb.counters[depth];
+	const uint32_t* __restrict__ queue = pb.queue[qsel];
+	uint32_t n_fallback = 0;
+	for (uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x; qi < count; qi += gridDim.x * blockDim.x) {
+		const uint32_t slot = queue[qi];
+		const float4 b = pb.rayB[slot];
+		const int32_t id = __float_as_int(b.w);
+		if (id < 0) continue;
+		const float4 a = pb.rayA[slot];
+		const f3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, b.x, b.y);
+		bool reached = true;
+		for (uint32_t n = sc.bvh2_leaf_parent[id]; n != 0xffffffffu; n = sc.bvh2_parent[n])
+			if (!ref_slab_hit(o, d, sc.bvh2[n])) { reached = false; break; }
+		if (!reached) {
+			Hit hit;
+			uint32_t nn = 0, nt = 0;
+			traverse_bvh2_ref<false>(sc.bvh2, sc.verts, sc.tris, o, d, hit, nn, nt);
+			reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(hit.t, __int_as_float(hit.id));
+			++n_fallback;
+		}
+	}
+	if (n_fallback) atomicAdd(&pb.stats[4], (unsigned long long)n_fallback);
 }
 
 // ---- shade: one iteration of radianceAlongSingleStep2 (kernel.cu:424-512) per queued path ----------------------

@@ -229,6 +229,23 @@ __device__ __forceinline__ void traverse_wide(const uint4* __restrict__ nodes, c
 	hit.t = r.best; hit.id = r.best_id; hit.rank = r.best_rank;
 }
 
+// rayAABBIntersect, BVH.h:51-83, in the reference's arithmetic: infinite-line slab test, six IEEE divisions, no t range,
+// the final z update skipped.  Not conservative (no rounding margin), which is why it can lose a triangle the ray hits.
+__device__ __forceinline__ bool ref_slab_hit(const f3 o, const f3 d, const cupt_bvh2_node& nd)
+{
+	float tmin = rdiv(rsub(nd.lo.x, o.x), d.x), tmax = rdiv(rsub(nd.hi.x, o.x), d.x);
+	if (tmin > tmax) { const float s = tmin; tmin = tmax; tmax = s; }
+	float tymin = rdiv(rsub(nd.lo.y, o.y), d.y), tymax = rdiv(rsub(nd.hi.y, o.y), d.y);
+	if (tymin > tymax) { const float s = tymin; tymin = tymax; tymax = s; }
+	if ((tmin > tymax) || (tymin > tmax)) return false;
+	if (tymin > tmin) tmin = tymin;
+	if (tymax < tmax) tmax = tymax;
+	float tzmin = rdiv(rsub(nd.lo.z, o.z), d.z), tzmax = rdiv(rsub(nd.hi.z, o.z), d.z);
+	if (tzmin > tzmax) { const float s = tzmin; tzmin = tzmax; tzmax = s; }
+	if ((tmin > tzmax) || (tzmin > tmax)) return false;
+	return true;
+}
+
 // trace(), kernel.cu:112-161, with rayAABBIntersect (BVH.h:51-83) and triIntersect (modelLoader.h:49-82) in the
 // reference's arithmetic; the visit counters (kernel.cu:133) are not kept.
 template <bool STATS>
@@ -258,19 +275,7 @@ __device__ __forceinline__ void traverse_bvh2_ref(const cupt_bvh2_node* __restri
 		} else {
 			const cupt_bvh2_node nd = nodes[e];
 			if (STATS) ++n_nodes;
-			bool b = true;
-			float tmin = rdiv(rsub(nd.lo.x, o.x), d.x), tmax = rdiv(rsub(nd.hi.x, o.x), d.x);
-			if (tmin > tmax) { const float s = tmin; tmin = tmax; tmax = s; }
-			float tymin = rdiv(rsub(nd.lo.y, o.y), d.y), tymax = rdiv(rsub(nd.hi.y, o.y), d.y);
-			if (tymin > tymax) { const float s = tymin; tymin = tymax; tymax = s; }
-			if ((tmin > tymax) || (tymin > tmax)) b = false;
-			if (b) {
-				if (tymin > tmin) tmin = tymin;
-				if (tymax < tmax) tmax = tymax;
-				float tzmin = rdiv(rsub(nd.lo.z, o.z), d.z), tzmax = rdiv(rsub(nd.hi.z, o.z), d.z);
-				if (tzmin > tzmax) { const float s = tzmin; tzmin = tzmax; tzmax = s; }
-				if ((tmin > tzmax) || (tzmin > tmax)) b = false;
-			}
+			const bool b = ref_slab_hit(o, d, nd);
 			if (b) { stack[i] = nd.right; stack[i + 1] = nd.left; ++i; }
 			else --i;
 		}

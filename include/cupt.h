@@ -143,7 +143,12 @@ int cupt_set_camera(cupt_context* c, const cupt_camera* cam);     /* kernel.cu:6
 
 enum { CUPT_INTEGRATOR_PT = 2 /* radianceAlongSingleStep2, kernel.cu:417-515 */,
        CUPT_INTEGRATOR_BDPT = 1 /* radianceAlongSingleStep, kernel.cu:217-415 */ };
-enum { CUPT_TRAVERSAL_WIDE = 0, CUPT_TRAVERSAL_REF_BVH2 = 1 /* trace(), kernel.cu:112-161 op for op */ };
+enum { CUPT_TRAVERSAL_WIDE = 0, CUPT_TRAVERSAL_REF_BVH2 = 1 /* trace(), kernel.cu:112-161 op for op */,
+       /* wide traversal, then every hit is checked against the reference tree's ancestor boxes with the reference's
+        * slab arithmetic and re-traced the reference's way if the reference would not have reached it: results equal
+        * trace() bit for bit on every ray.  Needs cupt_set_bvh AND cupt_set_bvh2, a wide BVH built with the
+        * cupt_bvh2_leaf_order ranks, and a scene without spheres. */
+       CUPT_TRAVERSAL_WIDE_STRICT = 2 };
 enum { CUPT_TRI_REFEXACT = 0 /* triIntersect, modelLoader.h:49-82, bit-identical */, CUPT_TRI_WATERTIGHT = 1 };
 
 typedef struct cupt_render_opts {
@@ -185,6 +190,7 @@ typedef struct cupt_stats {
 	uint64_t kernel_launches; /* launches of this library's kernels */
 	double ms_raygen, ms_extend, ms_shade, ms_accum;  /* time_stages */
 	uint64_t extend_launches;
+	uint64_t strict_retraces; /* CUPT_TRAVERSAL_WIDE_STRICT: rays re-traced with the reference's algorithm */
 } cupt_stats;
 int cupt_get_stats(cupt_context* c, cupt_stats* out);
 int cupt_reset_stats(cupt_context* c);

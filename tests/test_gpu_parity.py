@@ -225,3 +225,46 @@ def test_spheres_config1(ctx, get_case):
     close = np.all(np.abs(img - ref) <= 1e-3 * (1 + np.abs(ref)), axis=1)
     rel = np.sqrt(((img - ref) ** 2).mean()) / ref.mean()
     assert close.mean() >= 0.995 and rel <= 0.02, (close.mean(), rel)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_strict_mode_equals_the_reference_on_every_ray(ctx, get_case, name):
+    """CUPT_TRAVERSAL_WIDE_STRICT: wide traversal + ancestor check in the reference tree + rare re-trace.  Hits are the
+    reference's bit for bit on every ray (not only where the reference's slab test kept the nearest triangle), and
+    the radiance image is bit-identical to the REF_BVH2 mode's, hence within 1e-6 of the oracle."""
+    c = get_case(name)
+    load(ctx, c, api.TRAVERSAL_WIDE_STRICT, max_depth=5, seed=1234)
+    assert hits_equal(ctx.primary_hits(), c.osc.primary_hits(c.cam))
+    rng = np.random.default_rng(23)
+    pos = c.verts.view(np.float32).reshape(-1, 3)
+    o = rng.uniform(pos.min(0), pos.max(0), size=(30000, 3)); d = rng.normal(size=(30000, 3))
+    rays = np.concatenate([o, d / np.linalg.norm(d, axis=1, keepdims=True)], axis=1).astype(np.float32)
+    assert hits_equal(ctx.trace_rays(rays), c.osc.trace_rays(rays))
+    ctx.reset_accum(); ctx.render(0, 4); strict = ctx.read_accum(False)
+    ctx.set_options(traversal=api.TRAVERSAL_REF_BVH2)
+    ctx.reset_accum(); ctx.render(0, 4); ref = ctx.read_accum(False)
+    assert strict.tobytes() == ref.tobytes()
+
+
+def test_strict_mode_full_size(ctx, lib):
+    """config 2 at full size: the 26 primary rays on which the plain wide mode differs from the reference are gone"""
+    sc = scenes.atrium()
+    s = api.SceneHandle(); s.add_scene(sc)
+    n2, d2 = s.build_bvh2()
+    b = s.build_bvh(tie_rank=api.bvh2_leaf_order(n2, s.counts()[1]))
+    ctx.set_scene(s); ctx.set_bvh(b); ctx.set_bvh2(n2, d2); ctx.set_camera(api.make_camera(1024, 1024, **sc.camera))
+    ctx.set_options(traversal=api.TRAVERSAL_REF_BVH2, max_depth=5, seed=1234)
+    ri, rt = ctx.primary_hits()
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE)
+    wi, wt = ctx.primary_hits()
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE_STRICT)
+    ctx.reset_stats()
+    si, st = ctx.primary_hits()
+    assert hits_equal((si, st), (ri, rt))
+    plain_diff = int(((wi != ri) | (wt.view(np.uint32) != rt.view(np.uint32))).sum())
+    assert 0 < plain_diff <= 64 and ctx.stats()["strict_retraces"] >= plain_diff
+    ctx.reset_accum(); ctx.render(0, 2); a = ctx.read_accum(False)
+    ctx.set_options(traversal=api.TRAVERSAL_REF_BVH2)
+    ctx.reset_accum(); ctx.render(0, 2); r = ctx.read_accum(False)
+    assert a.tobytes() == r.tobytes()
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE)
