@@ -33,7 +33,7 @@ struct cupt_context {
 	// acceleration structures
 	uint4* d_nodes = nullptr; float4* d_prims = nullptr; int bvh_depth = 0; int64_t num_nodes = 0, num_prims = 0;
 	cupt_bvh2_node* d_bvh2 = nullptr; int bvh2_size = 0, bvh2_depth = 0;
-	uint32_t* d_bvh2_parent = nullptr; uint32_t* d_bvh2_leaf_parent = nullptr; int64_t bvh2_leaves = 0;
+	cupt_bvh2_node* d_bvh2_up = nullptr; uint32_t* d_bvh2_leaf_parent = nullptr; int64_t bvh2_leaves = 0;
 	// camera / options
 	cupt_camera cam{}; bool have_cam = false;
 	cupt_render_opts opts{};
@@ -133,7 +133,7 @@ DevScene make_scene(const cupt_context* c)
 {
 	DevScene sc;
 	sc.nodes = c->d_nodes; sc.prims = c->d_prims; sc.bvh2 = c->d_bvh2; sc.verts = c->d_verts; sc.tris = c->d_tris;
-	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.bvh2_parent = c->d_bvh2_parent; sc.bvh2_leaf_parent = c->d_bvh2_leaf_parent;
+	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.bvh2_up = c->d_bvh2_up; sc.bvh2_leaf_parent = c->d_bvh2_leaf_parent;
 	sc.lights = c->d_lights; sc.light_cdf = c->d_light_cdf; sc.spheres = c->d_spheres;
 	sc.numLights = c->num_lights; sc.totalLightArea = c->total_light_area;
 	sc.stack_cap = std::max(c->bvh_depth, 1);
@@ -231,7 +231,7 @@ void cupt_destroy(cupt_context* c)
 	drain_events(c);
 	for (StageEvent& ev : c->pool) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
 	cudaFree(c->d_verts); cudaFree(c->d_tris); cudaFree(c->d_trishade); cudaFree(c->d_mats); cudaFree(c->d_lights); cudaFree(c->d_light_cdf); cudaFree(c->d_spheres);
-	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2); cudaFree(c->d_bvh2_parent); cudaFree(c->d_bvh2_leaf_parent);
+	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2); cudaFree(c->d_bvh2_up); cudaFree(c->d_bvh2_leaf_parent);
 	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
 	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats);
 	cudaFree(c->d_accum);
@@ -370,7 +370,9 @@ int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int de
 				leaf_parent[tri] = (uint32_t)i;
 			} else if (ch < (uint32_t)size) parent[ch] = (uint32_t)i;
 		}
-	if ((rc = upload(&c->d_bvh2_parent, parent.data(), parent.size() * sizeof(uint32_t), c->stream))) return rc;
+	std::vector<cupt_bvh2_node> up(nodes, nodes + size);
+	for (int i = 0; i < size; ++i) { up[(size_t)i].left = parent[(size_t)i]; up[(size_t)i].right = 0u; }
+	if ((rc = upload(&c->d_bvh2_up, up.data(), up.size() * sizeof(cupt_bvh2_node), c->stream))) return rc;
 	if ((rc = upload(&c->d_bvh2_leaf_parent, leaf_parent.data(), leaf_parent.size() * sizeof(uint32_t), c->stream))) return rc;
 	c->bvh2_leaves = (int64_t)leaf_parent.size();
 	c->bvh2_size = size; c->bvh2_depth = depth;

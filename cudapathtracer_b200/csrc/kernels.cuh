@@ -26,7 +26,8 @@ struct DevScene {
 	const float4* trishade;        // TriShade
 	const float4* mats;            // MatF x2 float4
 	const float4* lights;          // LightTri x3 float4, numLights + 1 entries (last = triangle 0 fallback)
-	const uint32_t* bvh2_parent;   // strict mode: parent of every reference-layout inner node (root: 0xffffffff)
+	const cupt_bvh2_node* bvh2_up;  // strict mode: copy of the reference nodes with `left` = PARENT index (root: 0xffffffff): box and
+	                                // next link of the ancestor walk in one 32-byte sector
 	const uint32_t* bvh2_leaf_parent;  // strict mode: the inner node that holds each triangle's leaf link
 	const float* light_cdf;        // inclusive prefix sums of the light areas (only used above CUPT_LIGHT_SCAN_MAX lights)
 	const float4* spheres;         // SphereShade x3 float4: {centre, radius}, {diffuse, emissive flag}, {emission, 0}
@@ -367,9 +368,27 @@ __global__ void __launch_bounds__(256) k_verify_strict(DevScene sc, PathBuffers 
 		if (id < 0) continue;
 		const float4 a = pb.rayA[slot];
 		const f3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, b.x, b.y);
+		// Most ancestors contain the hit point comfortably; a division-free test with an explicit error margin proves
+		// "the reference accepts" for those (quotients by multiplication with 1/d are within 2^-22 relative of the
+		// reference's correctly rounded divisions), and only the rest run the reference's six divisions.
+		const float ix = 1.0f / d.x, iy = 1.0f / d.y, iz = 1.0f / d.z;
 		bool reached = true;
-		for (uint32_t n = sc.bvh2_leaf_parent[id]; n != 0xffffffffu; n = sc.bvh2_parent[n])
-			if (!ref_slab_hit(o, d, sc.bvh2[n])) { reached = false; break; }
+		for (uint32_t n = sc.bvh2_leaf_parent[id]; n != 0xffffffffu;) {
+			const uint4 w0 = ldg_nc_u4(reinterpret_cast<const uint4*>(sc.bvh2_up + n)), w1 = ldg_nc_u4(reinterpret_cast<const uint4*>(sc.bvh2_up + n) + 1);
+			cupt_bvh2_node nd;   // two 128-bit fetches (the struct itself is only 4-byte aligned and would load as eight words)
+			nd.lo.x = __uint_as_float(w0.x); nd.lo.y = __uint_as_float(w0.y); nd.lo.z = __uint_as_float(w0.z);
+			nd.hi.x = __uint_as_float(w0.w); nd.hi.y = __uint_as_float(w1.x); nd.hi.z = __uint_as_float(w1.y);
+			nd.left = w1.z; nd.right = w1.w;
+			n = nd.left;
+			const float x1 = rsub(nd.lo.x, o.x) * ix, x2 = rsub(nd.hi.x, o.x) * ix;
+			const float y1 = rsub(nd.lo.y, o.y) * iy, y2 = rsub(nd.hi.y, o.y) * iy;
+			const float z1 = rsub(nd.lo.z, o.z) * iz, z2 = rsub(nd.hi.z, o.z) * iz;
+			const float txn = fminf(x1, x2), txf = fmaxf(x1, x2), tyn = fminf(y1, y2), tyf = fmaxf(y1, y2);
+			const float tzn = fminf(z1, z2), tzf = fmaxf(z1, z2);
+			const float m = fmaxf(fmaxf(fmaxf(fabsf(x1), fabsf(x2)), fmaxf(fabsf(y1), fabsf(y2))), fmaxf(fabsf(z1), fabsf(z2))) * 9.5367431640625e-7f;
+			const bool sure = m < 1.0e30f && txn <= tyf - m && tyn <= txf - m && fmaxf(txn, tyn) <= tzf - m && tzn <= fminf(txf, tyf) - m;
+			if (!sure && !ref_slab_hit(o, d, nd)) { reached = false; break; }
+		}
 		if (!reached) {
 			Hit hit;
 			uint32_t nn = 0, nt = 0;
