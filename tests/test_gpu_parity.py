@@ -268,3 +268,35 @@ def test_strict_mode_full_size(ctx, lib):
     ctx.reset_accum(); ctx.render(0, 2); r = ctx.read_accum(False)
     assert a.tobytes() == r.tobytes()
     ctx.set_options(traversal=api.TRAVERSAL_WIDE)
+
+
+def test_native_render_loop_example(ctx, lib, tmp_path):
+    """examples/render_loop.cpp = the reference's main() (kernel.cu:565-790) in C++ over the C-ABI: OBJ in, PPM out.
+    Its image must be byte-identical to the same render driven through the Python binding."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "examples", "render_loop")
+    if not os.path.exists(exe):
+        import __graft_entry__
+        __graft_entry__.build()
+    sc = scenes.cornell_box()
+    obj, mtl = scenes.to_obj(sc)
+    (tmp_path / "models").mkdir()
+    (tmp_path / "models" / "cornell.obj").write_text(obj)
+    (tmp_path / "models" / "scene.mtl").write_text(mtl)
+    out = tmp_path / "image.ppm"
+    r = subprocess.run([exe, str(tmp_path / "models" / "cornell.obj"), str(tmp_path / "models") + "/", "64", "48", "8", "5", str(out), "strict"],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout
+    assert "Mrays/s (counted)" in r.stdout and "32 tris" in r.stdout
+    s = api.SceneHandle()
+    s.load_obj(str(tmp_path / "models" / "cornell.obj"), str(tmp_path / "models") + "/")
+    n2, d2 = s.build_bvh2()
+    b = s.build_bvh(tie_rank=api.bvh2_leaf_order(n2, s.counts()[1]))
+    ctx.set_scene(s); ctx.set_bvh(b); ctx.set_bvh2(n2, d2); ctx.set_camera(api.make_camera(64, 48, **sc.camera))
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE_STRICT, max_depth=5, seed=1234)
+    ctx.reset_accum(); ctx.render(0, 8)
+    ref = tmp_path / "ref.ppm"
+    api.write_ppm(str(ref), ctx.read_accum(True), 64, 48)
+    assert out.read_bytes() == ref.read_bytes()
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE)
