@@ -2,7 +2,8 @@
 oracle/build_ref.sh).  Run here (needs /root/reference); the vectors travel, the reference does not.
 
 For each small case: the reference's own loadOBJ output (via OBJ text), buildBVH() node array, primary hit ids and
-t bits of cameraRay + trace, and the f64 radiance sums of radianceAlongSingleStep2 with the keyed Philox stream.
+t bits of cameraRay + trace, and the f64 radiance sums of radianceAlongSingleStep2 and of the live
+radianceAlongSingleStep (BDPT) with the keyed Philox stream.
     python tests/golden/make_golden.py
 """
 import hashlib
@@ -42,6 +43,9 @@ def main():
             out[f"pt_sum_nb{nb}_spp{spp}_seed{seed}"] = ssum
             out[f"pt_mean_nb{nb}_spp{spp}_seed{seed}"] = mean
             out[f"pt_rays_nb{nb}_spp{spp}_seed{seed}"] = np.uint64(nrays)
+        # the LIVE integrator radianceAlongSingleStep (fixed-length BDPT, kernel.cu:217-415), same keyed Philox stream
+        mean, ssum, nrays = refbind.render(cam, integrator=1, num_bounces=3, rng=1, seed=1234, first_sample=0, num_samples=4)
+        out["bdpt_sum_spp4_seed1234"], out["bdpt_mean_spp4_seed1234"], out["bdpt_rays_spp4_seed1234"] = ssum, mean, np.uint64(nrays)
         np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
         print(name, "tris", len(tris), "nodes", len(nodes), "depth", depth, "hits", int((ids >= 0).sum()), "/", len(ids))
     ph = {f"{s}_{x}_{y}_{k}": refbind.philox_uniforms(s, x, y, k, 19) for s, x, y, k in ((1234, 0, 0, 0), (1234, 5, 7, 3), (2**40 + 17, 1023, 2159, 1023))}

@@ -28,6 +28,7 @@ def lib():
     if _lib is None:
         l = C.CDLL(ORACLE_SO)
         l.orc_render_pt.restype = C.c_ulonglong
+        l.orc_render_bdpt.restype = C.c_ulonglong
         _lib = l
     return _lib
 
@@ -92,6 +93,18 @@ class OracleScene:
         rays = lib().orc_render_pt(C.byref(self.c), _p(cam), num_bounces, C.c_uint64(seed), first_sample, num_samples,
                                    _p(mean), _p(ssum))
         return mean, ssum, int(rays)
+
+
+def _render_bdpt(self, cam, seed=1234, first_sample=0, num_samples=1):
+    """live integrator radianceAlongSingleStep (kernel.cu:217-415): (mean, sum, rays)"""
+    cam = np.ascontiguousarray(cam, dtype=CAMERA)
+    n = int(cam["pxlWidth"][0]) * int(cam["pxlHeight"][0])
+    mean, ssum = np.zeros((n, 3)), np.zeros((n, 3))
+    rays = lib().orc_render_bdpt(C.byref(self.c), _p(cam), C.c_uint64(seed), first_sample, num_samples, _p(mean), _p(ssum))
+    return mean, ssum, int(rays)
+
+
+OracleScene.render_bdpt = _render_bdpt
 
 
 def philox_uniforms(seed, x, y, sample, n):

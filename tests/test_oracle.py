@@ -37,6 +37,15 @@ def test_oracle_radiance_matches_golden_bit_for_bit(oracle, name):
         assert rays == int(g[f"pt_rays_nb{nb}_spp{spp}_seed{seed}"])
 
 
+@pytest.mark.parametrize("name", CASES)
+def test_oracle_bdpt_matches_golden_bit_for_bit(oracle, name):
+    """the live integrator radianceAlongSingleStep (kernel.cu:217-415): restatement == real reference, f64 bits and ray count"""
+    g, osc, cam = gold_case(oracle, name)
+    mean, ssum, rays = osc.render_bdpt(cam, 1234, 0, 4)
+    assert ssum.tobytes() == g["bdpt_sum_spp4_seed1234"].tobytes() and mean.tobytes() == g["bdpt_mean_spp4_seed1234"].tobytes()
+    assert rays == int(g["bdpt_rays_spp4_seed1234"])
+
+
 def test_oracle_philox_and_tonemap_match_golden(oracle):
     g = np.load(os.path.join(GOLD, "misc.npz"))
     for k in g.files:
@@ -62,6 +71,9 @@ def test_oracle_against_live_reference(oracle, ref):
     assert np.array_equal(ri, oi) and rt.tobytes() == ot.tobytes()
     rm, rs, rr = ref.render(cam, integrator=2, num_bounces=7, rng=1, seed=77, first_sample=3, num_samples=3)
     om, os_, orr = osc.render_pt(cam, 7, 77, 3, 3)
+    assert rm.tobytes() == om.tobytes() and rs.tobytes() == os_.tobytes() and rr == orr
+    rm, rs, rr = ref.render(cam, integrator=1, num_bounces=3, rng=1, seed=77, first_sample=2, num_samples=3)
+    om, os_, orr = osc.render_bdpt(cam, 77, 2, 3)
     assert rm.tobytes() == om.tobytes() and rs.tobytes() == os_.tobytes() and rr == orr
     rng = np.random.default_rng(1)
     rays = np.concatenate([rng.uniform(-10, 10, (5000, 3)), rng.normal(size=(5000, 3))], axis=1).astype(np.float32)
