@@ -5,7 +5,9 @@
 #include "host_common.h"
 #include "layout.h"
 #include "kernels.cuh"
+#include "bdpt.cuh"
 #include <algorithm>
+#include <map>
 #include <cstring>
 
 using namespace cupt;
@@ -44,19 +46,27 @@ struct cupt_context {
 	uint64_t launches = 0, extend_launches = 0;
 	double ms[4] = {0, 0, 0, 0};
 	std::vector<StageEvent> pending, pool;
+	std::map<void**, size_t> capacity;   // bytes behind each uploaded device pointer (upload())
 	int extend_blocks[2] = {0, 0};
 };
 
 namespace {
 
+// Device buffers keep their capacity: re-uploading a scene or BVH of the same (or a smaller) size neither frees nor
+// allocates, so it does not synchronise the device (cudaFree does) and is ordered on the context's stream behind
+// whatever render is still in flight.  The caller synchronises once after its last upload (staging temporaries).
 template <class T>
-int upload(T** dst, const void* src, size_t bytes, cudaStream_t st)
+int upload(cupt_context* c, T** dst, const void* src, size_t bytes)
 {
-	if (*dst) { CK(cudaFree(*dst)); *dst = nullptr; }
+	size_t& cap = c->capacity[(void**)dst];
+	if (bytes > cap || !*dst) {
+		if (*dst) { CK(cudaFree(*dst)); *dst = nullptr; cap = 0; }
+		if (bytes == 0) return CUPT_OK;
+		CK(cudaMalloc((void**)dst, bytes));
+		cap = bytes;
+	}
 	if (bytes == 0) return CUPT_OK;
-	CK(cudaMalloc((void**)dst, bytes));
-	CK(cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, st));
-	CK(cudaStreamSynchronize(st));  // the host staging buffers are temporaries
+	CK(cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
 	return CUPT_OK;
 }
 
@@ -264,8 +274,8 @@ int cupt_set_render_opts(cupt_context* c, const cupt_render_opts* o)
 {
 	if (!c || !o) return set_error(CUPT_ERR_INVALID, "bad arguments");
 	if (o->max_depth < 1 || o->max_depth > 62) return set_error(CUPT_ERR_INVALID, "max_depth must be in 1..62");
-	if (o->integrator != CUPT_INTEGRATOR_PT)
-		return set_error(CUPT_ERR_INVALID, "integrator %d is not implemented (only CUPT_INTEGRATOR_PT, kernel.cu:417-515)", o->integrator);
+	if (o->integrator != CUPT_INTEGRATOR_PT && o->integrator != CUPT_INTEGRATOR_BDPT)
+		return set_error(CUPT_ERR_INVALID, "unknown integrator %d", o->integrator);
 	if (o->traversal != CUPT_TRAVERSAL_WIDE && o->traversal != CUPT_TRAVERSAL_REF_BVH2 && o->traversal != CUPT_TRAVERSAL_WIDE_STRICT)
 		return set_error(CUPT_ERR_INVALID, "bad traversal");
 	if (o->tri_test != CUPT_TRI_REFEXACT) return set_error(CUPT_ERR_INVALID, "tri_test %d is not implemented", o->tri_test);
@@ -290,21 +300,21 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 	CK(cudaSetDevice(c->device));
 	const size_t nt = s->tris.size(), nm = s->mats.size(), nl = s->lights.size();
 	int rc;
-	if ((rc = upload(&c->d_verts, s->verts.data(), s->verts.size() * sizeof(cupt_vec3), c->stream))) return rc;
-	if ((rc = upload(&c->d_tris, s->tris.data(), nt * sizeof(cupt_triangle), c->stream))) return rc;
+	if ((rc = upload(c, &c->d_verts, s->verts.data(), s->verts.size() * sizeof(cupt_vec3)))) return rc;
+	if ((rc = upload(c, &c->d_tris, s->tris.data(), nt * sizeof(cupt_triangle)))) return rc;
 	std::vector<TriShade> ts(nt);
 	for (size_t i = 0; i < nt; ++i) {
 		ts[i].n[0] = s->tris[i].norm.x; ts[i].n[1] = s->tris[i].norm.y; ts[i].n[2] = s->tris[i].norm.z;
 		ts[i].mat = s->tris[i].mat;
 	}
-	if ((rc = upload(&c->d_trishade, ts.data(), nt * sizeof(TriShade), c->stream))) return rc;
+	if ((rc = upload(c, &c->d_trishade, ts.data(), nt * sizeof(TriShade)))) return rc;
 	std::vector<MatF> mf(nm);
 	for (size_t i = 0; i < nm; ++i) {
 		for (int k = 0; k < 3; ++k) { mf[i].albedo[k] = (float)s->mats[i].albedo[k]; mf[i].emission[k] = (float)s->mats[i].emission[k]; }
 		mf[i].emissive_flag = s->mats[i].emission[0] != 0 ? 1.f : 0.f;  // kernel.cu:453 tests the f64 value
 		mf[i].pad = 0.f;
 	}
-	if ((rc = upload(&c->d_mats, mf.data(), nm * sizeof(MatF), c->stream))) return rc;
+	if ((rc = upload(c, &c->d_mats, mf.data(), nm * sizeof(MatF)))) return rc;
 	// light table: per light v0, a1 = v1 - v0, a2 = v2 - v0 and area = length(cross(a1, a2)) / 2 (kernel.cu:472-477),
 	// plus the fallback entry for `selectedTri = 0` (kernel.cu:469)
 	std::vector<LightTri> lt(nl + 1);
@@ -316,12 +326,14 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 		lt[j].a1[0] = a1.x; lt[j].a1[1] = a1.y; lt[j].a1[2] = a1.z;
 		lt[j].a2[0] = a2.x; lt[j].a2[1] = a2.y; lt[j].a2[2] = a2.z;
 		lt[j].area = length3(cross3(a1, a2)) / 2;
+		const int32_t tri_index = j < nl ? s->lights[j] : 0;   // read back by the BDPT stages (scene.lights[j], kernel.cu:242)
+		memcpy(&lt[j].pad0, &tri_index, sizeof(int32_t));
 	}
-	if ((rc = upload(&c->d_lights, lt.data(), lt.size() * sizeof(LightTri), c->stream))) return rc;
+	if ((rc = upload(c, &c->d_lights, lt.data(), lt.size() * sizeof(LightTri)))) return rc;
 	std::vector<float> cdf(nl);
 	double run = 0;
 	for (size_t j = 0; j < nl; ++j) { run += (double)lt[j].area; cdf[j] = (float)run; }
-	if ((rc = upload(&c->d_light_cdf, cdf.data(), nl * sizeof(float), c->stream))) return rc;
+	if ((rc = upload(c, &c->d_light_cdf, cdf.data(), nl * sizeof(float)))) return rc;
 	std::vector<SphereShade> ss(s->spheres.size());
 	for (size_t i = 0; i < ss.size(); ++i) {
 		const cupt_sphere& sp = s->spheres[i];
@@ -330,9 +342,10 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 		ss[i].emissive_flag = sp.emm[0] != 0 ? 1.f : 0.f;
 		ss[i].pad = 0.f;
 	}
-	if ((rc = upload(&c->d_spheres, ss.data(), ss.size() * sizeof(SphereShade), c->stream))) return rc;
+	if ((rc = upload(c, &c->d_spheres, ss.data(), ss.size() * sizeof(SphereShade)))) return rc;
 	c->num_spheres = (int)ss.size();
 	c->num_tris = (int64_t)nt; c->num_lights = (int)nl; c->total_light_area = s->totalLightArea;
+	CK(cudaStreamSynchronize(c->stream));   // the staging vectors above are temporaries
 	return CUPT_OK;
 }
 
@@ -344,10 +357,11 @@ int cupt_set_bvh(cupt_context* c, const cupt_bvh* b)
 		return set_error(CUPT_ERR_LIMIT, "more than 2^27 primitive records (the extend kernel packs record index and lane into 32 bits)");
 	CK(cudaSetDevice(c->device));
 	int rc;
-	if ((rc = upload(&c->d_nodes, b->nodes.data(), b->nodes.size() * sizeof(Node8), c->stream))) return rc;
-	if ((rc = upload(&c->d_prims, b->prims.data(), b->prims.size() * sizeof(Prim48), c->stream))) return rc;
+	if ((rc = upload(c, &c->d_nodes, b->nodes.data(), b->nodes.size() * sizeof(Node8)))) return rc;
+	if ((rc = upload(c, &c->d_prims, b->prims.data(), b->prims.size() * sizeof(Prim48)))) return rc;
 	c->bvh_depth = b->depth; c->num_nodes = (int64_t)b->nodes.size(); c->num_prims = (int64_t)b->prims.size();
 	c->extend_blocks[0] = 0;
+	CK(cudaStreamSynchronize(c->stream));   // the caller may destroy the cupt_bvh right after this call
 	return CUPT_OK;
 }
 
@@ -358,7 +372,7 @@ int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int de
 		return set_error(CUPT_ERR_LIMIT, "BVH depth is too big (%d >= %d)", depth, CUPT_MAX_BVH2_DEPTH);
 	CK(cudaSetDevice(c->device));
 	int rc;
-	if ((rc = upload(&c->d_bvh2, nodes, (size_t)size * sizeof(cupt_bvh2_node), c->stream))) return rc;
+	if ((rc = upload(c, &c->d_bvh2, nodes, (size_t)size * sizeof(cupt_bvh2_node)))) return rc;
 	// parent links for the strict mode's ancestor walk (the reference stores child links only, BVH.h:111-115)
 	std::vector<uint32_t> parent((size_t)size, 0xffffffffu), leaf_parent;
 	for (int i = 0; i < size; ++i)
@@ -372,10 +386,11 @@ int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int de
 		}
 	std::vector<cupt_bvh2_node> up(nodes, nodes + size);
 	for (int i = 0; i < size; ++i) { up[(size_t)i].left = parent[(size_t)i]; up[(size_t)i].right = 0u; }
-	if ((rc = upload(&c->d_bvh2_up, up.data(), up.size() * sizeof(cupt_bvh2_node), c->stream))) return rc;
-	if ((rc = upload(&c->d_bvh2_leaf_parent, leaf_parent.data(), leaf_parent.size() * sizeof(uint32_t), c->stream))) return rc;
+	if ((rc = upload(c, &c->d_bvh2_up, up.data(), up.size() * sizeof(cupt_bvh2_node)))) return rc;
+	if ((rc = upload(c, &c->d_bvh2_leaf_parent, leaf_parent.data(), leaf_parent.size() * sizeof(uint32_t)))) return rc;
 	c->bvh2_leaves = (int64_t)leaf_parent.size();
 	c->bvh2_size = size; c->bvh2_depth = depth;
+	CK(cudaStreamSynchronize(c->stream));
 	return CUPT_OK;
 }
 
@@ -388,17 +403,45 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 	if ((rc = ensure_accum(c))) return rc;
 	const DevScene sc = make_scene(c);
 	PassParams probe = make_pass(c, 0, 1, 0);
+	const bool bdpt = c->opts.integrator == CUPT_INTEGRATOR_BDPT;
+	if (bdpt && c->num_spheres > 0) return set_error(CUPT_ERR_INVALID, "the BDPT integrator (kernel.cu:217-415) has no sphere support");
 	int S = c->opts.samples_per_pass;
-	if (S <= 0) S = (int)std::max<int64_t>(1, (int64_t)(64 << 20) / probe.p_pad);   // 64 Mi paths x 72 B = 4.8 GB of path state: long passes amortise the tail of every extend launch
+	// PT: 64 Mi paths x 72 B = 4.8 GB of path state: long passes amortise the tail of every extend launch;
+	// BDPT keeps four ray records and four connection records per path (288 B): 16 Mi paths
+	if (S <= 0) S = (int)std::max<int64_t>(1, (int64_t)((bdpt ? 16 : 64) << 20) / probe.p_pad);
 	S = std::min(S, std::max(1, num_samples));
-	if ((int64_t)probe.p_pad * S > 0x7fffffff) S = (int)(0x7fffffff / probe.p_pad);
-	if ((rc = ensure_paths(c, (size_t)probe.p_pad * S))) return rc;
+	const int64_t per_path = bdpt ? 4 : 1;
+	if ((int64_t)probe.p_pad * S * per_path > 0x7fffffff) S = (int)(0x7fffffff / (probe.p_pad * per_path));
+	if ((rc = ensure_paths(c, (size_t)probe.p_pad * S * per_path))) return rc;
 	const int grid = c->num_sms * 8;
 	for (int done = 0; done < num_samples; done += S) {
 		const int s_now = std::min(S, num_samples - done);
 		const PassParams pp = make_pass(c, first_sample + done, s_now, 0);
 		CK(cudaMemsetAsync(c->pb.counters, 0, 128 * sizeof(uint32_t), c->stream));
 		StageEvent ev;
+		if (bdpt) {
+			// radianceAlongSingleStep, kernel.cu:217-415, as three extend rounds (bdpt.cuh)
+			stage_begin(c, 0, ev);
+			k_bdpt_gen<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb);
+			stage_end(c, ev);
+			if ((rc = launch_extend(c, sc, 0, 0))) return rc;
+			stage_begin(c, 2, ev);
+			k_bdpt_mid<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb);
+			stage_end(c, ev);
+			if ((rc = launch_extend(c, sc, 1, 1))) return rc;
+			stage_begin(c, 2, ev);
+			k_bdpt_connect<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb);
+			stage_end(c, ev);
+			if ((rc = launch_extend(c, sc, 2, 0))) return rc;
+			stage_begin(c, 3, ev);
+			k_bdpt_resolve<<<grid, 256, 0, c->stream>>>(c->pb);
+			k_bdpt_accumulate<<<(pp.p_pad + 255) / 256, 256, 0, c->stream>>>(pp, c->pb, c->d_accum);
+			stage_end(c, ev);
+			c->launches += 5;
+			CK(cudaGetLastError());
+			c->samples_accumulated += (uint64_t)s_now;
+			continue;
+		}
 		stage_begin(c, 0, ev);
 		k_raygen<<<grid, 256, 0, c->stream>>>(pp, c->pb);
 		stage_end(c, ev);

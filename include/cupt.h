@@ -142,7 +142,7 @@ int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int de
 int cupt_set_camera(cupt_context* c, const cupt_camera* cam);     /* kernel.cu:642-651 */
 
 enum { CUPT_INTEGRATOR_PT = 2 /* radianceAlongSingleStep2, kernel.cu:417-515 */,
-       CUPT_INTEGRATOR_BDPT = 1 /* radianceAlongSingleStep, kernel.cu:217-415 */ };
+       CUPT_INTEGRATOR_BDPT = 1 /* radianceAlongSingleStep, kernel.cu:217-415: what drawPixel calls at HEAD (kernel.cu:549); max_depth is ignored */ };
 enum { CUPT_TRAVERSAL_WIDE = 0, CUPT_TRAVERSAL_REF_BVH2 = 1 /* trace(), kernel.cu:112-161 op for op */,
        /* wide traversal, then every hit is checked against the reference tree's ancestor boxes with the reference's
         * slab arithmetic and re-traced the reference's way if the reference would not have reached it: results equal
