@@ -283,6 +283,27 @@ class Context:
     def set_bvh(self, bvh: BvhHandle):
         _check(self.lib.cupt_set_bvh(self.h, bvh.h))
 
+    def build_bvh_device(self, max_leaf_tris=0, tie_rank: Optional[np.ndarray] = None) -> dict:
+        """cupt_build_bvh_device: wide BVH built on the GPU from the uploaded scene (replaces buildBVH + its upload)"""
+        rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, dtype=np.uint32)
+        opts = BvhOpts(0, max_leaf_tris, 0, None if rank is None else rank.ctypes.data)
+        i = BvhInfo()
+        _check(self.lib.cupt_build_bvh_device(self.h, C.byref(opts), C.byref(i)))
+        d = {n: getattr(i, n) for n, _ in BvhInfo._fields_}
+        ms = (C.c_float * 4)()
+        _check(self.lib.cupt_get_build_times(self.h, ms))
+        d.update(ms_total=ms[0], ms_sort=ms[1], ms_cluster=ms[2], ms_collapse=ms[3])
+        return d
+
+    def read_bvh(self):
+        """(nodes, prims, depth, clustering rounds) of the wide BVH currently on the device"""
+        counts = (C.c_int64 * 4)()
+        _check(self.lib.cupt_read_bvh(self.h, None, None, counts))
+        nodes = np.zeros(counts[0], dtype=NODE8)
+        prims = np.zeros(counts[1], dtype=PRIM48)
+        _check(self.lib.cupt_read_bvh(self.h, _ptr(nodes), _ptr(prims), counts))
+        return nodes, prims, int(counts[2]), int(counts[3])
+
     def set_bvh2(self, nodes: np.ndarray, depth: int):
         nodes = np.ascontiguousarray(nodes, dtype=BVH2_NODE)
         _check(self.lib.cupt_set_bvh2(self.h, _ptr(nodes), len(nodes), depth))

@@ -1,0 +1,620 @@
+// GPU-side construction of the wide quantised BVH: replaces buildBVH (BVH.h:133-474), the step
+// immediately before the hot path, with kernels that read the scene arrays cupt_set_scene already put in HBM and
+// write the Node8 / Prim48 arrays k_extend traverses, without a host round trip.
+//
+//   1. k_leaf_boxes     padded box per primitive (same 4-ulp padding as the host builder), centroid bounds
+//   2. k_morton         63-bit Morton code of the centroid, radix sort of (code, primitive)      [cub::DeviceRadixSort]
+//   3. PLOC rounds      parallel locally-ordered clustering (Meister & Bittner, "Parallel Locally-Ordered Clustering
+//                       for Bounding Volume Hierarchy Construction", TVCG 2018): every cluster finds the neighbour
+//                       within +-R positions of the Morton order whose union box has the smallest area; mutual pairs
+//                       merge; an order-preserving compaction closes the gaps.  Four launches per round
+//                       (k_ploc_nearest, k_ploc_count, k_scan_tiles, k_ploc_merge), ~log_1.5(N) rounds.
+//   4. collapse + emit  level by level from the root: open the child with the largest area until there are eight
+//                       (same rule as the host builder), octant-slot assignment, 8-bit quantisation, breadth-first
+//                       emission (k_collapse_count, k_scan_tiles, k_collapse_emit per level).
+//
+// The tree differs from the host builder's (binned SAH), the traversal result does not: k_extend returns the argmin
+// over all primitives whatever the tree (tests/test_gpu_parity.py compares with the brute force bit for bit).
+// Node numbering is deterministic (positions come from prefix sums, not from atomics).
+#include "host_common.h"
+#include "layout.h"
+#include "bvh_device.h"
+#include <cub/device/device_radix_sort.cuh>
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstring>
+
+namespace cupt {
+namespace devbuild {
+
+#define CKB(call)                                                                                          \
+	do {                                                                                                   \
+		cudaError_t e_ = (call);                                                                           \
+		if (e_ != cudaSuccess) {                                                                           \
+			ws.release();                                                                                  \
+			return set_error(CUPT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+		}                                                                                                  \
+	} while (0)
+
+constexpr int kTile = 256;        // threads per block = elements per scan tile
+constexpr int kRadius = 8;        // PLOC search radius
+
+// binary node: leaves are 0..N-1 in Morton order (left = -1 - primitive), inner nodes N..2N-2
+struct alignas(16) N2 {
+	float lo[3]; int32_t left;
+	float hi[3]; int32_t right;
+};
+
+__device__ __forceinline__ float half_area(const float lx, const float ly, const float lz, const float hx, const float hy, const float hz)
+{
+	const float dx = hx - lx, dy = hy - ly, dz = hz - lz;
+	return dx * dy + dx * dz + dy * dz;
+}
+
+// order-preserving float <-> uint for atomicMin/atomicMax
+__device__ __forceinline__ uint32_t f2ord(const float f) { const uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__host__ __device__ __forceinline__ float ord2f(const uint32_t o) { const uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o; float f; memcpy(&f, &u, 4); return f; }
+
+// ---- 1. primitive boxes ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTile) k_leaf_boxes(const float* __restrict__ verts, const cupt_triangle* __restrict__ tris, const int64_t nt,
+                                                      const float4* __restrict__ spheres, const int64_t N, N2* __restrict__ leaf, uint32_t* __restrict__ cbounds)
+{
+	const int64_t i = (int64_t)blockIdx.x * kTile + threadIdx.x;
+	float c[3] = {0.f, 0.f, 0.f};
+	const bool valid = i < N;
+	if (valid) {
+		float lo[3], hi[3];
+		if (i < nt) {
+			const cupt_triangle t = tris[i];
+			const int32_t vi[3] = {t.v0, t.v1, t.v2};
+			for (int a = 0; a < 3; ++a) { lo[a] = 3.0e38f; hi[a] = -3.0e38f; }
+			for (int k = 0; k < 3; ++k)
+				for (int a = 0; a < 3; ++a) { const float v = verts[3 * (size_t)vi[k] + a]; lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v); }
+		} else {
+			const float4 s = spheres[3 * (i - nt)];   // SphereShade: centre, radius
+			const float cc[3] = {s.x, s.y, s.z};
+			for (int a = 0; a < 3; ++a) { lo[a] = __fsub_rn(cc[a], s.w); hi[a] = __fadd_rn(cc[a], s.w); }
+		}
+		N2 n;
+		for (int a = 0; a < 3; ++a) {
+			c[a] = __fadd_rn(__fmul_rn(0.5f, lo[a]), __fmul_rn(0.5f, hi[a]));
+			const float m = fmaxf(fmaxf(fabsf(lo[a]), fabsf(hi[a])), 1e-30f);
+			const float pad = __fmul_rn(m, 4.8e-7f);   // 4 ulp, as bvh8_build.cpp: the reference's triangle test is plain f32
+			n.lo[a] = __fsub_rn(lo[a], pad); n.hi[a] = __fadd_rn(hi[a], pad);
+		}
+		n.left = -1 - (int32_t)i; n.right = -1;
+		leaf[i] = n;
+	}
+	// centroid bounds: warp reduce, one atomic pair per warp and axis
+	for (int a = 0; a < 3; ++a) {
+		uint32_t mn = valid ? f2ord(c[a]) : 0xffffffffu, mx = valid ? f2ord(c[a]) : 0u;
+		mn = __reduce_min_sync(0xffffffffu, mn); mx = __reduce_max_sync(0xffffffffu, mx);
+		if ((threadIdx.x & 31) == 0) { atomicMin(&cbounds[a], mn); atomicMax(&cbounds[3 + a], mx); }
+	}
+}
+
+// ---- 2. Morton codes -------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t spread21(uint64_t x)
+{
+	x &= 0x1fffffull;
+	x = (x | x << 32) & 0x1f00000000ffffull;
+	x = (x | x << 16) & 0x1f0000ff0000ffull;
+	x = (x | x << 8) & 0x100f00f00f00f00full;
+	x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+	x = (x | x << 2) & 0x1249249249249249ull;
+	return x;
+}
+
+__global__ void __launch_bounds__(kTile) k_morton(const N2* __restrict__ leaf, const int64_t N, const uint32_t* __restrict__ cbounds,
+                                                  uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
+{
+	const int64_t i = (int64_t)blockIdx.x * kTile + threadIdx.x;
+	if (i >= N) return;
+	const N2 n = leaf[i];
+	uint64_t code = 0;
+	for (int a = 0; a < 3; ++a) {
+		const float lo = ord2f(cbounds[a]), hi = ord2f(cbounds[3 + a]);
+		const float c = 0.5f * n.lo[a] + 0.5f * n.hi[a];
+		const float ext = hi - lo;
+		float u = ext > 0.f ? (c - lo) / ext : 0.f;
+		u = fminf(fmaxf(u, 0.f), 1.f);
+		const uint64_t q = (uint64_t)fminf(u * 2097152.0f, 2097151.0f);
+		code |= spread21(q) << (2 - a);
+	}
+	keys[i] = code; vals[i] = (uint32_t)i;
+}
+
+__global__ void __launch_bounds__(kTile) k_sorted_leaves(const N2* __restrict__ leaf, const uint32_t* __restrict__ order, const int64_t N,
+                                                         N2* __restrict__ nodes, uint32_t* __restrict__ cnt, uint32_t* __restrict__ cid)
+{
+	const int64_t i = (int64_t)blockIdx.x * kTile + threadIdx.x;
+	if (i >= N) return;
+	nodes[i] = leaf[order[i]];
+	cnt[i] = 1u; cid[i] = (uint32_t)i;
+}
+
+// ---- exclusive scan of per-tile 64-bit sums (two 32-bit counters packed in one word), one block -------------------
+__device__ __forceinline__ uint64_t warp_scan_incl(uint64_t v)
+{
+	for (int d = 1; d < 32; d <<= 1) {
+		const uint64_t o = __shfl_up_sync(0xffffffffu, v, d);
+		if ((threadIdx.x & 31) >= d) v += o;
+	}
+	return v;
+}
+// exclusive scan over the block's kTile values; returns the exclusive prefix, *total = the block sum
+__device__ __forceinline__ uint64_t block_scan_excl(const uint64_t v, uint64_t* s_warp /* kTile/32 + 1 */, uint64_t* total)
+{
+	const uint64_t incl = warp_scan_incl(v);
+	const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+	__syncthreads();   // s_warp may still be read from a previous call
+	if (l == 31) s_warp[w] = incl;
+	__syncthreads();
+	if (w == 0) {
+		uint64_t x = l < kTile / 32 ? s_warp[l] : 0ull;
+		const uint64_t xi = warp_scan_incl(x);
+		if (l < kTile / 32) s_warp[l] = xi - x;
+		if (l == kTile / 32 - 1) s_warp[kTile / 32] = xi;
+	}
+	__syncthreads();
+	*total = s_warp[kTile / 32];
+	return s_warp[w] + incl - v;
+}
+
+__global__ void __launch_bounds__(kTile) k_scan_tiles(uint64_t* __restrict__ tile_sums, const int ntiles, uint64_t* __restrict__ total_out)
+{
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	uint64_t carry = 0;
+	for (int base = 0; base < ntiles; base += kTile) {
+		const int i = base + threadIdx.x;
+		const uint64_t v = i < ntiles ? tile_sums[i] : 0ull;
+		uint64_t tot;
+		const uint64_t ex = block_scan_excl(v, s_warp, &tot);
+		if (i < ntiles) tile_sums[i] = carry + ex;
+		carry += tot;
+	}
+	if (threadIdx.x == 0) *total_out = carry;
+}
+
+// ---- 3. PLOC ---------------------------------------------------------------------------------------------------
+// Nearest neighbour of cluster i among positions i-R..i+R by the half-area of the union box.  Ties are broken by a
+// strict total order on UNORDERED pairs — (area, |i-j|, min(i,j) odd, min(i,j)) — so the globally smallest pair is
+// always mutual (progress every round) and a run of identical boxes pairs up as (0,1)(2,3)... instead of chaining.
+__global__ void __launch_bounds__(kTile) k_ploc_nearest(const N2* __restrict__ nodes, const uint32_t* __restrict__ cid, const int n, uint32_t* __restrict__ nn)
+{
+	__shared__ float s_box[6][kTile + 2 * kRadius];
+	const int base = (int)blockIdx.x * kTile - kRadius;
+	for (int k = threadIdx.x; k < kTile + 2 * kRadius; k += kTile) {
+		const int g = base + k;
+		if (g >= 0 && g < n) {
+			const float4* p = reinterpret_cast<const float4*>(&nodes[cid[g]]);
+			const float4 a = __ldg(p), b = __ldg(p + 1);
+			s_box[0][k] = a.x; s_box[1][k] = a.y; s_box[2][k] = a.z;
+			s_box[3][k] = b.x; s_box[4][k] = b.y; s_box[5][k] = b.z;
+		}
+	}
+	__syncthreads();
+	const int i = (int)blockIdx.x * kTile + threadIdx.x;
+	if (i >= n) return;
+	const int li = threadIdx.x + kRadius;
+	const float lx = s_box[0][li], ly = s_box[1][li], lz = s_box[2][li], hx = s_box[3][li], hy = s_box[4][li], hz = s_box[5][li];
+	float best = 3.0e38f;
+	int bj = -1;
+#pragma unroll
+	for (int d = 1; d <= kRadius; ++d) {
+		// within one distance: the candidate whose pair minimum is even first, then the lower minimum (= the left one)
+		const bool right_first = (((i - d) & 1) == 1) && ((i & 1) == 0);
+#pragma unroll
+		for (int side = 0; side < 2; ++side) {
+			const int off = ((side == 0) == right_first) ? d : -d;
+			const int j = i + off;
+			if (j < 0 || j >= n) continue;
+			const int lj = li + off;
+			const float a = half_area(fminf(lx, s_box[0][lj]), fminf(ly, s_box[1][lj]), fminf(lz, s_box[2][lj]),
+			                          fmaxf(hx, s_box[3][lj]), fmaxf(hy, s_box[4][lj]), fmaxf(hz, s_box[5][lj]));
+			if (a < best || bj < 0) { best = a; bj = j; }
+		}
+	}
+	nn[i] = (uint32_t)bj;
+}
+
+// valid = the slot survives the round (everything but the higher half of a mutual pair); leader = lower half
+__device__ __forceinline__ uint64_t ploc_flags(const uint32_t* __restrict__ nn, const int i, const int n, int* partner)
+{
+	if (i >= n) { *partner = -1; return 0ull; }
+	const int j = (int)nn[i];
+	const bool mutual = (int)nn[j] == i;
+	*partner = mutual ? j : -1;
+	const uint64_t valid = !(mutual && i > j), leader = mutual && i < j;
+	return valid | (leader << 32);
+}
+
+__global__ void __launch_bounds__(kTile) k_ploc_count(const uint32_t* __restrict__ nn, const int n, uint64_t* __restrict__ tile_sums)
+{
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	int partner;
+	const uint64_t f = ploc_flags(nn, (int)blockIdx.x * kTile + threadIdx.x, n, &partner);
+	uint64_t tot;
+	block_scan_excl(f, s_warp, &tot);
+	if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(kTile) k_ploc_merge(N2* __restrict__ nodes, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ cid_in,
+                                                      uint32_t* __restrict__ cid_out, const uint32_t* __restrict__ nn, const int n,
+                                                      const uint64_t* __restrict__ tile_offs, const uint32_t node_base)
+{
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	const int i = (int)blockIdx.x * kTile + threadIdx.x;
+	int partner;
+	const uint64_t f = ploc_flags(nn, i, n, &partner);
+	uint64_t tot;
+	const uint64_t pos = tile_offs[blockIdx.x] + block_scan_excl(f, s_warp, &tot);
+	if (!(f & 1ull)) return;
+	const uint32_t out = (uint32_t)pos;
+	if (f >> 32) {
+		const uint32_t id = node_base + (uint32_t)(pos >> 32);
+		const uint32_t l = cid_in[i], r = cid_in[partner];
+		const float4* pl = reinterpret_cast<const float4*>(&nodes[l]);
+		const float4* pr = reinterpret_cast<const float4*>(&nodes[r]);
+		const float4 la = pl[0], lb = pl[1], ra = pr[0], rb = pr[1];
+		float4 oa = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), __int_as_float((int32_t)l));
+		float4 ob = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), __int_as_float((int32_t)r));
+		float4* po = reinterpret_cast<float4*>(&nodes[id]);
+		po[0] = oa; po[1] = ob;
+		cnt[id] = cnt[l] + cnt[r];
+		cid_out[out] = id;
+	} else {
+		cid_out[out] = cid_in[i];
+	}
+}
+
+// ---- 4. collapse to 8-wide + emission ----------------------------------------------------------------------------
+struct Kids { int32_t id[8]; int n; };
+
+__device__ __forceinline__ float node_half_area(const N2* __restrict__ nodes, const int32_t id)
+{
+	const float4* p = reinterpret_cast<const float4*>(&nodes[id]);
+	const float4 a = __ldg(p), b = __ldg(p + 1);
+	return half_area(a.x, a.y, a.z, b.x, b.y, b.z);
+}
+
+// the children of one wide node: start from the binary node's two children and keep opening the inner child with the
+// largest area (bvh8_build.cpp does the same); a subtree with at most max_leaf primitives is a leaf and is not opened
+__device__ __forceinline__ void gather_kids(const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt, const int32_t root, const uint32_t max_leaf, Kids& k)
+{
+	if (cnt[root] <= max_leaf) { k.id[0] = root; k.n = 1; return; }
+	float area[8];
+	k.id[0] = nodes[root].left; k.id[1] = nodes[root].right; k.n = 2;
+#pragma unroll
+	for (int q = 0; q < 2; ++q) area[q] = cnt[k.id[q]] > max_leaf ? node_half_area(nodes, k.id[q]) : -1.f;
+	while (k.n < 8) {
+		int best = -1; float ba = -1.f;
+		for (int q = 0; q < k.n; ++q)
+			if (area[q] > ba) { ba = area[q]; best = q; }
+		if (best < 0) break;
+		const int32_t open = k.id[best];
+		const int32_t l = nodes[open].left, r = nodes[open].right;
+		k.id[best] = l; area[best] = cnt[l] > max_leaf ? fmaxf(node_half_area(nodes, l), 0.f) : -1.f;
+		k.id[k.n] = r; area[k.n] = cnt[r] > max_leaf ? fmaxf(node_half_area(nodes, r), 0.f) : -1.f;
+		k.n++;
+	}
+}
+
+// per item of the level: (inner children | leaf primitives << 32), reduced to one sum per tile
+__global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt, const int32_t* __restrict__ items,
+                                                          const int n_items, const uint32_t max_leaf, uint64_t* __restrict__ item_counts, uint64_t* __restrict__ tile_sums)
+{
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	const int i = (int)blockIdx.x * kTile + threadIdx.x;
+	uint64_t f = 0;
+	if (i < n_items) {
+		Kids k;
+		gather_kids(nodes, cnt, items[i], max_leaf, k);
+		uint32_t ni = 0, np = 0;
+		for (int q = 0; q < k.n; ++q) {
+			const uint32_t c = cnt[k.id[q]];
+			if (c > max_leaf) ni++; else np += c;
+		}
+		f = (uint64_t)ni | ((uint64_t)np << 32);
+		item_counts[i] = f;
+	}
+	uint64_t tot;
+	block_scan_excl(f, s_warp, &tot);
+	if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+}
+
+__device__ __forceinline__ int dev_float_exponent(const float v) { return (int)((__float_as_uint(v) >> 23) & 0xffu) - 127; }
+
+__device__ __forceinline__ void write_prim(const int32_t prim, const int64_t nt, const float* __restrict__ verts, const cupt_triangle* __restrict__ tris,
+                                           const float4* __restrict__ spheres, const uint32_t* __restrict__ rank, float4* __restrict__ out)
+{
+	float4 r0, r1, r2;
+	if (prim < nt) {
+		const cupt_triangle t = tris[prim];
+		const float* a = verts + 3 * (size_t)t.v0; const float* b = verts + 3 * (size_t)t.v1; const float* c = verts + 3 * (size_t)t.v2;
+		const float v0x = a[0], v0y = a[1], v0z = a[2];
+		const float e1x = __fsub_rn(b[0], v0x), e1y = __fsub_rn(b[1], v0y), e1z = __fsub_rn(b[2], v0z);   // modelLoader.h:57-58
+		const float e2x = __fsub_rn(c[0], v0x), e2y = __fsub_rn(c[1], v0y), e2z = __fsub_rn(c[2], v0z);
+		r0 = make_float4(v0x, v0y, v0z, e1x);
+		r1 = make_float4(e1y, e1z, e2x, e2y);
+		r2 = make_float4(e2z, __uint_as_float((uint32_t)prim), __uint_as_float(rank ? rank[prim] : (uint32_t)prim), __uint_as_float(0u));
+	} else {
+		const float4 s = spheres[3 * (size_t)(prim - nt)];
+		r0 = make_float4(s.x, s.y, s.z, s.w);
+		r1 = make_float4(0.f, 0.f, 0.f, 0.f);
+		r2 = make_float4(0.f, __uint_as_float((uint32_t)(prim - nt)), __uint_as_float((uint32_t)prim), __uint_as_float(1u));
+	}
+	out[0] = r0; out[1] = r1; out[2] = r2;
+}
+
+struct EmitArgs {
+	const N2* nodes; const uint32_t* cnt; const int32_t* items; int n_items; uint32_t max_leaf;
+	const uint64_t* item_counts; const uint64_t* tile_offs;
+	uint32_t level_base, next_base, prim_base;
+	int32_t* next_items; Node8* out_nodes; float4* out_prims;
+	const float* verts; const cupt_triangle* tris; const float4* spheres; const uint32_t* rank; int64_t nt;
+	double inv_root_area; double* sah;
+};
+
+__global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
+{
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	const int i = (int)blockIdx.x * kTile + threadIdx.x;
+	const uint64_t f = i < A.n_items ? A.item_counts[i] : 0ull;
+	uint64_t tot;
+	const uint64_t ex = A.tile_offs[blockIdx.x] + block_scan_excl(f, s_warp, &tot);
+	if (i >= A.n_items) return;
+	const int32_t self = A.items[i];
+	Kids k;
+	gather_kids(A.nodes, A.cnt, self, A.max_leaf, k);
+	float blo[3], bhi[3];
+	{
+		const float4* p = reinterpret_cast<const float4*>(&A.nodes[self]);
+		const float4 a = __ldg(p), b = __ldg(p + 1);
+		blo[0] = a.x; blo[1] = a.y; blo[2] = a.z; bhi[0] = b.x; bhi[1] = b.y; bhi[2] = b.z;
+	}
+	// octant slots: greedy assignment maximising dot(child centre - node centre, slot direction), as bvh8_build.cpp
+	float clo[8][3], chi[8][3], cost[8][8];
+	int slotOf[8], childIn[8];
+	for (int q = 0; q < 8; ++q) { slotOf[q] = -1; childIn[q] = -1; }
+	for (int q = 0; q < k.n; ++q) {
+		const float4* p = reinterpret_cast<const float4*>(&A.nodes[k.id[q]]);
+		const float4 a = __ldg(p), b = __ldg(p + 1);
+		clo[q][0] = a.x; clo[q][1] = a.y; clo[q][2] = a.z; chi[q][0] = b.x; chi[q][1] = b.y; chi[q][2] = b.z;
+		float d[3];
+		for (int a3 = 0; a3 < 3; ++a3) d[a3] = (0.5f * clo[q][a3] + 0.5f * chi[q][a3]) - (0.5f * blo[a3] + 0.5f * bhi[a3]);
+		for (int sl = 0; sl < 8; ++sl)
+			cost[q][sl] = ((sl & 4) ? d[0] : -d[0]) + ((sl & 2) ? d[1] : -d[1]) + ((sl & 1) ? d[2] : -d[2]);
+	}
+	for (int it = 0; it < k.n; ++it) {
+		int bk = -1, bs = -1; float bc = -3.0e38f;
+		for (int q = 0; q < k.n; ++q) {
+			if (slotOf[q] >= 0) continue;
+			for (int sl = 0; sl < 8; ++sl)
+				if (childIn[sl] < 0 && (cost[q][sl] > bc || bk < 0)) { bc = cost[q][sl]; bk = q; bs = sl; }
+		}
+		slotOf[bk] = bs; childIn[bs] = bk;
+	}
+	// quantisation grid: power-of-two cell per axis, at least 2^-24 of the coordinate magnitude
+	Node8 nd;
+	memset(&nd, 0, sizeof(nd));
+	double scale[3];
+	for (int a = 0; a < 3; ++a) {
+		nd.p[a] = blo[a];
+		const double ext = (double)bhi[a] - (double)blo[a];
+		int e = -126;
+		if (ext > 0) { e = (int)ceil(log2(ext / 255.0)); while (ldexp(255.0, e) < ext) ++e; }
+		const float m = fmaxf(fabsf(blo[a]), fabsf(bhi[a]));
+		e = max(e, dev_float_exponent(m) - 24);
+		e = max(-126, min(127, e));
+		nd.e[a] = (uint8_t)(e + 127);
+		scale[a] = ldexp(1.0, e);
+	}
+	const uint32_t child_off = (uint32_t)ex, prim_off = (uint32_t)(ex >> 32);
+	nd.child_base = A.next_base + child_off;
+	nd.tri_base = A.prim_base + prim_off;
+	uint32_t triOfs = 0, ninner = 0;
+	double sah = 0;
+	for (int sl = 0; sl < 8; ++sl) {
+		const int q = childIn[sl];
+		if (q < 0) continue;
+		const int32_t c = k.id[q];
+		for (int a = 0; a < 3; ++a) {
+			const double p = nd.p[a];
+			double ql = floor(((double)clo[q][a] - p) / scale[a]);
+			double qh = ceil(((double)chi[q][a] - p) / scale[a]);
+			while (ql > 0 && p + ql * scale[a] > (double)clo[q][a]) ql -= 1;
+			while (p + qh * scale[a] < (double)chi[q][a]) qh += 1;
+			ql = fmax(0.0, fmin(255.0, ql));
+			qh = fmin(255.0, fmax(qh, ql));   // hi <= node hi <= p + 255 * scale by construction of e
+			nd.qlo[a][sl] = (uint8_t)ql; nd.qhi[a][sl] = (uint8_t)qh;
+		}
+		const uint32_t cc = A.cnt[c];
+		const double area2 = 2.0 * (double)half_area(clo[q][0], clo[q][1], clo[q][2], chi[q][0], chi[q][1], chi[q][2]);
+		if (cc > A.max_leaf) {
+			nd.imask |= (uint8_t)(1u << sl);
+			nd.meta[sl] = (uint8_t)((1u << 5) | (24u + sl));
+			A.next_items[child_off + ninner++] = c;
+			sah += area2 * A.inv_root_area;
+		} else {
+			const uint32_t unary = cc == 1 ? 1u : (cc == 2 ? 3u : 7u);
+			nd.meta[sl] = (uint8_t)((unary << 5) | triOfs);
+			int32_t stack[4]; int sp = 0;
+			stack[sp++] = c;
+			uint32_t w = 0;
+			while (sp > 0) {                       // <= 3 primitives: left-first walk of the tiny subtree
+				const int32_t x = stack[--sp];
+				const int32_t l = A.nodes[x].left;
+				if (l < 0) {
+					write_prim(-1 - l, A.nt, A.verts, A.tris, A.spheres, A.rank, A.out_prims + 3 * (size_t)(nd.tri_base + triOfs + w));
+					++w;
+				} else {
+					stack[sp++] = A.nodes[x].right; stack[sp++] = l;
+				}
+			}
+			triOfs += cc;
+			sah += area2 * A.inv_root_area * cc;
+		}
+	}
+	const uint4* src = reinterpret_cast<const uint4*>(&nd);
+	uint4* dst = reinterpret_cast<uint4*>(&A.out_nodes[A.level_base + i]);
+#pragma unroll
+	for (int w = 0; w < 5; ++w) dst[w] = src[w];
+	atomicAdd(A.sah, sah);
+}
+
+struct Workspace {
+	std::vector<void*> ptrs;
+	template <class T>
+	cudaError_t alloc(T** p, size_t n)
+	{
+		const cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T));
+		if (e == cudaSuccess) ptrs.push_back((void*)*p);
+		return e;
+	}
+	void drop(void* p)
+	{
+		for (size_t i = 0; i < ptrs.size(); ++i)
+			if (ptrs[i] == p) { cudaFree(p); ptrs.erase(ptrs.begin() + (long)i); return; }
+	}
+	void forget(void* p)   // ownership leaves the workspace
+	{
+		for (size_t i = 0; i < ptrs.size(); ++i)
+			if (ptrs[i] == p) { ptrs.erase(ptrs.begin() + (long)i); return; }
+	}
+	void release()
+	{
+		for (void* p : ptrs) cudaFree(p);
+		ptrs.clear();
+	}
+};
+
+}  // namespace devbuild
+
+using namespace devbuild;
+
+int build_wide_bvh_device(cudaStream_t st, const float* verts, const cupt_triangle* tris, int64_t nt, const float4* spheres, int64_t ns,
+                          const uint32_t* rank, int max_leaf, DeviceBvh* out)
+{
+	const int64_t N = nt + ns;
+	if (N < 1) return set_error(CUPT_ERR_INVALID, "scene has no primitives");
+	if (N > (1ll << 27)) return set_error(CUPT_ERR_LIMIT, "more than 2^27 primitives");
+	max_leaf = std::max(1, std::min(3, max_leaf));
+	Workspace ws;
+	cudaEvent_t ev[5];
+	for (auto& e : ev) CKB(cudaEventCreate(&e));
+	const int tilesN = (int)((N + kTile - 1) / kTile);
+
+	// 1-2: boxes, Morton codes, sort
+	N2* leaf = nullptr; uint32_t* cbounds = nullptr;
+	uint64_t* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
+	CKB(ws.alloc(&leaf, (size_t)N)); CKB(ws.alloc(&cbounds, 6));
+	for (int b = 0; b < 2; ++b) { CKB(ws.alloc(&keys[b], (size_t)N)); CKB(ws.alloc(&vals[b], (size_t)N)); }
+	static const uint32_t cb_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+	CKB(cudaEventRecord(ev[0], st));
+	CKB(cudaMemcpyAsync(cbounds, cb_init, sizeof(cb_init), cudaMemcpyHostToDevice, st));
+	k_leaf_boxes<<<tilesN, kTile, 0, st>>>(verts, tris, nt, spheres, N, leaf, cbounds);
+	k_morton<<<tilesN, kTile, 0, st>>>(leaf, N, cbounds, keys[0], vals[0]);
+	cub::DoubleBuffer<uint64_t> dk(keys[0], keys[1]);
+	cub::DoubleBuffer<uint32_t> dv(vals[0], vals[1]);
+	size_t temp_bytes = 0;
+	CKB(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, dk, dv, (int)N, 0, 63, st));
+	uint8_t* temp = nullptr;
+	CKB(ws.alloc(&temp, temp_bytes));
+	CKB(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, dk, dv, (int)N, 0, 63, st));
+	CKB(cudaEventRecord(ev[1], st));
+
+	// 3: PLOC
+	N2* nodes = nullptr; uint32_t* cnt = nullptr; uint32_t* cid[2] = {nullptr, nullptr}; uint32_t* nn = nullptr;
+	uint64_t* tile_sums = nullptr; uint64_t* d_total = nullptr; uint64_t* h_total = nullptr;
+	CKB(ws.alloc(&nodes, (size_t)2 * N)); CKB(ws.alloc(&cnt, (size_t)2 * N));
+	CKB(ws.alloc(&cid[0], (size_t)N)); CKB(ws.alloc(&cid[1], (size_t)N)); CKB(ws.alloc(&nn, (size_t)N));
+	CKB(ws.alloc(&tile_sums, (size_t)tilesN + 1)); CKB(ws.alloc(&d_total, 1));
+	CKB(cudaMallocHost((void**)&h_total, sizeof(uint64_t)));
+	struct HostGuard { uint64_t* p; ~HostGuard() { cudaFreeHost(p); } } host_guard{h_total};
+	k_sorted_leaves<<<tilesN, kTile, 0, st>>>(leaf, dv.Current(), N, nodes, cnt, cid[0]);
+	CKB(cudaStreamSynchronize(st));
+	ws.drop(leaf); ws.drop(keys[0]); ws.drop(keys[1]); ws.drop(vals[0]); ws.drop(vals[1]); ws.drop(temp);
+	int n = (int)N, cur = 0, rounds = 0;
+	uint32_t node_base = (uint32_t)N;
+	while (n > 1) {
+		const int tiles = (n + kTile - 1) / kTile;
+		k_ploc_nearest<<<tiles, kTile, 0, st>>>(nodes, cid[cur], n, nn);
+		k_ploc_count<<<tiles, kTile, 0, st>>>(nn, n, tile_sums);
+		k_scan_tiles<<<1, kTile, 0, st>>>(tile_sums, tiles, d_total);
+		k_ploc_merge<<<tiles, kTile, 0, st>>>(nodes, cnt, cid[cur], cid[cur ^ 1], nn, n, tile_sums, node_base);
+		CKB(cudaMemcpyAsync(h_total, d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+		CKB(cudaStreamSynchronize(st));
+		const uint32_t valid = (uint32_t)*h_total, leaders = (uint32_t)(*h_total >> 32);
+		if (leaders == 0 || (int)valid + (int)leaders != n) { ws.release(); return set_error(CUPT_ERR_CUDA, "internal: PLOC round made no progress (n %d, valid %u, merged %u)", n, valid, leaders); }
+		n = (int)valid; node_base += leaders; cur ^= 1; ++rounds;
+	}
+	CKB(cudaEventRecord(ev[2], st));
+	const int32_t root = N == 1 ? 0 : (int32_t)node_base - 1;
+
+	// 4: collapse + emit, level by level
+	N2 root_box;
+	CKB(cudaMemcpyAsync(&root_box, nodes + root, sizeof(N2), cudaMemcpyDeviceToHost, st));
+	CKB(cudaStreamSynchronize(st));
+	const double rdx = (double)root_box.hi[0] - root_box.lo[0], rdy = (double)root_box.hi[1] - root_box.lo[1], rdz = (double)root_box.hi[2] - root_box.lo[2];
+	const double root_area = std::max(2.0 * (rdx * rdy + rdx * rdz + rdy * rdz), 1e-300);
+	int32_t* items[2] = {reinterpret_cast<int32_t*>(cid[0]), reinterpret_cast<int32_t*>(cid[1])};
+	uint64_t* item_counts = nullptr; double* d_sah = nullptr;
+	CKB(ws.alloc(&item_counts, (size_t)N / 2 + 2)); CKB(ws.alloc(&d_sah, 1));
+	CKB(cudaMemsetAsync(d_sah, 0, sizeof(double), st));
+	Node8* out_nodes = nullptr; float4* out_prims = nullptr;
+	size_t node_cap = (size_t)N / 3 + 1024;
+	CKB(ws.alloc(&out_nodes, node_cap)); CKB(ws.alloc(&out_prims, (size_t)N * 3));
+	CKB(cudaMemcpyAsync(items[0], &root, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+	int n_items = 1, lvl = 0, depth = 0;
+	uint32_t level_base = 0, prim_base = 0;
+	while (n_items > 0) {
+		++depth;
+		if ((size_t)level_base + (size_t)n_items > node_cap) {   // rare: grow the node array
+			const size_t ncap = std::max(node_cap * 2, (size_t)level_base + (size_t)n_items);
+			Node8* bigger = nullptr;
+			CKB(ws.alloc(&bigger, ncap));
+			CKB(cudaMemcpyAsync(bigger, out_nodes, (size_t)level_base * sizeof(Node8), cudaMemcpyDeviceToDevice, st));
+			CKB(cudaStreamSynchronize(st));
+			ws.drop(out_nodes); out_nodes = bigger; node_cap = ncap;
+		}
+		const int tiles = (n_items + kTile - 1) / kTile;
+		k_collapse_count<<<tiles, kTile, 0, st>>>(nodes, cnt, items[lvl], n_items, (uint32_t)max_leaf, item_counts, tile_sums);
+		k_scan_tiles<<<1, kTile, 0, st>>>(tile_sums, tiles, d_total);
+		EmitArgs A;
+		A.nodes = nodes; A.cnt = cnt; A.items = items[lvl]; A.n_items = n_items; A.max_leaf = (uint32_t)max_leaf;
+		A.item_counts = item_counts; A.tile_offs = tile_sums;
+		A.level_base = level_base; A.next_base = level_base + (uint32_t)n_items; A.prim_base = prim_base;
+		A.next_items = items[lvl ^ 1]; A.out_nodes = out_nodes; A.out_prims = out_prims;
+		A.verts = verts; A.tris = tris; A.spheres = spheres; A.rank = rank; A.nt = nt;
+		A.inv_root_area = 1.0 / root_area; A.sah = d_sah;
+		k_collapse_emit<<<tiles, kTile, 0, st>>>(A);
+		CKB(cudaMemcpyAsync(h_total, d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+		CKB(cudaStreamSynchronize(st));
+		level_base += (uint32_t)n_items;
+		prim_base += (uint32_t)(*h_total >> 32);
+		n_items = (int)(uint32_t)*h_total;
+		lvl ^= 1;
+		if (depth > 255) { ws.release(); return set_error(CUPT_ERR_LIMIT, "wide BVH deeper than 255 levels"); }
+	}
+	CKB(cudaEventRecord(ev[3], st));
+	double sah = 0;
+	CKB(cudaMemcpyAsync(&sah, d_sah, sizeof(double), cudaMemcpyDeviceToHost, st));
+	CKB(cudaStreamSynchronize(st));
+	CKB(cudaGetLastError());
+	if ((int64_t)prim_base != N) { ws.release(); return set_error(CUPT_ERR_CUDA, "internal: emitted %u primitive records for %lld primitives", prim_base, (long long)N); }
+	out->nodes = out_nodes; out->prims = out_prims;
+	out->num_nodes = level_base; out->num_prims = N;
+	out->nodes_capacity_bytes = node_cap * sizeof(Node8); out->prims_capacity_bytes = (size_t)N * 48;
+	out->depth = depth; out->ploc_rounds = rounds; out->sah_cost = sah;
+	cudaEventElapsedTime(&out->ms_sort, ev[0], ev[1]);
+	cudaEventElapsedTime(&out->ms_ploc, ev[1], ev[2]);
+	cudaEventElapsedTime(&out->ms_collapse, ev[2], ev[3]);
+	cudaEventElapsedTime(&out->ms_total, ev[0], ev[3]);
+	for (auto& e : ev) cudaEventDestroy(e);
+	ws.forget(out_nodes); ws.forget(out_prims);
+	ws.release();
+	return CUPT_OK;
+}
+
+}  // namespace cupt

@@ -1,0 +1,24 @@
+// GPU-side wide-BVH construction (bvh_device.cu); internal to libcupt, called by cupt_build_bvh_device (context.cu).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../../include/cupt.h"
+
+namespace cupt {
+
+struct DeviceBvh {
+	void* nodes = nullptr;      // Node8[num_nodes]   (cudaMalloc; ownership passes to the caller)
+	void* prims = nullptr;      // Prim48[num_prims]
+	int64_t num_nodes = 0, num_prims = 0;
+	size_t nodes_capacity_bytes = 0, prims_capacity_bytes = 0;
+	int depth = 0, ploc_rounds = 0;
+	double sah_cost = 0;
+	float ms_total = 0, ms_sort = 0, ms_ploc = 0, ms_collapse = 0;   // CUDA events on the build stream
+};
+
+// verts/tris/spheres: the device arrays of the uploaded scene (spheres: SphereShade records, centre + radius first);
+// rank: optional device array of tie-break ranks per triangle (NULL = triangle index)
+int build_wide_bvh_device(cudaStream_t stream, const float* verts, const cupt_triangle* tris, int64_t num_tris,
+                          const float4* spheres, int64_t num_spheres, const uint32_t* rank, int max_leaf, DeviceBvh* out);
+
+}  // namespace cupt

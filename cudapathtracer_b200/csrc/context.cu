@@ -6,6 +6,7 @@
 #include "layout.h"
 #include "kernels.cuh"
 #include "bdpt.cuh"
+#include "bvh_device.h"
 #include <algorithm>
 #include <map>
 #include <cstring>
@@ -48,6 +49,7 @@ struct cupt_context {
 	std::vector<StageEvent> pending, pool;
 	std::map<void**, size_t> capacity;   // bytes behind each uploaded device pointer (upload())
 	int extend_blocks[2] = {0, 0};
+	float build_ms[4] = {0, 0, 0, 0}; int build_rounds = 0;   // last cupt_build_bvh_device: total, sort, PLOC, collapse
 };
 
 namespace {
@@ -362,6 +364,55 @@ int cupt_set_bvh(cupt_context* c, const cupt_bvh* b)
 	c->bvh_depth = b->depth; c->num_nodes = (int64_t)b->nodes.size(); c->num_prims = (int64_t)b->prims.size();
 	c->extend_blocks[0] = 0;
 	CK(cudaStreamSynchronize(c->stream));   // the caller may destroy the cupt_bvh right after this call
+	return CUPT_OK;
+}
+
+int cupt_build_bvh_device(cupt_context* c, const cupt_bvh_opts* opts, cupt_bvh_info* info)
+{
+	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
+	if (!c->d_tris && c->num_spheres == 0) return set_error(CUPT_ERR_INVALID, "cupt_set_scene has not been called");
+	CK(cudaSetDevice(c->device));
+	uint32_t* d_rank = nullptr;
+	if (opts && opts->tie_rank && c->num_tris > 0) {
+		CK(cudaMalloc((void**)&d_rank, (size_t)c->num_tris * sizeof(uint32_t)));
+		CK(cudaMemcpyAsync(d_rank, opts->tie_rank, (size_t)c->num_tris * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+	}
+	DeviceBvh r;
+	const int rc = build_wide_bvh_device(c->stream, c->d_verts, c->d_tris, c->num_tris, c->d_spheres, c->num_spheres, d_rank,
+	                                     (opts && opts->max_leaf_tris >= 1) ? opts->max_leaf_tris : 3, &r);
+	cudaFree(d_rank);
+	if (rc) return rc;
+	cudaFree(c->d_nodes); cudaFree(c->d_prims);
+	c->d_nodes = (uint4*)r.nodes; c->d_prims = (float4*)r.prims;
+	c->capacity[(void**)&c->d_nodes] = r.nodes_capacity_bytes; c->capacity[(void**)&c->d_prims] = r.prims_capacity_bytes;
+	c->bvh_depth = r.depth; c->num_nodes = r.num_nodes; c->num_prims = r.num_prims;
+	c->extend_blocks[0] = 0;
+	if (info) {
+		info->num_nodes = r.num_nodes; info->num_tri_records = r.num_prims;
+		info->num_tris = c->num_tris; info->num_spheres = c->num_spheres;
+		info->depth = r.depth; info->node_bytes = (int32_t)sizeof(Node8); info->tri_bytes = (int32_t)sizeof(Prim48);
+		info->sah_cost = r.sah_cost; info->build_seconds = (double)r.ms_total * 1e-3;
+	}
+	c->build_ms[0] = r.ms_total; c->build_ms[1] = r.ms_sort; c->build_ms[2] = r.ms_ploc; c->build_ms[3] = r.ms_collapse; c->build_rounds = r.ploc_rounds;
+	return CUPT_OK;
+}
+
+int cupt_read_bvh(cupt_context* c, void* nodes80, void* tris48, int64_t* counts)
+{
+	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
+	if (!c->d_nodes) return set_error(CUPT_ERR_INVALID, "no wide BVH on the device");
+	CK(cudaSetDevice(c->device));
+	if (counts) { counts[0] = c->num_nodes; counts[1] = c->num_prims; counts[2] = c->bvh_depth; counts[3] = c->build_rounds; }
+	if (nodes80) CK(cudaMemcpyAsync(nodes80, c->d_nodes, (size_t)c->num_nodes * sizeof(Node8), cudaMemcpyDeviceToHost, c->stream));
+	if (tris48) CK(cudaMemcpyAsync(tris48, c->d_prims, (size_t)c->num_prims * sizeof(Prim48), cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	return CUPT_OK;
+}
+
+int cupt_get_build_times(cupt_context* c, float* ms4)
+{
+	if (!c || !ms4) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	for (int i = 0; i < 4; ++i) ms4[i] = c->build_ms[i];
 	return CUPT_OK;
 }
 

@@ -139,6 +139,15 @@ int cupt_set_stream(cupt_context* c, void* cuda_stream);          /* default: a 
 int cupt_set_scene(cupt_context* c, const cupt_scene* s);         /* kernel.cu:664-684 */
 int cupt_set_bvh(cupt_context* c, const cupt_bvh* b);             /* kernel.cu:686-691 (wide layout) */
 int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int depth); /* kernel.cu:686-691 verbatim */
+/* GPU-side construction of the wide BVH from the scene cupt_set_scene uploaded: replaces buildBVH (BVH.h:133-474)
+ * AND the upload (kernel.cu:686-691) in one call; Morton sort + parallel locally-ordered clustering + 8-wide collapse
+ * on the device (csrc/bvh_device.cu).  opts: max_leaf_tris and tie_rank are honoured (sah_bins, threads: host builder
+ * only); info may be NULL.  The tree differs from cupt_bvh_build's, the hits do not. */
+int cupt_build_bvh_device(cupt_context* c, const cupt_bvh_opts* opts, cupt_bvh_info* info);
+/* copy the device's wide BVH back (tests: structural invariants); counts = {nodes, records, depth, PLOC rounds}; any pointer may be NULL */
+int cupt_read_bvh(cupt_context* c, void* nodes80, void* tris48, int64_t* counts);
+/* CUDA-event times of the last cupt_build_bvh_device in ms: {total, boxes+Morton+sort, clustering, collapse+emit} */
+int cupt_get_build_times(cupt_context* c, float* ms4);
 int cupt_set_camera(cupt_context* c, const cupt_camera* cam);     /* kernel.cu:642-651 */
 
 enum { CUPT_INTEGRATOR_PT = 2 /* radianceAlongSingleStep2, kernel.cu:417-515 */,

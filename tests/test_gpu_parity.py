@@ -346,3 +346,78 @@ def test_bdpt_sample_ranges_compose_and_reject_spheres(ctx, get_case):
     with pytest.raises(api.CuptError):
         ctx.render(0, 1)
     ctx.set_options(integrator=api.INTEGRATOR_PT)
+
+
+def _random_rays(c, n, seed):
+    rng = np.random.default_rng(seed)
+    pos = c.verts.view(np.float32).reshape(-1, 3)
+    o = rng.uniform(pos.min(0), pos.max(0), size=(n, 3)); d = rng.normal(size=(n, 3))
+    return np.concatenate([o, d / np.linalg.norm(d, axis=1, keepdims=True)], axis=1).astype(np.float32)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_device_bvh_build(ctx, get_case, name):
+    """cupt_build_bvh_device (Morton sort + PLOC + 8-wide collapse on the GPU): the image it leaves in HBM satisfies the
+    same structural invariants as the host builder's, builds are deterministic, and every hit — hence the radiance
+    image — is bit-identical to the one traced through the host-built tree and to the oracle's brute force."""
+    from bvhcheck import check_wide_bvh
+    c = get_case(name)
+    load(ctx, c, api.TRAVERSAL_WIDE, max_depth=5, seed=1234)
+    host_hits = ctx.primary_hits()
+    rays = _random_rays(c, 30000, 41)
+    host_inco = ctx.trace_rays(rays)
+    ctx.reset_accum(); ctx.render(0, 3); host_img = ctx.read_accum(False)
+    for max_leaf in (1, 3):
+        info = ctx.build_bvh_device(max_leaf_tris=max_leaf, tie_rank=c.rank)
+        nodes, prims, depth, rounds = ctx.read_bvh()
+        assert depth == info["depth"] and len(nodes) == info["num_nodes"] and rounds >= 1
+        check_wide_bvh(c, nodes, prims, info, max_leaf)
+        ctx.build_bvh_device(max_leaf_tris=max_leaf, tie_rank=c.rank)
+        n2, p2, _, _ = ctx.read_bvh()
+        assert nodes.tobytes() == n2.tobytes() and prims.tobytes() == p2.tobytes()      # deterministic
+        assert hits_equal(ctx.primary_hits(), host_hits)
+        assert hits_equal(ctx.trace_rays(rays), host_inco)
+    bi, bt = c.osc.brute_force(rays, c.rank)
+    assert hits_equal(host_inco, (bi, bt))
+    ctx.reset_accum(); ctx.render(0, 3)
+    assert ctx.read_accum(False).tobytes() == host_img.tobytes()
+    # the strict mode works on top of the device-built tree as well (set_bvh2 was done by load())
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE_STRICT)
+    assert hits_equal(ctx.primary_hits(), c.osc.primary_hits(c.cam))
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE)
+
+
+def test_device_bvh_build_degenerate_inputs(ctx, get_case):
+    """one triangle, two triangles, 3000 copies of the same triangle (all Morton codes and all boxes equal: the
+    clustering must still halve every round, and the lowest rank wins every tie), spheres mixed with triangles"""
+    c = get_case("cornell")
+    pos = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1], [1, 0, 1], [0, 1, 1]], np.float32)
+    mats = c.mats[:1]
+    for ntri in (1, 2, 3000):
+        tris = np.zeros(ntri, dtype=c.tris.dtype)
+        tris["v0"], tris["v1"], tris["v2"] = 0, 1, 2
+        if ntri == 2:
+            tris["v0"][1], tris["v1"][1], tris["v2"][1] = 3, 4, 5
+        tris["norm"] = (0, 0, 1)
+        s = api.SceneHandle()
+        s.set_arrays(pos.view(c.verts.dtype).reshape(-1), tris, mats, np.zeros(0, np.int32), 0.0)
+        ctx.set_scene(s)
+        info = ctx.build_bvh_device()
+        nodes, prims, depth, rounds = ctx.read_bvh()
+        assert len(prims) == ntri and sorted(prims["id"].tolist()) == list(range(ntri))
+        assert rounds <= 2 * int(np.ceil(np.log2(max(ntri, 2)))) + 2, rounds
+        ctx.set_options(traversal=api.TRAVERSAL_WIDE)
+        ray = np.array([[0.2, 0.2, 5, 0, 0, -1], [0.2, 0.2, -5, 0, 0, 1], [5, 5, 5, 0, 0, -1]], np.float32)
+        ids, ts = ctx.trace_rays(ray)
+        assert ids[2] == -1
+        if ntri == 2:
+            assert ids[0] == 1 and ts[0] == np.float32(4.0) and ids[1] == 0 and ts[1] == np.float32(5.0)
+        else:
+            assert ids[0] == 0 and ids[1] == 0 and ts[0] == np.float32(5.0)           # every copy ties: rank = index, lowest wins
+    s = get_case("cornell_spheres")
+    ctx.set_scene(s.handle); ctx.set_camera(s.cam)
+    ctx.set_bvh(s.handle.build_bvh(tie_rank=s.rank))
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE)
+    want = ctx.primary_hits()
+    info = ctx.build_bvh_device(tie_rank=s.rank)
+    assert info["num_spheres"] == len(s.spheres) and hits_equal(ctx.primary_hits(), want)
