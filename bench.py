@@ -188,6 +188,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--traversal", default="wide", choices=["wide", "strict", "ref"], help="wide (default), strict = wide + reference-equality check, ref = the reference algorithm on its own BVH2")
     ap.add_argument("--integrator", default="pt", choices=["pt", "bdpt"], help="pt = radianceAlongSingleStep2 with max depth 5 (the metric's config); bdpt = the reference's live radianceAlongSingleStep (what the legacy kernel.cu runs)")
+    ap.add_argument("--bvh", default="host", choices=["host", "device"], help="host = binned-SAH builder (OpenMP), uploaded; device = cupt_build_bvh_device, rebuilt inside every e2e step")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -218,6 +219,12 @@ def main():
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
     ctx.set_scene(s); ctx.set_bvh(bvh); ctx.set_camera(cam)
+    dev_rank = None if n2 is None else api.bvh2_leaf_order(n2, s.counts()[1])
+    dev_info = None
+    if args.bvh == "device":
+        ctx.build_bvh_device(tie_rank=dev_rank)
+        dev_info = ctx.build_bvh_device(tie_rank=dev_rank)
+        info = dict(info, num_nodes=dev_info["num_nodes"], depth=dev_info["depth"])
     if n2 is not None:
         ctx.set_bvh2(n2, d2)
     ctx.set_options(max_depth=DEPTH, seed=SEED, traversal=mode, time_stages=1, collect_stats=0,
@@ -277,11 +284,17 @@ def main():
     # e2e through the C-ABI with host buffers (scene + BVH H2D, render, image D2H), same step
     host_img = np.empty((W * H, 3), dtype=np.float32)
     nv, nt, nm, nl, _ = s.counts()
-    h2d = nv * 12 + nt * 28 + nt * 16 + nm * 32 + (nl + 1) * 48 + info["num_nodes"] * 80 + info["num_tri_records"] * 48 + 32
+    h2d = nv * 12 + nt * 28 + nt * 16 + nm * 32 + (nl + 1) * 48 + 32
+    if args.bvh == "host":
+        h2d += info["num_nodes"] * 80 + info["num_tri_records"] * 48      # the device builder uploads no tree
     d2h = W * H * 12
 
     def e2e_step():
-        ctx.set_scene(s); ctx.set_bvh(bvh); ctx.set_camera(cam)
+        ctx.set_scene(s); ctx.set_camera(cam)
+        if args.bvh == "device":
+            ctx.build_bvh_device(tie_rank=dev_rank)      # the build itself is inside the e2e step
+        else:
+            ctx.set_bvh(bvh)
         if n2 is not None:
             ctx.set_bvh2(n2, d2)
         ctx.reset_accum(); ctx.render(first, SPP)
@@ -316,7 +329,8 @@ def main():
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "traversal": args.traversal, "integrator": args.integrator, "parallelism": f"sample ranges x{world}, replicated BVH, NCCL reduce of f32 accumulators",
                        "l2": "L2 flushed (256 MiB write) between timed steps; per-step path state (64 Mi paths x 72 B = 4.8 GB) exceeds the 126 MB L2, the 16 MB BVH is L2-resident within a step by design",
-                       "bvh": {"nodes": info["num_nodes"], "prims": info["num_tri_records"], "depth": info["depth"], "build_s_host": build_s}},
+                       "bvh": {"builder": args.bvh, "nodes": info["num_nodes"], "prims": info["num_tri_records"], "depth": info["depth"], "build_s_host": build_s,
+                               "build_ms_device": None if dev_info is None else {k: v for k, v in dev_info.items() if k.startswith("ms_")}}},
             "msamples_per_s": W * H * SPP * world * args.steps / (ms_total * 1e-3) / 1e6,
             "rays_per_step_per_gpu": rays_step, "rays_per_sample": rays_step / (W * H * SPP),
             "clocks": clocks,

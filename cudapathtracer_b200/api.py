@@ -37,7 +37,7 @@ class CuptError(RuntimeError):
 
 
 class BvhOpts(C.Structure):
-    _fields_ = [("sah_bins", C.c_int), ("max_leaf_tris", C.c_int), ("threads", C.c_int), ("tie_rank", C.c_void_p)]
+    _fields_ = [("sah_bins", C.c_int), ("max_leaf_tris", C.c_int), ("threads", C.c_int), ("tie_rank", C.c_void_p), ("ploc_radius", C.c_int)]
 
 
 class BvhInfo(C.Structure):
@@ -283,10 +283,10 @@ class Context:
     def set_bvh(self, bvh: BvhHandle):
         _check(self.lib.cupt_set_bvh(self.h, bvh.h))
 
-    def build_bvh_device(self, max_leaf_tris=0, tie_rank: Optional[np.ndarray] = None) -> dict:
+    def build_bvh_device(self, max_leaf_tris=0, tie_rank: Optional[np.ndarray] = None, radius=0) -> dict:
         """cupt_build_bvh_device: wide BVH built on the GPU from the uploaded scene (replaces buildBVH + its upload)"""
         rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, dtype=np.uint32)
-        opts = BvhOpts(0, max_leaf_tris, 0, None if rank is None else rank.ctypes.data)
+        opts = BvhOpts(0, max_leaf_tris, 0, None if rank is None else rank.ctypes.data, radius)
         i = BvhInfo()
         _check(self.lib.cupt_build_bvh_device(self.h, C.byref(opts), C.byref(i)))
         d = {n: getattr(i, n) for n, _ in BvhInfo._fields_}
@@ -294,6 +294,9 @@ class Context:
         _check(self.lib.cupt_get_build_times(self.h, ms))
         d.update(ms_total=ms[0], ms_sort=ms[1], ms_cluster=ms[2], ms_collapse=ms[3])
         return d
+
+    def release_workspace(self):
+        _check(self.lib.cupt_release_workspace(self.h))
 
     def read_bvh(self):
         """(nodes, prims, depth, clustering rounds) of the wide BVH currently on the device"""

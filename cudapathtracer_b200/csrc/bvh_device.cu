@@ -6,7 +6,8 @@
 //   2. k_morton         63-bit Morton code of the centroid, radix sort of (code, primitive)      [cub::DeviceRadixSort]
 //   3. PLOC rounds      parallel locally-ordered clustering (Meister & Bittner, "Parallel Locally-Ordered Clustering
 //                       for Bounding Volume Hierarchy Construction", TVCG 2018): every cluster finds the neighbour
-//                       within +-R positions of the Morton order whose union box has the smallest area; mutual pairs
+//                       within +-R positions of the Morton order (R = 4 by default: measured best on config 2, DESIGN.md
+//                       §4) whose union box has the smallest area; mutual pairs
 //                       merge; an order-preserving compaction closes the gaps.  Four launches per round
 //                       (k_ploc_nearest, k_ploc_count, k_scan_tiles, k_ploc_merge), ~log_1.5(N) rounds.
 //   4. collapse + emit  level by level from the root: open the child with the largest area until there are eight
@@ -27,17 +28,7 @@
 namespace cupt {
 namespace devbuild {
 
-#define CKB(call)                                                                                          \
-	do {                                                                                                   \
-		cudaError_t e_ = (call);                                                                           \
-		if (e_ != cudaSuccess) {                                                                           \
-			ws.release();                                                                                  \
-			return set_error(CUPT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
-		}                                                                                                  \
-	} while (0)
-
 constexpr int kTile = 256;        // threads per block = elements per scan tile
-constexpr int kRadius = 8;        // PLOC search radius
 
 // binary node: leaves are 0..N-1 in Morton order (left = -1 - primitive), inner nodes N..2N-2
 struct alignas(16) N2 {
@@ -180,6 +171,7 @@ __global__ void __launch_bounds__(kTile) k_scan_tiles(uint64_t* __restrict__ til
 // Nearest neighbour of cluster i among positions i-R..i+R by the half-area of the union box.  Ties are broken by a
 // strict total order on UNORDERED pairs — (area, |i-j|, min(i,j) odd, min(i,j)) — so the globally smallest pair is
 // always mutual (progress every round) and a run of identical boxes pairs up as (0,1)(2,3)... instead of chaining.
+template <int kRadius>
 __global__ void __launch_bounds__(kTile) k_ploc_nearest(const N2* __restrict__ nodes, const uint32_t* __restrict__ cid, const int n, uint32_t* __restrict__ nn)
 {
 	__shared__ float s_box[6][kTile + 2 * kRadius];
@@ -463,53 +455,86 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 	atomicAdd(A.sah, sah);
 }
 
-struct Workspace {
-	std::vector<void*> ptrs;
-	template <class T>
-	cudaError_t alloc(T** p, size_t n)
-	{
-		const cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T));
-		if (e == cudaSuccess) ptrs.push_back((void*)*p);
-		return e;
-	}
-	void drop(void* p)
-	{
-		for (size_t i = 0; i < ptrs.size(); ++i)
-			if (ptrs[i] == p) { cudaFree(p); ptrs.erase(ptrs.begin() + (long)i); return; }
-	}
-	void forget(void* p)   // ownership leaves the workspace
-	{
-		for (size_t i = 0; i < ptrs.size(); ++i)
-			if (ptrs[i] == p) { ptrs.erase(ptrs.begin() + (long)i); return; }
-	}
-	void release()
-	{
-		for (void* p : ptrs) cudaFree(p);
-		ptrs.clear();
-	}
-};
-
 }  // namespace devbuild
 
 using namespace devbuild;
 
-int build_wide_bvh_device(cudaStream_t st, const float* verts, const cupt_triangle* tris, int64_t nt, const float4* spheres, int64_t ns,
-                          const uint32_t* rank, int max_leaf, DeviceBvh* out)
+// ---- workspace arena: one allocation that only grows, kept by the context between builds --------------------------
+// (cudaMalloc / cudaFree per build cost more than the build itself and cudaFree synchronises the device)
+int BuildArena::reserve(size_t bytes)
+{
+	if (!h_total) {
+		if (cudaMallocHost((void**)&h_total, sizeof(uint64_t)) != cudaSuccess) return set_error(CUPT_ERR_CUDA, "cudaMallocHost failed");
+		for (auto& e : ev)
+			if (cudaEventCreate(&e) != cudaSuccess) return set_error(CUPT_ERR_CUDA, "cudaEventCreate failed");
+	}
+	off = 0;
+	if (bytes <= cap) return CUPT_OK;
+	if (base) { cudaFree(base); base = nullptr; cap = 0; }
+	const cudaError_t e = cudaMalloc(&base, bytes);
+	if (e != cudaSuccess) return set_error(CUPT_ERR_NOMEM, "BVH build workspace of %zu bytes: %s", bytes, cudaGetErrorString(e));
+	cap = bytes;
+	return CUPT_OK;
+}
+
+void BuildArena::destroy()
+{
+	if (base) cudaFree(base);
+	if (h_total) { cudaFreeHost(h_total); for (auto& e : ev) cudaEventDestroy(e); }
+	base = nullptr; h_total = nullptr; cap = off = 0;
+}
+
+namespace {
+inline size_t up256(size_t x) { return (x + 255) & ~(size_t)255; }
+template <class T>
+T* take(BuildArena& a, size_t n)
+{
+	T* p = reinterpret_cast<T*>(static_cast<char*>(a.base) + a.off);
+	a.off += up256(std::max<size_t>(n, 1) * sizeof(T));
+	return p;
+}
+}  // namespace
+
+#define CKB(call)                                                                                          \
+	do {                                                                                                   \
+		cudaError_t e_ = (call);                                                                           \
+		if (e_ != cudaSuccess)                                                                             \
+			return set_error(CUPT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+	} while (0)
+
+int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts, const cupt_triangle* tris, int64_t nt, const float4* spheres, int64_t ns,
+                          const uint32_t* rank, int max_leaf, int radius, DeviceBvh* out)
 {
 	const int64_t N = nt + ns;
 	if (N < 1) return set_error(CUPT_ERR_INVALID, "scene has no primitives");
 	if (N > (1ll << 27)) return set_error(CUPT_ERR_LIMIT, "more than 2^27 primitives");
 	max_leaf = std::max(1, std::min(3, max_leaf));
-	Workspace ws;
-	cudaEvent_t ev[5];
-	for (auto& e : ev) CKB(cudaEventCreate(&e));
 	const int tilesN = (int)((N + kTile - 1) / kTile);
+	const size_t n = (size_t)N;
+
+	size_t temp_bytes = 0;
+	{
+		cub::DoubleBuffer<uint64_t> dk(nullptr, nullptr);
+		cub::DoubleBuffer<uint32_t> dv(nullptr, nullptr);
+		CKB(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, dk, dv, (int)N, 0, 63, st));
+	}
+	// everything the build touches except its two outputs, in one arena; the sort buffers are dead once the sorted
+	// leaves are written, the collapse reuses the cluster arrays for its level queues
+	const size_t need = up256(n * sizeof(N2)) + up256(64) + 2 * up256(n * 8) + 2 * up256(n * 4) + up256(temp_bytes + 256)
+	                    + up256(2 * n * sizeof(N2)) + up256(2 * n * 4) + 3 * up256(n * 4) + up256(((size_t)tilesN + 1) * 8) + up256(64)
+	                    + up256((n / 2 + 2) * 8) + up256(64) + 4096;
+	int rc;
+	if ((rc = arena.reserve(need))) return rc;
+	cudaEvent_t* ev = arena.ev;
+	uint64_t* h_total = arena.h_total;
 
 	// 1-2: boxes, Morton codes, sort
-	N2* leaf = nullptr; uint32_t* cbounds = nullptr;
-	uint64_t* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
-	CKB(ws.alloc(&leaf, (size_t)N)); CKB(ws.alloc(&cbounds, 6));
-	for (int b = 0; b < 2; ++b) { CKB(ws.alloc(&keys[b], (size_t)N)); CKB(ws.alloc(&vals[b], (size_t)N)); }
+	N2* leaf = take<N2>(arena, n);
+	uint32_t* cbounds = take<uint32_t>(arena, 6);
+	uint64_t* keys[2]; uint32_t* vals[2];
+	for (int b = 0; b < 2; ++b) keys[b] = take<uint64_t>(arena, n);
+	for (int b = 0; b < 2; ++b) vals[b] = take<uint32_t>(arena, n);
+	uint8_t* temp = take<uint8_t>(arena, temp_bytes + 256);
 	static const uint32_t cb_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
 	CKB(cudaEventRecord(ev[0], st));
 	CKB(cudaMemcpyAsync(cbounds, cb_init, sizeof(cb_init), cudaMemcpyHostToDevice, st));
@@ -517,66 +542,77 @@ int build_wide_bvh_device(cudaStream_t st, const float* verts, const cupt_triang
 	k_morton<<<tilesN, kTile, 0, st>>>(leaf, N, cbounds, keys[0], vals[0]);
 	cub::DoubleBuffer<uint64_t> dk(keys[0], keys[1]);
 	cub::DoubleBuffer<uint32_t> dv(vals[0], vals[1]);
-	size_t temp_bytes = 0;
-	CKB(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, dk, dv, (int)N, 0, 63, st));
-	uint8_t* temp = nullptr;
-	CKB(ws.alloc(&temp, temp_bytes));
 	CKB(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, dk, dv, (int)N, 0, 63, st));
 	CKB(cudaEventRecord(ev[1], st));
 
 	// 3: PLOC
-	N2* nodes = nullptr; uint32_t* cnt = nullptr; uint32_t* cid[2] = {nullptr, nullptr}; uint32_t* nn = nullptr;
-	uint64_t* tile_sums = nullptr; uint64_t* d_total = nullptr; uint64_t* h_total = nullptr;
-	CKB(ws.alloc(&nodes, (size_t)2 * N)); CKB(ws.alloc(&cnt, (size_t)2 * N));
-	CKB(ws.alloc(&cid[0], (size_t)N)); CKB(ws.alloc(&cid[1], (size_t)N)); CKB(ws.alloc(&nn, (size_t)N));
-	CKB(ws.alloc(&tile_sums, (size_t)tilesN + 1)); CKB(ws.alloc(&d_total, 1));
-	CKB(cudaMallocHost((void**)&h_total, sizeof(uint64_t)));
-	struct HostGuard { uint64_t* p; ~HostGuard() { cudaFreeHost(p); } } host_guard{h_total};
+	N2* nodes = take<N2>(arena, 2 * n);
+	uint32_t* cnt = take<uint32_t>(arena, 2 * n);
+	uint32_t* cid[2] = {take<uint32_t>(arena, n), take<uint32_t>(arena, n)};
+	uint32_t* nn = take<uint32_t>(arena, n);
+	uint64_t* tile_sums = take<uint64_t>(arena, (size_t)tilesN + 1);
+	uint64_t* d_total = take<uint64_t>(arena, 1);
+	uint64_t* item_counts = take<uint64_t>(arena, n / 2 + 2);
+	double* d_sah = take<double>(arena, 1);
+	if (arena.off > arena.cap) return set_error(CUPT_ERR_CUDA, "internal: BVH build workspace undersized (%zu > %zu)", arena.off, arena.cap);
 	k_sorted_leaves<<<tilesN, kTile, 0, st>>>(leaf, dv.Current(), N, nodes, cnt, cid[0]);
-	CKB(cudaStreamSynchronize(st));
-	ws.drop(leaf); ws.drop(keys[0]); ws.drop(keys[1]); ws.drop(vals[0]); ws.drop(vals[1]); ws.drop(temp);
-	int n = (int)N, cur = 0, rounds = 0;
+	int cn = (int)N, cur = 0, rounds = 0;
 	uint32_t node_base = (uint32_t)N;
-	while (n > 1) {
-		const int tiles = (n + kTile - 1) / kTile;
-		k_ploc_nearest<<<tiles, kTile, 0, st>>>(nodes, cid[cur], n, nn);
-		k_ploc_count<<<tiles, kTile, 0, st>>>(nn, n, tile_sums);
+	while (cn > 1) {
+		const int tiles = (cn + kTile - 1) / kTile;
+		switch (radius) {
+		case 32: k_ploc_nearest<32><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
+		case 16: k_ploc_nearest<16><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
+		case 8: k_ploc_nearest<8><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
+		case 2: k_ploc_nearest<2><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
+		case 1: k_ploc_nearest<1><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
+		default: k_ploc_nearest<4><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
+		}
+		k_ploc_count<<<tiles, kTile, 0, st>>>(nn, cn, tile_sums);
 		k_scan_tiles<<<1, kTile, 0, st>>>(tile_sums, tiles, d_total);
-		k_ploc_merge<<<tiles, kTile, 0, st>>>(nodes, cnt, cid[cur], cid[cur ^ 1], nn, n, tile_sums, node_base);
+		k_ploc_merge<<<tiles, kTile, 0, st>>>(nodes, cnt, cid[cur], cid[cur ^ 1], nn, cn, tile_sums, node_base);
 		CKB(cudaMemcpyAsync(h_total, d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
 		CKB(cudaStreamSynchronize(st));
 		const uint32_t valid = (uint32_t)*h_total, leaders = (uint32_t)(*h_total >> 32);
-		if (leaders == 0 || (int)valid + (int)leaders != n) { ws.release(); return set_error(CUPT_ERR_CUDA, "internal: PLOC round made no progress (n %d, valid %u, merged %u)", n, valid, leaders); }
-		n = (int)valid; node_base += leaders; cur ^= 1; ++rounds;
+		if (leaders == 0 || (int)valid + (int)leaders != cn)
+			return set_error(CUPT_ERR_CUDA, "internal: PLOC round made no progress (n %d, valid %u, merged %u)", cn, valid, leaders);
+		cn = (int)valid; node_base += leaders; cur ^= 1; ++rounds;
 	}
 	CKB(cudaEventRecord(ev[2], st));
 	const int32_t root = N == 1 ? 0 : (int32_t)node_base - 1;
 
-	// 4: collapse + emit, level by level
+	// 4: collapse + emit, level by level, into the caller's buffers (reused when large enough)
 	N2 root_box;
 	CKB(cudaMemcpyAsync(&root_box, nodes + root, sizeof(N2), cudaMemcpyDeviceToHost, st));
 	CKB(cudaStreamSynchronize(st));
 	const double rdx = (double)root_box.hi[0] - root_box.lo[0], rdy = (double)root_box.hi[1] - root_box.lo[1], rdz = (double)root_box.hi[2] - root_box.lo[2];
 	const double root_area = std::max(2.0 * (rdx * rdy + rdx * rdz + rdy * rdz), 1e-300);
 	int32_t* items[2] = {reinterpret_cast<int32_t*>(cid[0]), reinterpret_cast<int32_t*>(cid[1])};
-	uint64_t* item_counts = nullptr; double* d_sah = nullptr;
-	CKB(ws.alloc(&item_counts, (size_t)N / 2 + 2)); CKB(ws.alloc(&d_sah, 1));
 	CKB(cudaMemsetAsync(d_sah, 0, sizeof(double), st));
-	Node8* out_nodes = nullptr; float4* out_prims = nullptr;
-	size_t node_cap = (size_t)N / 3 + 1024;
-	CKB(ws.alloc(&out_nodes, node_cap)); CKB(ws.alloc(&out_prims, (size_t)N * 3));
+	if (out->prims_capacity_bytes < n * 48) {
+		if (out->prims) { CKB(cudaFree(out->prims)); out->prims = nullptr; out->prims_capacity_bytes = 0; }
+		CKB(cudaMalloc(&out->prims, n * 48));
+		out->prims_capacity_bytes = n * 48;
+	}
+	if (out->nodes_capacity_bytes < (n / 3 + 1024) * sizeof(Node8)) {
+		if (out->nodes) { CKB(cudaFree(out->nodes)); out->nodes = nullptr; out->nodes_capacity_bytes = 0; }
+		CKB(cudaMalloc(&out->nodes, (n / 3 + 1024) * sizeof(Node8)));
+		out->nodes_capacity_bytes = (n / 3 + 1024) * sizeof(Node8);
+	}
 	CKB(cudaMemcpyAsync(items[0], &root, sizeof(int32_t), cudaMemcpyHostToDevice, st));
 	int n_items = 1, lvl = 0, depth = 0;
 	uint32_t level_base = 0, prim_base = 0;
 	while (n_items > 0) {
 		++depth;
-		if ((size_t)level_base + (size_t)n_items > node_cap) {   // rare: grow the node array
-			const size_t ncap = std::max(node_cap * 2, (size_t)level_base + (size_t)n_items);
-			Node8* bigger = nullptr;
-			CKB(ws.alloc(&bigger, ncap));
-			CKB(cudaMemcpyAsync(bigger, out_nodes, (size_t)level_base * sizeof(Node8), cudaMemcpyDeviceToDevice, st));
+		const size_t want = ((size_t)level_base + (size_t)n_items) * sizeof(Node8);
+		if (want > out->nodes_capacity_bytes) {   // rare (the first guess is N/3 nodes): grow the node array
+			const size_t ncap = std::max(out->nodes_capacity_bytes * 2, want);
+			void* bigger = nullptr;
+			CKB(cudaMalloc(&bigger, ncap));
+			CKB(cudaMemcpyAsync(bigger, out->nodes, (size_t)level_base * sizeof(Node8), cudaMemcpyDeviceToDevice, st));
 			CKB(cudaStreamSynchronize(st));
-			ws.drop(out_nodes); out_nodes = bigger; node_cap = ncap;
+			CKB(cudaFree(out->nodes));
+			out->nodes = bigger; out->nodes_capacity_bytes = ncap;
 		}
 		const int tiles = (n_items + kTile - 1) / kTile;
 		k_collapse_count<<<tiles, kTile, 0, st>>>(nodes, cnt, items[lvl], n_items, (uint32_t)max_leaf, item_counts, tile_sums);
@@ -585,7 +621,7 @@ int build_wide_bvh_device(cudaStream_t st, const float* verts, const cupt_triang
 		A.nodes = nodes; A.cnt = cnt; A.items = items[lvl]; A.n_items = n_items; A.max_leaf = (uint32_t)max_leaf;
 		A.item_counts = item_counts; A.tile_offs = tile_sums;
 		A.level_base = level_base; A.next_base = level_base + (uint32_t)n_items; A.prim_base = prim_base;
-		A.next_items = items[lvl ^ 1]; A.out_nodes = out_nodes; A.out_prims = out_prims;
+		A.next_items = items[lvl ^ 1]; A.out_nodes = static_cast<Node8*>(out->nodes); A.out_prims = static_cast<float4*>(out->prims);
 		A.verts = verts; A.tris = tris; A.spheres = spheres; A.rank = rank; A.nt = nt;
 		A.inv_root_area = 1.0 / root_area; A.sah = d_sah;
 		k_collapse_emit<<<tiles, kTile, 0, st>>>(A);
@@ -595,25 +631,20 @@ int build_wide_bvh_device(cudaStream_t st, const float* verts, const cupt_triang
 		prim_base += (uint32_t)(*h_total >> 32);
 		n_items = (int)(uint32_t)*h_total;
 		lvl ^= 1;
-		if (depth > 255) { ws.release(); return set_error(CUPT_ERR_LIMIT, "wide BVH deeper than 255 levels"); }
+		if (depth > 255) return set_error(CUPT_ERR_LIMIT, "wide BVH deeper than 255 levels");
 	}
 	CKB(cudaEventRecord(ev[3], st));
 	double sah = 0;
 	CKB(cudaMemcpyAsync(&sah, d_sah, sizeof(double), cudaMemcpyDeviceToHost, st));
 	CKB(cudaStreamSynchronize(st));
 	CKB(cudaGetLastError());
-	if ((int64_t)prim_base != N) { ws.release(); return set_error(CUPT_ERR_CUDA, "internal: emitted %u primitive records for %lld primitives", prim_base, (long long)N); }
-	out->nodes = out_nodes; out->prims = out_prims;
+	if ((int64_t)prim_base != N) return set_error(CUPT_ERR_CUDA, "internal: emitted %u primitive records for %lld primitives", prim_base, (long long)N);
 	out->num_nodes = level_base; out->num_prims = N;
-	out->nodes_capacity_bytes = node_cap * sizeof(Node8); out->prims_capacity_bytes = (size_t)N * 48;
 	out->depth = depth; out->ploc_rounds = rounds; out->sah_cost = sah;
 	cudaEventElapsedTime(&out->ms_sort, ev[0], ev[1]);
 	cudaEventElapsedTime(&out->ms_ploc, ev[1], ev[2]);
 	cudaEventElapsedTime(&out->ms_collapse, ev[2], ev[3]);
 	cudaEventElapsedTime(&out->ms_total, ev[0], ev[3]);
-	for (auto& e : ev) cudaEventDestroy(e);
-	ws.forget(out_nodes); ws.forget(out_prims);
-	ws.release();
 	return CUPT_OK;
 }
 

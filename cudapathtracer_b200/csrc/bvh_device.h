@@ -6,11 +6,23 @@
 
 namespace cupt {
 
+// workspace kept by the context between builds: one device allocation that only grows, a pinned word, four events
+struct BuildArena {
+	void* base = nullptr;
+	size_t cap = 0, off = 0;
+	uint64_t* h_total = nullptr;
+	cudaEvent_t ev[4] = {};
+	int reserve(size_t bytes);
+	void destroy();
+};
+
 struct DeviceBvh {
-	void* nodes = nullptr;      // Node8[num_nodes]   (cudaMalloc; ownership passes to the caller)
+	// in/out: the caller's buffers (cudaMalloc) and their capacities; reused when large enough, else replaced
+	void* nodes = nullptr;      // Node8[num_nodes]
 	void* prims = nullptr;      // Prim48[num_prims]
-	int64_t num_nodes = 0, num_prims = 0;
 	size_t nodes_capacity_bytes = 0, prims_capacity_bytes = 0;
+	// out
+	int64_t num_nodes = 0, num_prims = 0;
 	int depth = 0, ploc_rounds = 0;
 	double sah_cost = 0;
 	float ms_total = 0, ms_sort = 0, ms_ploc = 0, ms_collapse = 0;   // CUDA events on the build stream
@@ -18,7 +30,8 @@ struct DeviceBvh {
 
 // verts/tris/spheres: the device arrays of the uploaded scene (spheres: SphereShade records, centre + radius first);
 // rank: optional device array of tie-break ranks per triangle (NULL = triangle index)
-int build_wide_bvh_device(cudaStream_t stream, const float* verts, const cupt_triangle* tris, int64_t num_tris,
-                          const float4* spheres, int64_t num_spheres, const uint32_t* rank, int max_leaf, DeviceBvh* out);
+int build_wide_bvh_device(cudaStream_t stream, BuildArena& arena, const float* verts, const cupt_triangle* tris, int64_t num_tris,
+                          const float4* spheres, int64_t num_spheres, const uint32_t* rank, int max_leaf,
+                          int radius /* 1, 2, 4 (default), 8, 16, 32 */, DeviceBvh* out);
 
 }  // namespace cupt

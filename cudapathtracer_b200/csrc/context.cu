@@ -49,6 +49,7 @@ struct cupt_context {
 	std::vector<StageEvent> pending, pool;
 	std::map<void**, size_t> capacity;   // bytes behind each uploaded device pointer (upload())
 	int extend_blocks[2] = {0, 0};
+	BuildArena arena; uint32_t* d_build_rank = nullptr;
 	float build_ms[4] = {0, 0, 0, 0}; int build_rounds = 0;   // last cupt_build_bvh_device: total, sort, PLOC, collapse
 };
 
@@ -156,7 +157,7 @@ int check_ready(const cupt_context* c, bool need_shading, bool need_cam = true)
 {
 	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
 	if (need_cam && !c->have_cam) return set_error(CUPT_ERR_INVALID, "no camera set (cupt_set_camera)");
-	if (c->opts.traversal != CUPT_TRAVERSAL_REF_BVH2 && !c->d_nodes) return set_error(CUPT_ERR_INVALID, "no wide BVH set (cupt_set_bvh)");
+	if (c->opts.traversal != CUPT_TRAVERSAL_REF_BVH2 && (!c->d_nodes || c->num_nodes == 0)) return set_error(CUPT_ERR_INVALID, "no wide BVH set (cupt_set_bvh)");
 	if (c->opts.traversal != CUPT_TRAVERSAL_WIDE && (!c->d_bvh2 || !c->d_tris)) return set_error(CUPT_ERR_INVALID, "no reference BVH2 / scene set");
 	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE_STRICT && (c->num_spheres > 0 || c->bvh2_leaves != c->num_tris))
 		return set_error(CUPT_ERR_INVALID, "strict mode needs a sphere-free scene and the reference BVH2 of the same scene");
@@ -246,7 +247,7 @@ void cupt_destroy(cupt_context* c)
 	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2); cudaFree(c->d_bvh2_up); cudaFree(c->d_bvh2_leaf_parent);
 	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
 	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats);
-	cudaFree(c->d_accum);
+	cudaFree(c->d_accum); cudaFree(c->d_build_rank); c->arena.destroy();
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;
 }
@@ -374,17 +375,18 @@ int cupt_build_bvh_device(cupt_context* c, const cupt_bvh_opts* opts, cupt_bvh_i
 	CK(cudaSetDevice(c->device));
 	uint32_t* d_rank = nullptr;
 	if (opts && opts->tie_rank && c->num_tris > 0) {
-		CK(cudaMalloc((void**)&d_rank, (size_t)c->num_tris * sizeof(uint32_t)));
-		CK(cudaMemcpyAsync(d_rank, opts->tie_rank, (size_t)c->num_tris * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+		int rcu;
+		if ((rcu = upload(c, &c->d_build_rank, opts->tie_rank, (size_t)c->num_tris * sizeof(uint32_t)))) return rcu;
+		d_rank = c->d_build_rank;
 	}
 	DeviceBvh r;
-	const int rc = build_wide_bvh_device(c->stream, c->d_verts, c->d_tris, c->num_tris, c->d_spheres, c->num_spheres, d_rank,
-	                                     (opts && opts->max_leaf_tris >= 1) ? opts->max_leaf_tris : 3, &r);
-	cudaFree(d_rank);
-	if (rc) return rc;
-	cudaFree(c->d_nodes); cudaFree(c->d_prims);
-	c->d_nodes = (uint4*)r.nodes; c->d_prims = (float4*)r.prims;
+	r.nodes = c->d_nodes; r.prims = c->d_prims;
+	r.nodes_capacity_bytes = c->d_nodes ? c->capacity[(void**)&c->d_nodes] : 0; r.prims_capacity_bytes = c->d_prims ? c->capacity[(void**)&c->d_prims] : 0;
+	const int rc = build_wide_bvh_device(c->stream, c->arena, c->d_verts, c->d_tris, c->num_tris, c->d_spheres, c->num_spheres, d_rank,
+	                                     (opts && opts->max_leaf_tris >= 1) ? opts->max_leaf_tris : 3, opts ? opts->ploc_radius : 0, &r);
+	c->d_nodes = (uint4*)r.nodes; c->d_prims = (float4*)r.prims;   // the builder may have replaced them even when it failed later
 	c->capacity[(void**)&c->d_nodes] = r.nodes_capacity_bytes; c->capacity[(void**)&c->d_prims] = r.prims_capacity_bytes;
+	if (rc) { c->num_nodes = c->num_prims = 0; return rc; }
 	c->bvh_depth = r.depth; c->num_nodes = r.num_nodes; c->num_prims = r.num_prims;
 	c->extend_blocks[0] = 0;
 	if (info) {
@@ -406,6 +408,15 @@ int cupt_read_bvh(cupt_context* c, void* nodes80, void* tris48, int64_t* counts)
 	if (nodes80) CK(cudaMemcpyAsync(nodes80, c->d_nodes, (size_t)c->num_nodes * sizeof(Node8), cudaMemcpyDeviceToHost, c->stream));
 	if (tris48) CK(cudaMemcpyAsync(tris48, c->d_prims, (size_t)c->num_prims * sizeof(Prim48), cudaMemcpyDeviceToHost, c->stream));
 	CK(cudaStreamSynchronize(c->stream));
+	return CUPT_OK;
+}
+
+int cupt_release_workspace(cupt_context* c)
+{
+	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
+	CK(cudaSetDevice(c->device));
+	CK(cudaStreamSynchronize(c->stream));
+	c->arena.destroy();
 	return CUPT_OK;
 }
 

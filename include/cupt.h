@@ -116,6 +116,7 @@ typedef struct cupt_bvh_opts {
 	int max_leaf_tris;     /* triangles per BVH8 child leaf, 1..3 (default 3) */
 	int threads;           /* host threads, 0 = all */
 	const uint32_t* tie_rank;  /* optional rank per triangle (cupt_bvh2_leaf_order); NULL = triangle index */
+	int ploc_radius;       /* cupt_build_bvh_device only: neighbour search radius of the clustering: 1, 2, 4 (default, also for any other value), 8, 16 or 32 */
 } cupt_bvh_opts;
 typedef struct cupt_bvh_info {
 	int64_t num_nodes;       /* 80-byte BVH8 nodes */
@@ -146,6 +147,8 @@ int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int de
 int cupt_build_bvh_device(cupt_context* c, const cupt_bvh_opts* opts, cupt_bvh_info* info);
 /* copy the device's wide BVH back (tests: structural invariants); counts = {nodes, records, depth, PLOC rounds}; any pointer may be NULL */
 int cupt_read_bvh(cupt_context* c, void* nodes80, void* tris48, int64_t* counts);
+/* the build workspace (about 150 B per primitive) stays allocated between builds; this frees it */
+int cupt_release_workspace(cupt_context* c);
 /* CUDA-event times of the last cupt_build_bvh_device in ms: {total, boxes+Morton+sort, clustering, collapse+emit} */
 int cupt_get_build_times(cupt_context* c, float* ms4);
 int cupt_set_camera(cupt_context* c, const cupt_camera* cam);     /* kernel.cu:642-651 */

@@ -9,13 +9,14 @@ from cudapathtracer_b200 import api
 sc, s, cam = bench.build_scene()
 ctx = api.Context(0)
 ctx.set_scene(s); ctx.set_camera(cam)
-for which in ("host", "device"):
+for which in ["host"] + ["device" + r for r in os.environ.get("RADII", "1,2,4,8").split(",")]:
     if which == "host":
         t0 = time.perf_counter(); b = s.build_bvh(); ctx.set_bvh(b); wall = time.perf_counter() - t0
         info = b.info()
     else:
-        ctx.build_bvh_device()
-        t0 = time.perf_counter(); info = ctx.build_bvh_device(); wall = time.perf_counter() - t0
+        R = int(which[6:])
+        ctx.build_bvh_device(radius=R)
+        t0 = time.perf_counter(); info = ctx.build_bvh_device(radius=R); wall = time.perf_counter() - t0
     rec = {"builder": which, "build_wall_ms": round(wall * 1e3, 2), **{k: (round(v, 3) if isinstance(v, float) else v) for k, v in info.items()}}
     for integ, name in ((api.INTEGRATOR_PT, "pt"), (api.INTEGRATOR_BDPT, "bdpt")):
         ctx.set_options(max_depth=bench.DEPTH, seed=bench.SEED, traversal=api.TRAVERSAL_WIDE, integrator=integ, collect_stats=1, time_stages=0)

@@ -10,6 +10,7 @@ import oraclebind
 PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
 W, SPP, DEPTH = 1024, 16, 5
 BVH = os.environ.get("BVH", "device")
+RADIUS = int(os.environ.get("RADIUS", "0"))
 
 
 def main():
@@ -25,8 +26,8 @@ def main():
         ctx.set_scene(s); ctx.set_camera(cam)
         b = None
         if BVH == "device":   # built on the GPU from the uploaded scene (csrc/bvh_device.cu)
-            ctx.build_bvh_device()   # warm-up (first-use allocations), then the timed build
-            t0 = time.time(); info = ctx.build_bvh_device(); tb = time.time() - t0
+            ctx.build_bvh_device(radius=RADIUS)   # warm-up (first-use allocations), then the timed build
+            t0 = time.time(); info = ctx.build_bvh_device(radius=RADIUS); tb = time.time() - t0
         else:
             t0 = time.time(); b = s.build_bvh(); tb = time.time() - t0
             info = b.info()
@@ -44,7 +45,7 @@ def main():
         rays = stb["rays"]
         bpr = npr * 80 + tpr * 48 + 44
         ext_gbs = rays * bpr / (stb["ms_extend"] * 1e-3) / 1e9
-        rec = {"config": 4, "triangles": n, "gen_s": round(tg, 2), "bvh": BVH, "bvh_build_s": round(tb, 3), "bvh_build_ms_device": {k: round(v, 2) for k, v in info.items() if k.startswith("ms_")}, "nodes": info["num_nodes"], "depth": info["depth"],
+        rec = {"config": 4, "triangles": n, "gen_s": round(tg, 2), "bvh": BVH, "ploc_radius": RADIUS, "bvh_build_s": round(tb, 3), "bvh_build_ms_device": {k: round(v, 2) for k, v in info.items() if k.startswith("ms_")}, "nodes": info["num_nodes"], "depth": info["depth"],
                "bvh_mb": round((info["num_nodes"] * 80 + info["num_tri_records"] * 48) / 1e6, 1), "image": f"{W}x{W}", "spp": SPP, "max_depth": DEPTH,
                "ms": round(best * 1e3, 2), "mrays_per_s": round(rays / best / 1e6, 1), "rays_per_sample": round(rays / (W * W * SPP), 3),
                "nodes_per_ray": round(npr, 2), "tris_per_ray": round(tpr, 2), "bytes_per_ray": round(bpr, 1), "ms_extend": round(stb["ms_extend"], 2),
