@@ -342,6 +342,20 @@ class Context:
         _check(self.lib.cupt_read_accum(self.h, _ptr(out), int(normalise)))
         return out
 
+    def read_image_rgb8(self, mirror_x: bool = False) -> np.ndarray:
+        """tonemapped 8-bit image [H, W, 3] computed on the device (kernel.cu:763-778 without the file)"""
+        h, w = self.shape
+        out = np.empty((h, w, 3), dtype=np.uint8)
+        _check(self.lib.cupt_read_image_rgb8(self.h, _ptr(out), int(mirror_x)))
+        return out
+
+    def read_heatmap(self):
+        """(nodes visited, primitives tested) per pixel by the primary rays, two [H, W] float arrays"""
+        h, w = self.shape
+        a = np.empty((h, w), dtype=np.float32); b = np.empty((h, w), dtype=np.float32)
+        _check(self.lib.cupt_read_heatmap(self.h, _ptr(a), _ptr(b)))
+        return a, b
+
     def copy_accum_device(self, dst_ptr: int):
         _check(self.lib.cupt_copy_accum_device(self.h, C.c_void_p(dst_ptr)))
 
@@ -379,6 +393,11 @@ def write_ppm(path: str, rgb_mean: np.ndarray, width: int, height: int):
     """kernel.cu:763-778"""
     rgb_mean = np.ascontiguousarray(rgb_mean, dtype=np.float32)
     _check(load_library().cupt_write_ppm(path.encode(), _ptr(rgb_mean), width, height))
+
+
+def write_ppm8(path: str, rgb8: np.ndarray):
+    rgb8 = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    _check(load_library().cupt_write_ppm8(path.encode(), _ptr(rgb8), rgb8.shape[1], rgb8.shape[0]))
 
 
 def tonemap(rgb_mean: np.ndarray) -> np.ndarray:

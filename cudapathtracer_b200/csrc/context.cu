@@ -7,6 +7,7 @@
 #include "kernels.cuh"
 #include "bdpt.cuh"
 #include "bvh_device.h"
+#include "output.cuh"
 #include <algorithm>
 #include <map>
 #include <cstring>
@@ -49,7 +50,7 @@ struct cupt_context {
 	std::vector<StageEvent> pending, pool;
 	std::map<void**, size_t> capacity;   // bytes behind each uploaded device pointer (upload())
 	int extend_blocks[2] = {0, 0};
-	BuildArena arena; uint32_t* d_build_rank = nullptr;
+	BuildArena arena; uint32_t* d_build_rank = nullptr; uint8_t* d_rgb8 = nullptr;
 	float build_ms[4] = {0, 0, 0, 0}; int build_rounds = 0;   // last cupt_build_bvh_device: total, sort, PLOC, collapse
 };
 
@@ -247,7 +248,7 @@ void cupt_destroy(cupt_context* c)
 	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2); cudaFree(c->d_bvh2_up); cudaFree(c->d_bvh2_leaf_parent);
 	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
 	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats);
-	cudaFree(c->d_accum); cudaFree(c->d_build_rank); c->arena.destroy();
+	cudaFree(c->d_accum); cudaFree(c->d_build_rank); cudaFree(c->d_rgb8); c->arena.destroy();
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;
 }
@@ -613,6 +614,55 @@ int cupt_read_primary_hits(cupt_context* c, int32_t* tri_id, float* t)
 {
 	if (!tri_id || !t) return set_error(CUPT_ERR_INVALID, "null output");
 	return primary_pass(c, tri_id, t, nullptr);
+}
+
+int cupt_read_image_rgb8(cupt_context* c, uint8_t* rgb, int mirror_x)
+{
+	if (!c || !rgb) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (!c->d_accum || c->samples_accumulated == 0) return set_error(CUPT_ERR_INVALID, "nothing has been rendered");
+	CK(cudaSetDevice(c->device));
+	const int W = c->cam.pxlWidth, H = c->cam.pxlHeight;
+	const size_t bytes = (size_t)W * H * 3;
+	int rc;
+	if (c->capacity[(void**)&c->d_rgb8] < bytes) {
+		if (c->d_rgb8) { CK(cudaFree(c->d_rgb8)); c->d_rgb8 = nullptr; }
+		CK(cudaMalloc((void**)&c->d_rgb8, bytes));
+		c->capacity[(void**)&c->d_rgb8] = bytes;
+	}
+	(void)rc;
+	k_tonemap_rgb8<<<(W * H + 255) / 256, 256, 0, c->stream>>>(c->d_accum, 1.0f / (float)c->samples_accumulated, W, H, mirror_x, c->d_rgb8);
+	c->launches++;
+	CK(cudaGetLastError());
+	CK(cudaMemcpyAsync(rgb, c->d_rgb8, bytes, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	return CUPT_OK;
+}
+
+int cupt_read_heatmap(cupt_context* c, float* nodes_visited, float* prims_tested)
+{
+	if (!c || (!nodes_visited && !prims_tested)) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	int rc;
+	const int saved = c->opts.traversal;
+	c->opts.traversal = CUPT_TRAVERSAL_WIDE;           // the map is of the wide BVH, whatever mode renders
+	rc = check_ready(c, false);
+	c->opts.traversal = saved;
+	if (rc) return rc;
+	CK(cudaSetDevice(c->device));
+	const size_t P = (size_t)c->cam.pxlWidth * c->cam.pxlHeight;
+	float* d = nullptr;
+	CK(cudaMalloc((void**)&d, 2 * P * sizeof(float)));
+	const DevScene sc = make_scene(c);
+	const PassParams pp = make_pass(c, 0, 1, 1);
+	const size_t smem = (size_t)sc.stack_cap * 128 * sizeof(uint2);
+	CK(cudaFuncSetAttribute(k_heatmap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	k_heatmap<<<(unsigned)((P + 127) / 128), 128, smem, c->stream>>>(sc, pp, d, d + P);
+	c->launches++;
+	CK(cudaGetLastError());
+	if (nodes_visited) CK(cudaMemcpyAsync(nodes_visited, d, P * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+	if (prims_tested) CK(cudaMemcpyAsync(prims_tested, d + P, P * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	cudaFree(d);
+	return CUPT_OK;
 }
 
 int cupt_camera_rays(cupt_context* c, float* rays_host)

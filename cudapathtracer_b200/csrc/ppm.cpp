@@ -46,4 +46,18 @@ int cupt_write_ppm(const char* path, const float* rgb_mean, int width, int heigh
 	return rc == 0 ? CUPT_OK : set_error(CUPT_ERR_IO, "write to %s failed", path);
 }
 
+int cupt_write_ppm8(const char* path, const uint8_t* rgb, int width, int height)
+{
+	if (!path || !rgb || width <= 0 || height <= 0)
+		return set_error(CUPT_ERR_INVALID, "bad arguments");
+	FILE* fp = fopen(path, "w");
+	if (!fp)
+		return set_error(CUPT_ERR_IO, "cannot open %s for writing", path);
+	fprintf(fp, "P3 %d %d 255\n", width, height);
+	const size_t n = (size_t)width * height;
+	for (size_t i = 0; i < n; ++i) fprintf(fp, "%d %d %d ", rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]);
+	int rc = fclose(fp);
+	return rc == 0 ? CUPT_OK : set_error(CUPT_ERR_IO, "write to %s failed", path);
+}
+
 }  // extern "C"

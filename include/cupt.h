@@ -210,6 +210,14 @@ int cupt_reset_stats(cupt_context* c);
 /* ---- output — kernel.cu:763-778 ------------------------------------------------------------------ */
 /* P3 PPM: x mirrored, Reinhard c/(c+1) (color.h:59-62), gamma 1/2.2 (color.h:68-71), (int)(c*255) truncation */
 int cupt_write_ppm(const char* path, const float* rgb_mean, int width, int height);
+/* the same output stage on the device: mean = sum / samples, normalized (color.h:59-62), gammaCorrect with (float)(1/2.2)
+ * (color.h:68-71, kernel.cu:774), (int)(c*255); 3 bytes per pixel come back instead of 12.  mirror_x = 1 flips x like
+ * the reference's writer (kernel.cu:768).  rgb: width*height*3 bytes, row-major. */
+int cupt_read_image_rgb8(cupt_context* c, uint8_t* rgb, int mirror_x);
+int cupt_write_ppm8(const char* path, const uint8_t* rgb, int width, int height);   /* P3 text like kernel.cu:763-778, no mirroring */
+/* traversal-cost heat map of the primary rays: wide-BVH nodes visited / primitives tested per pixel (the reference's
+ * per-ray step counter, kernel.cu:121,132,152, which drew keepers/"sponza bvh.ppm").  Either pointer may be NULL. */
+int cupt_read_heatmap(cupt_context* c, float* nodes_visited, float* prims_tested);
 int cupt_tonemap(const float* rgb_mean, int64_t npixels, int32_t* out_rgb255);
 
 #ifdef __cplusplus

@@ -421,3 +421,28 @@ def test_device_bvh_build_degenerate_inputs(ctx, get_case):
     want = ctx.primary_hits()
     info = ctx.build_bvh_device(tie_rank=s.rank)
     assert info["num_spheres"] == len(s.spheres) and hits_equal(ctx.primary_hits(), want)
+
+
+def test_device_output_stage(ctx, get_case, tmp_path):
+    """tonemap on the device == the host restatement of kernel.cu:763-778 (which tests/
+    test_scene_ingest.py pins against the reference's normalized/gammaCorrect) except where device pow differs from
+    glibc's by an ulp right at a truncation boundary (<= 0.1 % of the values, by one level); heat map of the primary rays."""
+    c = get_case("cornell_lights")
+    load(ctx, c, api.TRAVERSAL_WIDE, max_depth=5, seed=3, collect_stats=1)
+    ctx.reset_accum(); ctx.render(0, 8)
+    want = api.tonemap(ctx.read_accum(True)).reshape(c.h, c.w, 3)
+    got = ctx.read_image_rgb8()
+    diff = np.abs(got.astype(np.int32) - want.astype(np.int32))
+    assert got.shape == (c.h, c.w, 3) and diff.max() <= 1 and (diff != 0).mean() <= 1e-3
+    assert np.array_equal(ctx.read_image_rgb8(mirror_x=True), got[:, ::-1])
+    api.write_ppm8(str(tmp_path / "a.ppm"), got[:, ::-1]); api.write_ppm(str(tmp_path / "b.ppm"), ctx.read_accum(True), c.w, c.h)
+    ta, tb = open(tmp_path / "a.ppm").read().split(), open(tmp_path / "b.ppm").read().split()
+    assert ta[:4] == tb[:4] and len(ta) == len(tb) and np.mean(np.array(ta[4:], int) != np.array(tb[4:], int)) <= 1e-3
+    nodes, prims = ctx.read_heatmap()
+    ids, _ = ctx.primary_hits()
+    assert nodes.shape == (c.h, c.w) and nodes.min() >= 1 and prims[ids.reshape(c.h, c.w) >= 0].min() >= 1
+    ctx.reset_stats(); ctx.primary_hits(); st = ctx.stats()
+    # the wavefront kernel defers primitive tests by one step, so it culls a little later than the single-ray walk
+    assert 0.9 * st["nodes_visited"] <= nodes.sum() <= 1.1 * st["nodes_visited"]
+    assert 0.9 * st["tris_tested"] <= prims.sum() <= 1.1 * st["tris_tested"]
+    ctx.set_options(collect_stats=0)
