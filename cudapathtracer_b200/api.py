@@ -30,6 +30,7 @@ MAX_FLOAT = np.float32(100000.0)
 INTEGRATOR_PT, INTEGRATOR_BDPT = 2, 1
 TRAVERSAL_WIDE, TRAVERSAL_REF_BVH2, TRAVERSAL_WIDE_STRICT = 0, 1, 2
 TRI_REFEXACT, TRI_WATERTIGHT = 0, 1
+OBJ_FACE_MATERIALS, OBJ_DEDUP_MATERIALS = 1, 2
 
 
 class CuptError(RuntimeError):
@@ -133,11 +134,22 @@ class SceneHandle:
     def clear(self):
         _check(self.lib.cupt_scene_clear(self.h))
 
-    def load_obj(self, path: str, mtl_dir: Optional[str] = None, origin=(0.0, 0.0, 0.0), scale: float = 1.0, flip: bool = False):
-        """loadOBJ(filename, origin, scale, flipNormals) — modelLoader.h:125"""
+    def load_obj(self, path: str, mtl_dir: Optional[str] = None, origin=(0.0, 0.0, 0.0), scale: float = 1.0, flip: bool = False,
+                 face_materials: bool = False, dedup_materials: bool = False):
+        """loadOBJ(filename, origin, scale, flipNormals) — modelLoader.h:125; the two flags go beyond the reference
+        (per-face materials, de-duplicated material table: SURVEY 8f rank 2)"""
         o = (C.c_float * 3)(*origin)
-        _check(self.lib.cupt_scene_load_obj(self.h, path.encode(), None if mtl_dir is None else mtl_dir.encode(),
-                                            o, C.c_float(scale), int(flip)))
+        flags = (OBJ_FACE_MATERIALS if face_materials else 0) | (OBJ_DEDUP_MATERIALS if dedup_materials else 0)
+        _check(self.lib.cupt_scene_load_obj_ex(self.h, path.encode(), None if mtl_dir is None else mtl_dir.encode(),
+                                               o, C.c_float(scale), int(flip), flags))
+
+    def save(self, path: str):
+        """binary scene cache (cupt_scene_save)"""
+        _check(self.lib.cupt_scene_save(self.h, path.encode()))
+
+    def load(self, path: str):
+        """replace the contents with a scene cache written by save()"""
+        _check(self.lib.cupt_scene_load(self.h, path.encode()))
 
     def add_materials(self, mats: np.ndarray, duplicate_table: bool = True) -> int:
         mats = np.ascontiguousarray(mats, dtype=MATERIAL)

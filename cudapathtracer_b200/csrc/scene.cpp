@@ -136,8 +136,8 @@ int cupt_scene_add_shape_facemats(cupt_scene* s, const float* positions, int nve
 	return append_shape(s, positions, nverts, indices, ntris, 0, face_materials, origin, scale, flip_normals);
 }
 
-int cupt_scene_load_obj(cupt_scene* s, const char* path, const char* mtl_dir, const float origin[3], float scale,
-                        int flip_normals)
+int cupt_scene_load_obj_ex(cupt_scene* s, const char* path, const char* mtl_dir, const float origin[3], float scale,
+                           int flip_normals, int flags)
 {
 	if (!s || !path)
 		return set_error(CUPT_ERR_INVALID, "bad arguments");
@@ -153,25 +153,159 @@ int cupt_scene_load_obj(cupt_scene* s, const char* path, const char* mtl_dir, co
 			table[i].albedo[k] = materials[i].diffuse[k];
 			table[i].emission[k] = materials[i].emission[k];
 		}
-	int matsOffset = 0;
-	rc = cupt_scene_add_materials(s, table.empty() ? nullptr : &table[0], (int)table.size(), 1, &matsOffset);
-	if (rc != CUPT_OK)
-		return rc;
+	// file material index -> scene material index
+	std::vector<int> remap(table.size());
+	if (flags & CUPT_OBJ_DEDUP_MATERIALS) {
+		// one entry per distinct material instead of the reference's table appended twice per file
+		for (size_t i = 0; i < table.size(); ++i) {
+			int found = -1;
+			for (size_t j = 0; j < s->mats.size() && found < 0; ++j)
+				if (memcmp(&s->mats[j], &table[i], sizeof(cupt_material)) == 0) found = (int)j;
+			if (found < 0) { found = (int)s->mats.size(); s->mats.push_back(table[i]); }
+			remap[i] = found;
+		}
+	} else {
+		int matsOffset = 0;
+		rc = cupt_scene_add_materials(s, table.empty() ? nullptr : &table[0], (int)table.size(), 1, &matsOffset);
+		if (rc != CUPT_OK)
+			return rc;
+		for (size_t i = 0; i < table.size(); ++i) remap[i] = (int)i + matsOffset;
+	}
+	std::vector<int32_t> face;
 	for (size_t i = 0; i < shapes.size(); ++i) {
 		const ObjShape& sh = shapes[i];
 		const int ntris = (int)(sh.indices.size() / 3);
 		if (ntris == 0)
 			continue;
-		// ONE material per shape: material_ids[0] + matsOffset (modelLoader.h:189).  tinyobj reports -1 for
-		// "no material"; the reference then indexes the slot before its table.  That is rejected here.
-		int mat = sh.material_ids[0] + matsOffset;
-		if (sh.material_ids[0] < 0)
-			return set_error(CUPT_ERR_PARSE, "shape '%s' has no material (usemtl missing or unknown)", sh.name.c_str());
+		const int32_t* face_mats = nullptr;
+		int mat = 0;
+		if (flags & CUPT_OBJ_FACE_MATERIALS) {
+			// material_ids[k] per triangle (the reference takes material_ids[0] for the whole shape, modelLoader.h:189)
+			face.resize((size_t)ntris);
+			for (int t = 0; t < ntris; ++t) {
+				const int32_t m = sh.material_ids[(size_t)t];
+				if (m < 0 || m >= (int32_t)remap.size())
+					return set_error(CUPT_ERR_PARSE, "shape '%s' face %d has no material (usemtl missing or unknown)", sh.name.c_str(), t);
+				face[(size_t)t] = remap[(size_t)m];
+			}
+			face_mats = &face[0];
+		} else {
+			// ONE material per shape: material_ids[0] + matsOffset (modelLoader.h:189).  tinyobj reports -1 for
+			// "no material"; the reference then indexes the slot before its table.  That is rejected here.
+			if (sh.material_ids[0] < 0 || sh.material_ids[0] >= (int32_t)remap.size())
+				return set_error(CUPT_ERR_PARSE, "shape '%s' has no material (usemtl missing or unknown)", sh.name.c_str());
+			mat = remap[(size_t)sh.material_ids[0]];
+		}
 		rc = append_shape(s, sh.positions.empty() ? nullptr : &sh.positions[0], (int)(sh.positions.size() / 3),
-		                  &sh.indices[0], ntris, mat, nullptr, origin, scale, flip_normals);
+		                  &sh.indices[0], ntris, mat, face_mats, origin, scale, flip_normals);
 		if (rc != CUPT_OK)
 			return rc;
 	}
+	return CUPT_OK;
+}
+
+int cupt_scene_load_obj(cupt_scene* s, const char* path, const char* mtl_dir, const float origin[3], float scale,
+                        int flip_normals)
+{
+	return cupt_scene_load_obj_ex(s, path, mtl_dir, origin, scale, flip_normals, 0);   // the reference's semantics
+}
+
+// ---- binary scene cache: the five arrays verbatim + FNV-1a checksum ----------------------------
+namespace {
+struct CacheHeader {
+	char magic[8];            // "CUPTSCN1"
+	uint64_t nverts, ntris, nmats, nlights, nspheres;
+	float totalLightArea;
+	uint32_t pod_sizes;       // sizeof(vec3) | sizeof(triangle) << 8 | sizeof(material) << 16 | sizeof(sphere) << 24
+};
+uint64_t fnv1a(uint64_t h, const void* p, size_t n)
+{
+	const unsigned char* b = static_cast<const unsigned char*>(p);
+	for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; }
+	return h;
+}
+const uint32_t kPodSizes = (uint32_t)sizeof(cupt_vec3) | ((uint32_t)sizeof(cupt_triangle) << 8) | ((uint32_t)sizeof(cupt_material) << 16) | ((uint32_t)sizeof(cupt_sphere) << 24);
+}  // namespace
+
+int cupt_scene_save(const cupt_scene* s, const char* path)
+{
+	if (!s || !path)
+		return set_error(CUPT_ERR_INVALID, "bad arguments");
+	FILE* fp = fopen(path, "wb");
+	if (!fp)
+		return set_error(CUPT_ERR_IO, "cannot open %s for writing", path);
+	CacheHeader h;
+	memset(&h, 0, sizeof(h));
+	memcpy(h.magic, "CUPTSCN1", 8);
+	h.nverts = s->verts.size(); h.ntris = s->tris.size(); h.nmats = s->mats.size(); h.nlights = s->lights.size(); h.nspheres = s->spheres.size();
+	h.totalLightArea = s->totalLightArea; h.pod_sizes = kPodSizes;
+	uint64_t sum = fnv1a(14695981039346656037ull, &h, sizeof(h));
+	bool ok = fwrite(&h, sizeof(h), 1, fp) == 1;
+	auto put = [&](const void* p, size_t bytes) {
+		if (bytes == 0) return;
+		sum = fnv1a(sum, p, bytes);
+		ok = ok && fwrite(p, 1, bytes, fp) == bytes;
+	};
+	put(s->verts.data(), s->verts.size() * sizeof(cupt_vec3));
+	put(s->tris.data(), s->tris.size() * sizeof(cupt_triangle));
+	put(s->mats.data(), s->mats.size() * sizeof(cupt_material));
+	put(s->lights.data(), s->lights.size() * sizeof(int32_t));
+	put(s->spheres.data(), s->spheres.size() * sizeof(cupt_sphere));
+	ok = ok && fwrite(&sum, sizeof(sum), 1, fp) == 1;
+	ok = (fclose(fp) == 0) && ok;
+	return ok ? CUPT_OK : set_error(CUPT_ERR_IO, "write to %s failed", path);
+}
+
+int cupt_scene_load(cupt_scene* s, const char* path)
+{
+	if (!s || !path)
+		return set_error(CUPT_ERR_INVALID, "bad arguments");
+	FILE* fp = fopen(path, "rb");
+	if (!fp)
+		return set_error(CUPT_ERR_IO, "cannot open %s", path);
+	CacheHeader h;
+	if (fread(&h, sizeof(h), 1, fp) != 1 || memcmp(h.magic, "CUPTSCN1", 8) != 0 || h.pod_sizes != kPodSizes) {
+		fclose(fp);
+		return set_error(CUPT_ERR_PARSE, "%s is not a scene cache of this library version", path);
+	}
+	const uint64_t lim = 0x7fffffffull;
+	if (h.nverts > lim || h.ntris > lim || h.nmats > lim || h.nlights > h.ntris || h.nspheres > lim) {
+		fclose(fp);
+		return set_error(CUPT_ERR_PARSE, "%s: implausible counts in the header", path);
+	}
+	cupt_scene t;
+	uint64_t sum = fnv1a(14695981039346656037ull, &h, sizeof(h));
+	bool ok = true;
+	auto get = [&](void* p, size_t bytes) {
+		if (bytes == 0 || !ok) return;
+		ok = fread(p, 1, bytes, fp) == bytes;
+		if (ok) sum = fnv1a(sum, p, bytes);
+	};
+	try {
+		t.verts.resize(h.nverts); t.tris.resize(h.ntris); t.mats.resize(h.nmats); t.lights.resize(h.nlights); t.spheres.resize(h.nspheres);
+	} catch (...) {
+		fclose(fp);
+		return set_error(CUPT_ERR_NOMEM, "out of memory reading %s", path);
+	}
+	get(t.verts.data(), t.verts.size() * sizeof(cupt_vec3));
+	get(t.tris.data(), t.tris.size() * sizeof(cupt_triangle));
+	get(t.mats.data(), t.mats.size() * sizeof(cupt_material));
+	get(t.lights.data(), t.lights.size() * sizeof(int32_t));
+	get(t.spheres.data(), t.spheres.size() * sizeof(cupt_sphere));
+	uint64_t stored = 0;
+	ok = ok && fread(&stored, sizeof(stored), 1, fp) == 1;
+	fclose(fp);
+	if (!ok) return set_error(CUPT_ERR_PARSE, "%s is truncated", path);
+	if (stored != sum) return set_error(CUPT_ERR_PARSE, "%s: checksum mismatch", path);
+	for (const cupt_triangle& tr : t.tris)
+		if (tr.v0 < 0 || tr.v1 < 0 || tr.v2 < 0 || (uint64_t)tr.v0 >= h.nverts || (uint64_t)tr.v1 >= h.nverts || (uint64_t)tr.v2 >= h.nverts ||
+		    tr.mat < 0 || (uint64_t)tr.mat >= h.nmats)
+			return set_error(CUPT_ERR_PARSE, "%s: triangle references outside the arrays", path);
+	for (int32_t l : t.lights)
+		if (l < 0 || (uint64_t)l >= h.ntris) return set_error(CUPT_ERR_PARSE, "%s: light index outside the triangle array", path);
+	t.totalLightArea = h.totalLightArea;
+	s->verts.swap(t.verts); s->tris.swap(t.tris); s->mats.swap(t.mats); s->lights.swap(t.lights); s->spheres.swap(t.spheres);
+	s->totalLightArea = t.totalLightArea;
 	return CUPT_OK;
 }
 

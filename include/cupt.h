@@ -82,6 +82,16 @@ int cupt_scene_clear(cupt_scene* s);
  * reference hard-codes as "models/" (modelLoader.h:132); NULL means "models/".  Appends, like the reference. */
 int cupt_scene_load_obj(cupt_scene* s, const char* path, const char* mtl_dir,
                         const float origin[3], float scale, int flip_normals);
+/* SURVEY 8f rank 2 — ingest fidelity beyond the reference's loader: */
+enum { CUPT_OBJ_FACE_MATERIALS = 1,   /* material_ids[k] per triangle instead of material_ids[0] per shape (modelLoader.h:189);
+                                         the vendored loader splits shapes at usemtl, so this only guards against a parser that does not */
+       CUPT_OBJ_DEDUP_MATERIALS = 2 };/* one table entry per distinct material instead of the table appended twice per file (modelLoader.h:138-159) */
+int cupt_scene_load_obj_ex(cupt_scene* s, const char* path, const char* mtl_dir, const float origin[3], float scale,
+                           int flip_normals, int flags);   /* flags = 0: exactly cupt_scene_load_obj */
+/* binary scene cache: the arrays verbatim with a checksum; load REPLACES the scene's contents (CUPT_ERR_PARSE on a
+ * foreign, truncated or corrupted file) */
+int cupt_scene_save(const cupt_scene* s, const char* path);
+int cupt_scene_load(cupt_scene* s, const char* path);
 /* the same append for an in-memory shape: materials first (appended twice like modelLoader.h:138-159 when
  * duplicate_table != 0), then one call per shape with ONE material per shape (modelLoader.h:189). */
 int cupt_scene_add_materials(cupt_scene* s, const cupt_material* mats, int n, int duplicate_table, int* first_index);
