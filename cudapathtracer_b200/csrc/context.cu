@@ -51,6 +51,7 @@ struct cupt_context {
 	std::map<void**, size_t> capacity;   // bytes behind each uploaded device pointer (upload())
 	int extend_blocks[2] = {0, 0};
 	BuildArena arena; uint32_t* d_build_rank = nullptr; uint8_t* d_rgb8 = nullptr;
+	float4* d_prims_wt = nullptr; bool wt_valid = false;   // CUPT_TRI_WATERTIGHT: vertex records, same order as d_prims
 	float build_ms[4] = {0, 0, 0, 0}; int build_rounds = 0;   // last cupt_build_bvh_device: total, sort, PLOC, collapse
 };
 
@@ -146,7 +147,7 @@ PassParams make_pass(const cupt_context* c, int first_sample, int samples, int f
 DevScene make_scene(const cupt_context* c)
 {
 	DevScene sc;
-	sc.nodes = c->d_nodes; sc.prims = c->d_prims; sc.bvh2 = c->d_bvh2; sc.verts = c->d_verts; sc.tris = c->d_tris;
+	sc.nodes = c->d_nodes; sc.prims = (c->opts.tri_test == CUPT_TRI_WATERTIGHT && c->wt_valid) ? c->d_prims_wt : c->d_prims; sc.bvh2 = c->d_bvh2; sc.verts = c->d_verts; sc.tris = c->d_tris;
 	sc.trishade = c->d_trishade; sc.mats = c->d_mats; sc.bvh2_up = c->d_bvh2_up; sc.bvh2_leaf_parent = c->d_bvh2_leaf_parent;
 	sc.lights = c->d_lights; sc.light_cdf = c->d_light_cdf; sc.spheres = c->d_spheres;
 	sc.numLights = c->num_lights; sc.totalLightArea = c->total_light_area;
@@ -154,7 +155,7 @@ DevScene make_scene(const cupt_context* c)
 	return sc;
 }
 
-int check_ready(const cupt_context* c, bool need_shading, bool need_cam = true)
+int check_ready(cupt_context* c, bool need_shading, bool need_cam = true)
 {
 	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
 	if (need_cam && !c->have_cam) return set_error(CUPT_ERR_INVALID, "no camera set (cupt_set_camera)");
@@ -163,6 +164,23 @@ int check_ready(const cupt_context* c, bool need_shading, bool need_cam = true)
 	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE_STRICT && (c->num_spheres > 0 || c->bvh2_leaves != c->num_tris))
 		return set_error(CUPT_ERR_INVALID, "strict mode needs a sphere-free scene and the reference BVH2 of the same scene");
 	if (need_shading && !c->d_trishade) return set_error(CUPT_ERR_INVALID, "no scene set (cupt_set_scene)");
+	if (c->opts.tri_test == CUPT_TRI_WATERTIGHT) {
+		if (c->opts.traversal != CUPT_TRAVERSAL_WIDE)
+			return set_error(CUPT_ERR_INVALID, "CUPT_TRI_WATERTIGHT needs CUPT_TRAVERSAL_WIDE (the other modes reproduce the reference's own test)");
+		if (!c->d_tris && c->num_prims > c->num_spheres) return set_error(CUPT_ERR_INVALID, "no scene set (cupt_set_scene)");
+		if (!c->wt_valid) {   // vertex records (kind 2) in the order of the wide BVH's primitive array, made once per BVH
+			const size_t bytes = (size_t)c->num_prims * 48;
+			if (c->capacity[(void**)&c->d_prims_wt] < bytes) {
+				if (c->d_prims_wt) { CK(cudaFree(c->d_prims_wt)); c->d_prims_wt = nullptr; }
+				CK(cudaMalloc((void**)&c->d_prims_wt, bytes));
+				c->capacity[(void**)&c->d_prims_wt] = bytes;
+			}
+			k_vertex_prims<<<(unsigned)((c->num_prims + 255) / 256), 256, 0, c->stream>>>(c->d_prims, c->num_prims, c->d_verts, c->d_tris, c->d_prims_wt);
+			CK(cudaGetLastError());
+			c->launches++;
+			c->wt_valid = true;
+		}
+	}
 	return CUPT_OK;
 }
 
@@ -248,7 +266,7 @@ void cupt_destroy(cupt_context* c)
 	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2); cudaFree(c->d_bvh2_up); cudaFree(c->d_bvh2_leaf_parent);
 	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
 	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats);
-	cudaFree(c->d_accum); cudaFree(c->d_build_rank); cudaFree(c->d_rgb8); c->arena.destroy();
+	cudaFree(c->d_accum); cudaFree(c->d_build_rank); cudaFree(c->d_rgb8); cudaFree(c->d_prims_wt); c->arena.destroy();
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;
 }
@@ -282,7 +300,7 @@ int cupt_set_render_opts(cupt_context* c, const cupt_render_opts* o)
 		return set_error(CUPT_ERR_INVALID, "unknown integrator %d", o->integrator);
 	if (o->traversal != CUPT_TRAVERSAL_WIDE && o->traversal != CUPT_TRAVERSAL_REF_BVH2 && o->traversal != CUPT_TRAVERSAL_WIDE_STRICT)
 		return set_error(CUPT_ERR_INVALID, "bad traversal");
-	if (o->tri_test != CUPT_TRI_REFEXACT) return set_error(CUPT_ERR_INVALID, "tri_test %d is not implemented", o->tri_test);
+	if (o->tri_test != CUPT_TRI_REFEXACT && o->tri_test != CUPT_TRI_WATERTIGHT) return set_error(CUPT_ERR_INVALID, "unknown tri_test %d", o->tri_test);
 	c->opts = *o;
 	return CUPT_OK;
 }
@@ -349,6 +367,7 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 	if ((rc = upload(c, &c->d_spheres, ss.data(), ss.size() * sizeof(SphereShade)))) return rc;
 	c->num_spheres = (int)ss.size();
 	c->num_tris = (int64_t)nt; c->num_lights = (int)nl; c->total_light_area = s->totalLightArea;
+	c->wt_valid = false;
 	CK(cudaStreamSynchronize(c->stream));   // the staging vectors above are temporaries
 	return CUPT_OK;
 }
@@ -364,7 +383,7 @@ int cupt_set_bvh(cupt_context* c, const cupt_bvh* b)
 	if ((rc = upload(c, &c->d_nodes, b->nodes.data(), b->nodes.size() * sizeof(Node8)))) return rc;
 	if ((rc = upload(c, &c->d_prims, b->prims.data(), b->prims.size() * sizeof(Prim48)))) return rc;
 	c->bvh_depth = b->depth; c->num_nodes = (int64_t)b->nodes.size(); c->num_prims = (int64_t)b->prims.size();
-	c->extend_blocks[0] = 0;
+	c->extend_blocks[0] = 0; c->wt_valid = false;
 	CK(cudaStreamSynchronize(c->stream));   // the caller may destroy the cupt_bvh right after this call
 	return CUPT_OK;
 }
@@ -387,6 +406,7 @@ int cupt_build_bvh_device(cupt_context* c, const cupt_bvh_opts* opts, cupt_bvh_i
 	                                     (opts && opts->max_leaf_tris >= 1) ? opts->max_leaf_tris : 3, opts ? opts->ploc_radius : 0, &r);
 	c->d_nodes = (uint4*)r.nodes; c->d_prims = (float4*)r.prims;   // the builder may have replaced them even when it failed later
 	c->capacity[(void**)&c->d_nodes] = r.nodes_capacity_bytes; c->capacity[(void**)&c->d_prims] = r.prims_capacity_bytes;
+	c->wt_valid = false;
 	if (rc) { c->num_nodes = c->num_prims = 0; return rc; }
 	c->bvh_depth = r.depth; c->num_nodes = r.num_nodes; c->num_prims = r.num_prims;
 	c->extend_blocks[0] = 0;

@@ -268,10 +268,11 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 							const uint32_t kind = __float_as_uint(r2.w);
 							float t;
 							if (kind == 0u) t = tri_refexact(po, pd, r0, r1, r2);
+							else if (kind == 2u) t = tri_watertight(po, pd, r0, r1, r2);
 							else t = sphere_nearest(po, pd, r0, r1);
 							if (0.0f < t) {
 								hkey = ((unsigned long long)__float_as_uint(t) << 32) | __float_as_uint(r2.z);
-								hid = __float_as_uint(r2.y) | (kind << 31);
+								hid = __float_as_uint(r2.y) | ((kind & 1u) << 31);
 								atomicMin(&wkeys[owner], hkey);
 							}
 							if (STATS) ++n_tris;
@@ -548,6 +549,24 @@ __global__ void __launch_bounds__(256) k_accumulate(PassParams pp, PathBuffers p
 	}
 	float* a = accum + 3 * ((size_t)y * pp.cam.pxlWidth + x);
 	a[0] += sr; a[1] += sg; a[2] += sb;
+}
+
+// CUPT_TRI_WATERTIGHT: a second primitive array in the same order whose triangle records hold the three exact
+// vertices (kind 2) instead of v0, e1, e2
+__global__ void __launch_bounds__(256) k_vertex_prims(const float4* __restrict__ prims, const int64_t n, const float* __restrict__ verts,
+                                                      const cupt_triangle* __restrict__ tris, float4* __restrict__ out)
+{
+	const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float4 r0 = prims[3 * i], r1 = prims[3 * i + 1], r2 = prims[3 * i + 2];
+	if (__float_as_uint(r2.w) == 0u) {
+		const cupt_triangle t = tris[__float_as_uint(r2.y)];
+		const float* a = verts + 3 * (size_t)t.v0; const float* b = verts + 3 * (size_t)t.v1; const float* c = verts + 3 * (size_t)t.v2;
+		r0 = make_float4(a[0], a[1], a[2], b[0]);
+		r1 = make_float4(b[1], b[2], c[0], c[1]);
+		r2 = make_float4(c[2], r2.y, r2.z, __uint_as_float(2u));
+	}
+	out[3 * i] = r0; out[3 * i + 1] = r1; out[3 * i + 2] = r2;
 }
 
 // ---- parity hooks ----------------------------------------------------------------------------------------------

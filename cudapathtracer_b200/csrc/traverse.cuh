@@ -41,6 +41,55 @@ __device__ __forceinline__ float tri_refexact(const f3 o, const f3 d, const floa
 	return rdot(e2, r);
 }
 
+// Watertight ray-triangle test after Woop, Benthin, Wald, "Watertight Ray/Triangle Intersection" (JCGT 2013), for
+// records of kind 2 (a = v0, b = v1, c = v2: the exact vertices, not edges, so that two triangles sharing an edge see
+// the same numbers).  CUPT_TRI_WATERTIGHT only: NOT the reference's test (modelLoader.h:49-82 lets 5 of 1 048 576
+// primary rays of config 2 slip between triangles), so this mode is outside the bit-exact parity statement.
+// Every product and difference is individually rounded (an FMA would make the edge function of a shared edge
+// differ between its two triangles); an edge function that comes out as exactly 0 is re-evaluated in double.
+__device__ __forceinline__ float tri_watertight(const f3 o, const f3 d, const float4 r0, const float4 r1, const float4 r2)
+{
+	const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+	const int kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
+	const float dzc = kz == 0 ? d.x : (kz == 1 ? d.y : d.z);
+	const bool swp = dzc < 0.0f;   // keep the winding when the dominant component is negative
+#define CUPT_PERM(v, X, Y, Z)                                                   \
+	{                                                                           \
+		const float c0 = kz == 0 ? (v).y : (kz == 1 ? (v).z : (v).x);           \
+		const float c1 = kz == 0 ? (v).z : (kz == 1 ? (v).x : (v).y);           \
+		X = swp ? c1 : c0; Y = swp ? c0 : c1;                                   \
+		Z = kz == 0 ? (v).x : (kz == 1 ? (v).y : (v).z);                        \
+	}
+	float dx, dy, dz;
+	CUPT_PERM(d, dx, dy, dz)
+	const float Sx = rdiv(dx, dz), Sy = rdiv(dy, dz), Sz = rdiv(1.0f, dz);
+	const f3 A = rsub3(mk3(r0.x, r0.y, r0.z), o), B = rsub3(mk3(r0.w, r1.x, r1.y), o), C = rsub3(mk3(r1.z, r1.w, r2.x), o);
+	float Akx, Aky, Akz, Bkx, Bky, Bkz, Ckx, Cky, Ckz;
+	CUPT_PERM(A, Akx, Aky, Akz)
+	CUPT_PERM(B, Bkx, Bky, Bkz)
+	CUPT_PERM(C, Ckx, Cky, Ckz)
+#undef CUPT_PERM
+	const float Ax = rsub(Akx, rmul(Sx, Akz)), Ay = rsub(Aky, rmul(Sy, Akz));
+	const float Bx = rsub(Bkx, rmul(Sx, Bkz)), By = rsub(Bky, rmul(Sy, Bkz));
+	const float Cx = rsub(Ckx, rmul(Sx, Ckz)), Cy = rsub(Cky, rmul(Sy, Ckz));
+	float U = rsub(rmul(Cx, By), rmul(Cy, Bx));
+	float V = rsub(rmul(Ax, Cy), rmul(Ay, Cx));
+	float W = rsub(rmul(Bx, Ay), rmul(By, Ax));
+	if (U == 0.0f || V == 0.0f || W == 0.0f) {
+		U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+		V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+		W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+	}
+	if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f))
+		return CUPT_MAX_FLOAT;
+	const float det = radd(radd(U, V), W);
+	if (det == 0.0f)
+		return CUPT_MAX_FLOAT;
+	const float Az = rmul(Sz, Akz), Bz = rmul(Sz, Bkz), Cz = rmul(Sz, Ckz);
+	const float T = radd(radd(rmul(U, Az), rmul(V, Bz)), rmul(W, Cz));
+	return rdiv(T, det);   // <= 0 (behind the origin) is rejected by the caller's 0 < t
+}
+
 // analytic ray-sphere, nearest root with 0 < t (no reference code exists, sphere.h:7-13 is a POD only: PARITY
 // UNPINNED; the test-side CPU restatement repeats exactly this arithmetic).  Every operation is individually rounded.
 //   c = centre - o, dd = d.d, b = c.d, p = c - (b/dd) d (closest approach), disc = r^2 - p.p,
@@ -183,11 +232,12 @@ __device__ __forceinline__ void wide_prim_step(const float4* __restrict__ prims,
 	const uint32_t kind = __float_as_uint(r2.w);
 	float t;
 	if (kind == 0u) t = tri_refexact(r.o, r.d, r0, r1, r2);
+	else if (kind == 2u) t = tri_watertight(r.o, r.d, r0, r1, r2);
 	else t = sphere_nearest(r.o, r.d, r0, r1);
 	const uint32_t rank = __float_as_uint(r2.z);
 	if (0.0f < t && (t < r.best || (t == r.best && rank < r.best_rank))) {
 		r.best = t; r.best_rank = rank;
-		r.best_id = (int32_t)(__float_as_uint(r2.y) | (kind << 31));
+		r.best_id = (int32_t)(__float_as_uint(r2.y) | ((kind & 1u) << 31));
 	}
 }
 

@@ -171,7 +171,9 @@ enum { CUPT_TRAVERSAL_WIDE = 0, CUPT_TRAVERSAL_REF_BVH2 = 1 /* trace(), kernel.c
         * trace() bit for bit on every ray.  Needs cupt_set_bvh AND cupt_set_bvh2, a wide BVH built with the
         * cupt_bvh2_leaf_order ranks, and a scene without spheres. */
        CUPT_TRAVERSAL_WIDE_STRICT = 2 };
-enum { CUPT_TRI_REFEXACT = 0 /* triIntersect, modelLoader.h:49-82, bit-identical */, CUPT_TRI_WATERTIGHT = 1 };
+enum { CUPT_TRI_REFEXACT = 0 /* triIntersect, modelLoader.h:49-82, bit-identical */,
+       CUPT_TRI_WATERTIGHT = 1 /* Woop-Benthin-Wald test on exact vertices (wide traversal only): no ray slips between two
+                                  triangles that share an edge; NOT the reference's arithmetic, outside the parity statement */ };
 
 typedef struct cupt_render_opts {
 	int32_t max_depth;        /* NUM_BOUNCES (kernel.cu:33) made run-time: path segments per sample */
