@@ -175,6 +175,12 @@ class SceneHandle:
             self.add_shape(sh.positions, sh.indices, sh.material + first, origin, scale, flip)
         if getattr(scene, "spheres", None):
             self.add_spheres(spheres_array(scene.spheres))
+        for m in getattr(scene, "specular", ()):
+            self.set_specular(m + first)
+
+    def set_specular(self, material: int, specular: bool = True):
+        """mark a material as a perfect mirror (extension for BASELINE config 5; the reference is diffuse only)"""
+        _check(self.lib.cupt_scene_set_specular(self.h, int(material), int(specular)))
 
     def add_spheres(self, spheres: np.ndarray):
         spheres = np.ascontiguousarray(spheres, dtype=SPHERE)

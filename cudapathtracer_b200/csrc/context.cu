@@ -334,7 +334,7 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 	for (size_t i = 0; i < nm; ++i) {
 		for (int k = 0; k < 3; ++k) { mf[i].albedo[k] = (float)s->mats[i].albedo[k]; mf[i].emission[k] = (float)s->mats[i].emission[k]; }
 		mf[i].emissive_flag = s->mats[i].emission[0] != 0 ? 1.f : 0.f;  // kernel.cu:453 tests the f64 value
-		mf[i].pad = 0.f;
+		mf[i].specular_flag = (i < s->mat_specular.size() && s->mat_specular[i]) ? 1.f : 0.f;
 	}
 	if ((rc = upload(c, &c->d_mats, mf.data(), nm * sizeof(MatF)))) return rc;
 	// light table: per light v0, a1 = v1 - v0, a2 = v2 - v0 and area = length(cross(a1, a2)) / 2 (kernel.cu:472-477),

@@ -46,6 +46,7 @@ struct cupt_scene {
 	std::vector<int32_t> lights;
 	float totalLightArea = 0.f;
 	std::vector<cupt_sphere> spheres;
+	std::vector<uint8_t> mat_specular;   // optional, per material: 1 = perfect mirror (not in the reference; cupt_scene_set_specular)
 };
 
 namespace cupt {

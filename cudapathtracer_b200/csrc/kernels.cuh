@@ -468,9 +468,12 @@ __global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathB
 				slot_to_pixel(pp, slot, x, y, sl);
 				PhiloxStream rng;
 				rng.init(pp.seed, (uint32_t)x, (uint32_t)y, (uint32_t)(pp.first_sample + sl));
-				const float a = rng.draw(draw++);                                    // kernel.cu:459
 				f3 lDir;
-				if (a < 0.5f) {
+				if (m1.w != 0.f && id >= 0) {
+					// perfect mirror (extension, config 5; no reference code): d - 2 (d.n) n, weight *= albedo, no random numbers
+					lDir = rnormalized(rsub3(d, rmul3(normal, rmul(2.0f, rdot(d, normal)))));
+					wr *= m0.x; wg *= m0.y; wb *= m0.z;
+				} else if (rng.draw(draw++) < 0.5f) {                                // kernel.cu:459
 					// cosineWeightedRay, kernel.cu:78-99
 					const float u1 = rng.draw(draw++), u2 = rng.draw(draw++);
 					const float r = __fsqrt_rn(u1);

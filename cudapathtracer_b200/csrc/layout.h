@@ -60,7 +60,7 @@ struct alignas(16) MatF {       // per material (modelLoader.h:21-25)
 	float albedo[3];
 	float emissive_flag;        // 1 when emission.r != 0 in f64 (modelLoader.h:191, kernel.cu:453)
 	float emission[3];
-	float pad;
+	float specular_flag;        // 1 = perfect mirror (an extension: the reference has diffuse materials only)
 };
 struct alignas(16) LightTri {   // per light triangle (+ one fallback entry for triangle 0, kernel.cu:469)
 	float v0[3];

@@ -101,7 +101,7 @@ int cupt_scene_clear(cupt_scene* s)
 {
 	if (!s)
 		return set_error(CUPT_ERR_INVALID, "null scene");
-	s->verts.clear(); s->tris.clear(); s->mats.clear(); s->lights.clear(); s->spheres.clear();
+	s->verts.clear(); s->tris.clear(); s->mats.clear(); s->lights.clear(); s->spheres.clear(); s->mat_specular.clear();
 	s->totalLightArea = 0.f;
 	return CUPT_OK;
 }
@@ -214,7 +214,7 @@ int cupt_scene_load_obj(cupt_scene* s, const char* path, const char* mtl_dir, co
 namespace {
 struct CacheHeader {
 	char magic[8];            // "CUPTSCN1"
-	uint64_t nverts, ntris, nmats, nlights, nspheres;
+	uint64_t nverts, ntris, nmats, nlights, nspheres, nflags;
 	float totalLightArea;
 	uint32_t pod_sizes;       // sizeof(vec3) | sizeof(triangle) << 8 | sizeof(material) << 16 | sizeof(sphere) << 24
 };
@@ -237,7 +237,7 @@ int cupt_scene_save(const cupt_scene* s, const char* path)
 	CacheHeader h;
 	memset(&h, 0, sizeof(h));
 	memcpy(h.magic, "CUPTSCN1", 8);
-	h.nverts = s->verts.size(); h.ntris = s->tris.size(); h.nmats = s->mats.size(); h.nlights = s->lights.size(); h.nspheres = s->spheres.size();
+	h.nverts = s->verts.size(); h.ntris = s->tris.size(); h.nmats = s->mats.size(); h.nlights = s->lights.size(); h.nspheres = s->spheres.size(); h.nflags = s->mat_specular.size();
 	h.totalLightArea = s->totalLightArea; h.pod_sizes = kPodSizes;
 	uint64_t sum = fnv1a(14695981039346656037ull, &h, sizeof(h));
 	bool ok = fwrite(&h, sizeof(h), 1, fp) == 1;
@@ -251,6 +251,7 @@ int cupt_scene_save(const cupt_scene* s, const char* path)
 	put(s->mats.data(), s->mats.size() * sizeof(cupt_material));
 	put(s->lights.data(), s->lights.size() * sizeof(int32_t));
 	put(s->spheres.data(), s->spheres.size() * sizeof(cupt_sphere));
+	put(s->mat_specular.data(), s->mat_specular.size());
 	ok = ok && fwrite(&sum, sizeof(sum), 1, fp) == 1;
 	ok = (fclose(fp) == 0) && ok;
 	return ok ? CUPT_OK : set_error(CUPT_ERR_IO, "write to %s failed", path);
@@ -269,7 +270,7 @@ int cupt_scene_load(cupt_scene* s, const char* path)
 		return set_error(CUPT_ERR_PARSE, "%s is not a scene cache of this library version", path);
 	}
 	const uint64_t lim = 0x7fffffffull;
-	if (h.nverts > lim || h.ntris > lim || h.nmats > lim || h.nlights > h.ntris || h.nspheres > lim) {
+	if (h.nverts > lim || h.ntris > lim || h.nmats > lim || h.nlights > h.ntris || h.nspheres > lim || h.nflags > h.nmats) {
 		fclose(fp);
 		return set_error(CUPT_ERR_PARSE, "%s: implausible counts in the header", path);
 	}
@@ -282,7 +283,7 @@ int cupt_scene_load(cupt_scene* s, const char* path)
 		if (ok) sum = fnv1a(sum, p, bytes);
 	};
 	try {
-		t.verts.resize(h.nverts); t.tris.resize(h.ntris); t.mats.resize(h.nmats); t.lights.resize(h.nlights); t.spheres.resize(h.nspheres);
+		t.verts.resize(h.nverts); t.tris.resize(h.ntris); t.mats.resize(h.nmats); t.lights.resize(h.nlights); t.spheres.resize(h.nspheres); t.mat_specular.resize(h.nflags);
 	} catch (...) {
 		fclose(fp);
 		return set_error(CUPT_ERR_NOMEM, "out of memory reading %s", path);
@@ -292,6 +293,7 @@ int cupt_scene_load(cupt_scene* s, const char* path)
 	get(t.mats.data(), t.mats.size() * sizeof(cupt_material));
 	get(t.lights.data(), t.lights.size() * sizeof(int32_t));
 	get(t.spheres.data(), t.spheres.size() * sizeof(cupt_sphere));
+	get(t.mat_specular.data(), t.mat_specular.size());
 	uint64_t stored = 0;
 	ok = ok && fread(&stored, sizeof(stored), 1, fp) == 1;
 	fclose(fp);
@@ -304,8 +306,17 @@ int cupt_scene_load(cupt_scene* s, const char* path)
 	for (int32_t l : t.lights)
 		if (l < 0 || (uint64_t)l >= h.ntris) return set_error(CUPT_ERR_PARSE, "%s: light index outside the triangle array", path);
 	t.totalLightArea = h.totalLightArea;
-	s->verts.swap(t.verts); s->tris.swap(t.tris); s->mats.swap(t.mats); s->lights.swap(t.lights); s->spheres.swap(t.spheres);
+	s->verts.swap(t.verts); s->tris.swap(t.tris); s->mats.swap(t.mats); s->lights.swap(t.lights); s->spheres.swap(t.spheres); s->mat_specular.swap(t.mat_specular);
 	s->totalLightArea = t.totalLightArea;
+	return CUPT_OK;
+}
+
+int cupt_scene_set_specular(cupt_scene* s, int material, int specular)
+{
+	if (!s || material < 0 || material >= (int)s->mats.size())
+		return set_error(CUPT_ERR_INVALID, "material %d outside the table", material);
+	if (s->mat_specular.size() < s->mats.size()) s->mat_specular.resize(s->mats.size(), 0);
+	s->mat_specular[(size_t)material] = specular ? 1 : 0;
 	return CUPT_OK;
 }
 

@@ -32,6 +32,7 @@ class Scene:
     shapes: List[Shape]
     camera: dict  # pos, distFromFilm, focalLength, radius (reference camera.h:26-35)
     spheres: list = dataclasses.field(default_factory=list)  # (centre xyz, radius, diffuse rgb, emm rgb): sphere.h:7-13
+    specular: list = dataclasses.field(default_factory=list)  # material indices that are perfect mirrors (config 5; not in the reference)
 
     @property
     def num_triangles(self) -> int:
@@ -148,7 +149,7 @@ def arch(x, z0, z1, y_spring, thickness, depth, nseg):
 REFERENCE_CAMERA = dict(pos=(0.0, 1.0, 3.0), distFromFilm=1.0, focalLength=3.0, radius=0.0)  # kernel.cu:642-646
 
 
-def cornell_box(extra_lights: int = 0, spheres: bool = False) -> Scene:
+def cornell_box(extra_lights: int = 0, spheres: bool = False, specular: bool = False) -> Scene:
     """McGuire-style Cornell box: 32 triangles, all normals facing the room.
     `extra_lights` > 0 adds that many small emissive triangles under the ceiling (config 5 needs >= 8
     emissive triangles)."""
@@ -182,7 +183,8 @@ def cornell_box(extra_lights: int = 0, spheres: bool = False) -> Scene:
     if spheres:   # config 1: "Cornell-box sphere scene (sphere.h)": a diffuse sphere on the short box, an emissive one in the air
         sph = [((0.33, 0.85, 0.37), 0.25, (0.5, 0.75, 0.25), (0.0, 0.0, 0.0)),
                ((-0.6, 1.5, 0.3), 0.125, (0.75, 0.75, 0.75), (4.0, 3.0, 2.0))]
-    return Scene(mats, shapes, dict(REFERENCE_CAMERA), sph)
+    # config 5 ("mixed diffuse/specular"): the tall box and the back wall become mirrors
+    return Scene(mats, shapes, dict(REFERENCE_CAMERA), sph, [6, 2] if specular else [])
 
 
 def atrium(n_tris: int = 262144, seed: int = 1) -> Scene:

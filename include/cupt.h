@@ -102,6 +102,9 @@ int cupt_scene_add_shape_facemats(cupt_scene* s, const float* positions, int nve
                                   int ntris, const int32_t* face_materials, const float origin[3], float scale,
                                   int flip_normals);
 /* spheres: sphere.h:7-13 has the POD only; the intersector is new (parity unpinned) */
+/* BASELINE config 5 ("mixed diffuse/specular"): mark a material as a perfect mirror.  NOT in the reference (all its
+ * materials are diffuse, kernel.cu:101-104); honoured by CUPT_INTEGRATOR_PT only; parity unpinned. */
+int cupt_scene_set_specular(cupt_scene* s, int material, int specular);
 int cupt_scene_add_spheres(cupt_scene* s, const cupt_sphere* spheres, int n);
 /* raw access to the arrays in reference layout */
 int cupt_scene_set_arrays(cupt_scene* s, const cupt_vec3* verts, int nverts, const cupt_triangle* tris, int ntris,

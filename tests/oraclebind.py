@@ -17,7 +17,7 @@ class _Scene(C.Structure):
     _fields_ = [("verts", C.c_void_p), ("tris", C.c_void_p), ("mats", C.c_void_p), ("lights", C.c_void_p),
                 ("numVerts", C.c_int32), ("numTris", C.c_int32), ("numMats", C.c_int32), ("numLights", C.c_int32),
                 ("totalLightArea", C.c_float), ("nodes", C.c_void_p), ("numNodes", C.c_int32),
-                ("spheres", C.c_void_p), ("numSpheres", C.c_int32)]
+                ("spheres", C.c_void_p), ("numSpheres", C.c_int32), ("mat_specular", C.c_void_p)]
 
 
 _lib = None
@@ -44,7 +44,7 @@ def _p(a):
 class OracleScene:
     """scene arrays in reference layout + a reference-layout BVH2 node array"""
 
-    def __init__(self, verts, tris, mats, lights, total_light_area, nodes, spheres=None):
+    def __init__(self, verts, tris, mats, lights, total_light_area, nodes, spheres=None, specular=None):
         self.verts = np.ascontiguousarray(verts, dtype=VEC3)
         self.tris = np.ascontiguousarray(tris, dtype=TRIANGLE)
         self.mats = np.ascontiguousarray(mats, dtype=MATERIAL)
@@ -52,7 +52,11 @@ class OracleScene:
         self.nodes = np.ascontiguousarray(nodes, dtype=BVH2_NODE)
         self.c = _Scene(self.verts.ctypes.data, self.tris.ctypes.data, self.mats.ctypes.data, self.lights.ctypes.data,
                         len(self.verts), len(self.tris), len(self.mats), len(self.lights),
-                        float(total_light_area), self.nodes.ctypes.data, len(self.nodes), None, 0)
+                        float(total_light_area), self.nodes.ctypes.data, len(self.nodes), None, 0, None)
+        if specular is not None and len(specular):   # material indices that are perfect mirrors (extension, unpinned)
+            self.specular = np.zeros(len(self.mats), dtype=np.uint8)
+            self.specular[np.asarray(specular, dtype=np.int64)] = 1
+            self.c.mat_specular = self.specular.ctypes.data
         if spheres is not None and len(spheres):
             self.spheres = np.ascontiguousarray(spheres, dtype=SPHERE)
             self.c.spheres, self.c.numSpheres = self.spheres.ctypes.data, len(self.spheres)

@@ -517,3 +517,25 @@ def test_watertight_triangle_test(ctx, get_case):
     assert np.all(np.abs(wt[both] - rt[both]) <= 2e-5 * rt[both])
     assert abs(wt_img.mean() - ref_img.mean()) <= 0.02 * ref_img.mean()
     print("rays through shared edges lost by the reference test:", slipped, "of", len(rays))
+
+
+def test_specular_materials_config5(ctx, get_case):
+    """BASELINE config 5: Cornell box with triangle lights and mixed diffuse / mirror materials at max depth 16.  The
+    mirror is an extension (the reference has diffuse materials only): PARITY UNPINNED, checked against the oracle's
+    restatement of the same rule (d - 2 (d.n) n, weight *= albedo, no random numbers) with the path tracer's tolerances."""
+    c = get_case("cornell_specular")
+    plain = get_case("cornell_lights")
+    spp, seed, nb = 4, 21, 16
+    _, osum, orays = c.osc.render_pt(c.cam, nb, seed, 0, spp)
+    _, psum, _ = plain.osc.render_pt(plain.cam, nb, seed, 0, spp)
+    want = osum / spp
+    assert np.abs(osum - psum).max() > 0.1                                            # the mirrors change the image
+    for mode, frac, rel_tol in ((api.TRAVERSAL_REF_BVH2, 0.999, 0.01), (api.TRAVERSAL_WIDE, 0.98, 0.15)):
+        load(ctx, c, mode, max_depth=nb, seed=seed, collect_stats=1)
+        ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, spp)
+        img = ctx.read_accum(True).astype(np.float64)
+        close = np.all(np.abs(img - want) <= 1e-3 * (1 + np.abs(want)), axis=1)
+        rel = np.sqrt(((img - want) ** 2).mean()) / want.mean()
+        assert close.mean() >= frac and rel <= rel_tol, (mode, close.mean(), rel)
+        assert 0.3 * orays < ctx.stats()["rays"] <= orays
+    ctx.set_options(collect_stats=0, max_depth=5)
