@@ -188,9 +188,14 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--traversal", default="wide", choices=["wide", "strict", "ref"], help="wide (default), strict = wide + reference-equality check, ref = the reference algorithm on its own BVH2")
     ap.add_argument("--integrator", default="pt", choices=["pt", "bdpt"], help="pt = radianceAlongSingleStep2 with max depth 5 (the metric's config); bdpt = the reference's live radianceAlongSingleStep (what the legacy kernel.cu runs)")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3], help="BASELINE.json config: 2 (default: 1024^2, 64 spp per GPU, weak scaling) or 3 (3840x2160, 1024 spp split over the GPUs, strong scaling)")
     ap.add_argument("--tri-test", default="refexact", choices=["refexact", "watertight"], help="refexact = the reference's triIntersect bit for bit (default); watertight = Woop et al. on exact vertices")
     ap.add_argument("--bvh", default="host", choices=["host", "device"], help="host = binned-SAH builder (OpenMP), uploaded; device = cupt_build_bvh_device, rebuilt inside every e2e step")
     args = ap.parse_args()
+    global W, H, SPP, WORKLOAD
+    if args.config == 3:
+        W, H, SPP = 3840, 2160, 1024
+        WORKLOAD = f"atrium {NTRIS} tris (procedural, seed 1), {W}x{H}, {SPP} spp over all GPUs, max depth {DEPTH}, seed {SEED}"
     if args.impl == "reference":
         return run_reference_arm(args)
 
@@ -234,11 +239,17 @@ def main():
     accum_t = torch.zeros(W * H * 3, dtype=torch.float32, device="cuda")
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
     from cudapathtracer_b200 import sharding
-    first, _ = sharding.weak_sample_range(rank, SPP)
+    if args.config == 3:   # strong scaling: the frame's samples are split over the ranks
+        first, spp_rank = sharding.sample_range(rank, world, SPP)
+        samples_step = W * H * SPP
+    else:
+        first, _ = sharding.weak_sample_range(rank, SPP)
+        spp_rank = SPP
+        samples_step = W * H * SPP * world
 
     def step():
         ctx.reset_accum()
-        ctx.render(first, SPP)
+        ctx.render(first, spp_rank)
         if world > 1:
             ctx.copy_accum_device(accum_t.data_ptr())
             sharding.reduce_accumulators(accum_t, dst=0)
@@ -299,7 +310,7 @@ def main():
             ctx.set_bvh(bvh)
         if n2 is not None:
             ctx.set_bvh2(n2, d2)
-        ctx.reset_accum(); ctx.render(first, SPP)
+        ctx.reset_accum(); ctx.render(first, spp_rank)
         if world > 1:
             ctx.copy_accum_device(accum_t.data_ptr())
             dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
@@ -327,14 +338,14 @@ def main():
         achieved = bytes_step * args.steps / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None
         line = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong" if args.config == 3 else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "traversal": args.traversal, "integrator": args.integrator, "tri_test": args.tri_test, "parallelism": f"sample ranges x{world}, replicated BVH, NCCL reduce of f32 accumulators",
                        "l2": "L2 flushed (256 MiB write) between timed steps; per-step path state (64 Mi paths x 72 B = 4.8 GB) exceeds the 126 MB L2, the 16 MB BVH is L2-resident within a step by design",
                        "bvh": {"builder": args.bvh, "nodes": info["num_nodes"], "prims": info["num_tri_records"], "depth": info["depth"], "build_s_host": build_s,
                                "build_ms_device": None if dev_info is None else {k: v for k, v in dev_info.items() if k.startswith("ms_")}}},
-            "msamples_per_s": W * H * SPP * world * args.steps / (ms_total * 1e-3) / 1e6,
-            "rays_per_step_per_gpu": rays_step, "rays_per_sample": rays_step / (W * H * SPP),
+            "msamples_per_s": samples_step * args.steps / (ms_total * 1e-3) / 1e6,
+            "rays_per_step_per_gpu": rays_step, "rays_per_sample": rays_step / (W * H * spp_rank),
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": n_e2e},
             "gpu_launches": int(st["kernel_launches"]),

@@ -12,6 +12,7 @@
 #include <atomic>
 #include <chrono>
 #include <cstring>
+#include <cstdlib>
 #include <omp.h>
 
 namespace cupt {
@@ -185,6 +186,46 @@ int cupt_bvh_build(const cupt_scene* s, const cupt_bvh_opts* opts, cupt_bvh** ou
 	if (!bvh)
 		return set_error(CUPT_ERR_NOMEM, "out of memory");
 	bvh->num_tris = nt; bvh->num_spheres = ns;
+	// ---- cost-optimal collapse (after Ylitie, Karras, Laine 2017, section 3.1) --------------------------------
+	// c[i] = cheapest way to hang the subtree of a binary node under a wide node using at most i of its slots:
+	//   leaf:      A * P * c_prim                                   (binary leaves hold <= max_leaf primitives)
+	//   c[1]:      A * c_node + D[8]      the subtree becomes a wide node of its own
+	//   c[i>1]:    min(D[i], c[i-1]),     D[j] = min_k c_left[k] + c_right[j-k]
+	// The greedy rule (open the largest child until there are eight) left 45 % of config 2's nodes with two children.
+	struct Dp { float c[8]; uint8_t split[9]; };
+	const char* env_collapse = getenv("CUPT_COLLAPSE");
+	const bool use_dp = !(env_collapse && strcmp(env_collapse, "greedy") == 0);
+	const char* env_cp = getenv("CUPT_COLLAPSE_CPRIM");
+	const float c_prim = env_cp ? (float)atof(env_cp) : 0.3f, c_node = 1.0f;
+	std::vector<Dp> dp;
+	if (use_dp) {
+		const int32_t n2count = B.next.load();
+		dp.resize((size_t)n2count);
+		for (int32_t i = n2count - 1; i >= 0; --i) {   // children are allocated after their parent: descending = bottom-up
+			const Node2& n = B.nodes[(size_t)i];
+			Dp& d = dp[(size_t)i];
+			const float A = (float)n.box.area();
+			if (n.left < 0) {
+				for (int k = 0; k < 8; ++k) d.c[k] = A * (float)n.count * c_prim;
+				memset(d.split, 0, sizeof(d.split));
+				continue;
+			}
+			const Dp& l = dp[(size_t)n.left];
+			const Dp& r = dp[(size_t)n.right];
+			float D[9];
+			for (int j = 2; j <= 8; ++j) {
+				float best = 3.0e38f; int bk = 1;
+				for (int k = 1; k < j; ++k) {
+					const float v = l.c[std::min(k, 7)] + r.c[std::min(j - k, 7)];
+					if (v < best) { best = v; bk = k; }
+				}
+				D[j] = best; d.split[j] = (uint8_t)bk;
+			}
+			d.c[0] = 0.f;
+			d.c[1] = A * c_node + D[8];
+			for (int k = 2; k <= 7; ++k) d.c[k] = std::min(D[k], d.c[k - 1]);
+		}
+	}
 	struct Pending { int32_t n2; int32_t depth; };
 	std::vector<Pending> queue;
 	queue.push_back({0, 1});
@@ -202,6 +243,23 @@ int cupt_bvh_build(const cupt_scene* s, const cupt_bvh_opts* opts, cupt_bvh** ou
 		int nk = 0;
 		if (n2.left < 0) {
 			kids[nk++] = cur.n2;  // root is a leaf: one leaf child
+		} else if (use_dp) {
+			// cost-optimal cut below this node (dp[] above): distribute the eight slots over the two subtrees
+			struct Frame { int32_t n; int budget; };
+			Frame st[64]; int sp = 0;
+			const int k8 = dp[(size_t)cur.n2].split[8];
+			st[sp++] = {n2.right, 8 - k8}; st[sp++] = {n2.left, k8};
+			while (sp > 0) {
+				const Frame f = st[--sp];
+				const Node2& m = B.nodes[f.n];
+				if (m.left < 0) { kids[nk++] = f.n; continue; }
+				int i = std::min(f.budget, 7);
+				const Dp& d = dp[(size_t)f.n];
+				while (i > 1 && d.c[i] == d.c[i - 1]) --i;
+				if (i == 1) { kids[nk++] = f.n; continue; }     // a wide node of its own
+				const int k = d.split[i];
+				st[sp++] = {m.right, i - k}; st[sp++] = {m.left, k};
+			}
 		} else {
 			kids[nk++] = n2.left; kids[nk++] = n2.right;
 			while (nk < 8) {
