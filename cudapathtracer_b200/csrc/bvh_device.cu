@@ -10,9 +10,10 @@
 //                       §4) whose union box has the smallest area; mutual pairs
 //                       merge; an order-preserving compaction closes the gaps.  Four launches per round
 //                       (k_ploc_nearest, k_ploc_count, k_scan_tiles, k_ploc_merge), ~log_1.5(N) rounds.
-//   4. collapse + emit  level by level from the root: open the child with the largest area until there are eight
-//                       (same rule as the host builder), octant-slot assignment, 8-bit quantisation, breadth-first
-//                       emission (k_collapse_count, k_scan_tiles, k_collapse_emit per level).
+//   4. collapse + emit  level by level from the root: the cost-optimal cut of every wide node (dynamic programme over
+//                       slot budgets, filled in by k_ploc_merge as nodes are created; same rule as the host builder),
+//                       octant-slot assignment, 8-bit quantisation, breadth-first emission (k_collapse_count,
+//                       k_scan_tiles, k_collapse_emit per level).
 //
 // The tree differs from the host builder's (binned SAH), the traversal result does not: k_extend returns the argmin
 // over all primitives whatever the tree (tests/test_gpu_parity.py compares with the brute force bit for bit).
@@ -231,9 +232,34 @@ __global__ void __launch_bounds__(kTile) k_ploc_count(const uint32_t* __restrict
 	if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
 }
 
+// Cost-optimal collapse (Ylitie, Karras, Laine 2017, section 3.1; the host builder does the same, bvh8_build.cpp):
+// c[i-1] = cheapest way to hang the subtree under a wide node using at most i of its slots (i = 1..7), splits = for
+// j = 2..8 the number of slots that go to the left child, 3 bits each.  A subtree of at most max_leaf primitives is a
+// leaf slot: A * P * c_prim for every i.  Filled in by k_ploc_merge the moment a node is created (its children are
+// complete subtrees by then), read by gather_kids top-down.
+struct alignas(16) Dp { float c[7]; uint32_t splits; };
+constexpr float kCostNode = 1.0f, kCostPrim = 0.3f;
+
+__device__ __forceinline__ void dp_of(const Dp* __restrict__ dp, const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt,
+                                      const uint32_t id, const uint32_t max_leaf, float c[8])
+{
+	const uint32_t n = cnt[id];
+	if (n <= max_leaf) {
+		const float4* p = reinterpret_cast<const float4*>(&nodes[id]);
+		const float4 a = p[0], b = p[1];
+		const float v = half_area(a.x, a.y, a.z, b.x, b.y, b.z) * (float)n * kCostPrim;
+#pragma unroll
+		for (int i = 1; i <= 7; ++i) c[i] = v;
+	} else {
+		const float4* p = reinterpret_cast<const float4*>(&dp[id]);
+		const float4 a = p[0], b = p[1];
+		c[1] = a.x; c[2] = a.y; c[3] = a.z; c[4] = a.w; c[5] = b.x; c[6] = b.y; c[7] = b.z;
+	}
+}
+
 __global__ void __launch_bounds__(kTile) k_ploc_merge(N2* __restrict__ nodes, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ cid_in,
                                                       uint32_t* __restrict__ cid_out, const uint32_t* __restrict__ nn, const int n,
-                                                      const uint64_t* __restrict__ tile_offs, const uint32_t node_base)
+                                                      const uint64_t* __restrict__ tile_offs, const uint32_t node_base, Dp* __restrict__ dp, const uint32_t max_leaf)
 {
 	__shared__ uint64_t s_warp[kTile / 32 + 1];
 	const int i = (int)blockIdx.x * kTile + threadIdx.x;
@@ -253,8 +279,35 @@ __global__ void __launch_bounds__(kTile) k_ploc_merge(N2* __restrict__ nodes, ui
 		float4 ob = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), __int_as_float((int32_t)r));
 		float4* po = reinterpret_cast<float4*>(&nodes[id]);
 		po[0] = oa; po[1] = ob;
-		cnt[id] = cnt[l] + cnt[r];
+		const uint32_t total = cnt[l] + cnt[r];
+		cnt[id] = total;
 		cid_out[out] = id;
+		if (total > max_leaf) {
+			float cl[8], cr[8];
+			dp_of(dp, nodes, cnt, l, max_leaf, cl);
+			dp_of(dp, nodes, cnt, r, max_leaf, cr);
+			Dp d;
+			uint32_t splits = 0u;
+			float D8 = 0.f;
+#pragma unroll
+			for (int j = 2; j <= 8; ++j) {
+				float best = 3.0e38f; uint32_t bk = 1u;
+#pragma unroll
+				for (int k = 1; k < j; ++k) {
+					const float v = cl[k < 7 ? k : 7] + cr[(j - k) < 7 ? (j - k) : 7];
+					if (v < best) { best = v; bk = (uint32_t)k; }
+				}
+				splits |= bk << (3 * (j - 2));
+				if (j <= 7) d.c[j - 1] = best; else D8 = best;
+			}
+			d.c[0] = half_area(oa.x, oa.y, oa.z, ob.x, ob.y, ob.z) * kCostNode + D8;
+#pragma unroll
+			for (int i = 1; i < 7; ++i) d.c[i] = fminf(d.c[i], d.c[i - 1]);
+			d.splits = splits;
+			float4* pd = reinterpret_cast<float4*>(&dp[id]);
+			pd[0] = make_float4(d.c[0], d.c[1], d.c[2], d.c[3]);
+			pd[1] = make_float4(d.c[4], d.c[5], d.c[6], __uint_as_float(d.splits));
+		}
 	} else {
 		cid_out[out] = cid_in[i];
 	}
@@ -270,30 +323,37 @@ __device__ __forceinline__ float node_half_area(const N2* __restrict__ nodes, co
 	return half_area(a.x, a.y, a.z, b.x, b.y, b.z);
 }
 
-// the children of one wide node: start from the binary node's two children and keep opening the inner child with the
-// largest area (bvh8_build.cpp does the same); a subtree with at most max_leaf primitives is a leaf and is not opened
-__device__ __forceinline__ void gather_kids(const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt, const int32_t root, const uint32_t max_leaf, Kids& k)
+// the children of one wide node: the cost-optimal cut below the binary node `root` (Dp above); a subtree with at most
+// max_leaf primitives is a leaf slot.  Children come out in left-first order.
+__device__ __forceinline__ void gather_kids(const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt, const Dp* __restrict__ dp,
+                                            const int32_t root, const uint32_t max_leaf, Kids& k)
 {
+	k.n = 0;
 	if (cnt[root] <= max_leaf) { k.id[0] = root; k.n = 1; return; }
-	float area[8];
-	k.id[0] = nodes[root].left; k.id[1] = nodes[root].right; k.n = 2;
-#pragma unroll
-	for (int q = 0; q < 2; ++q) area[q] = cnt[k.id[q]] > max_leaf ? node_half_area(nodes, k.id[q]) : -1.f;
-	while (k.n < 8) {
-		int best = -1; float ba = -1.f;
-		for (int q = 0; q < k.n; ++q)
-			if (area[q] > ba) { ba = area[q]; best = q; }
-		if (best < 0) break;
-		const int32_t open = k.id[best];
-		const int32_t l = nodes[open].left, r = nodes[open].right;
-		k.id[best] = l; area[best] = cnt[l] > max_leaf ? fmaxf(node_half_area(nodes, l), 0.f) : -1.f;
-		k.id[k.n] = r; area[k.n] = cnt[r] > max_leaf ? fmaxf(node_half_area(nodes, r), 0.f) : -1.f;
-		k.n++;
+	int32_t st_n[16]; int st_b[16]; int sp = 0;
+	{
+		const int k8 = (int)((dp[root].splits >> 18) & 7u);
+		st_n[sp] = nodes[root].right; st_b[sp++] = 8 - k8;
+		st_n[sp] = nodes[root].left; st_b[sp++] = k8;
+	}
+	while (sp > 0) {
+		--sp;
+		const int32_t n = st_n[sp];
+		int i = min(st_b[sp], 7);
+		if (cnt[n] <= max_leaf) { k.id[k.n++] = n; continue; }
+		const float4* p = reinterpret_cast<const float4*>(&dp[n]);
+		const float4 a = __ldg(p), b = __ldg(p + 1);
+		const float c[8] = {0.f, a.x, a.y, a.z, a.w, b.x, b.y, b.z};
+		while (i > 1 && c[i] == c[i - 1]) --i;
+		if (i == 1) { k.id[k.n++] = n; continue; }   // a wide node of its own
+		const int kl = (int)((__float_as_uint(b.w) >> (3 * (i - 2))) & 7u);
+		st_n[sp] = nodes[n].right; st_b[sp++] = i - kl;
+		st_n[sp] = nodes[n].left; st_b[sp++] = kl;
 	}
 }
 
 // per item of the level: (inner children | leaf primitives << 32), reduced to one sum per tile
-__global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt, const int32_t* __restrict__ items,
+__global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt, const Dp* __restrict__ dp, const int32_t* __restrict__ items,
                                                           const int n_items, const uint32_t max_leaf, uint64_t* __restrict__ item_counts, uint64_t* __restrict__ tile_sums)
 {
 	__shared__ uint64_t s_warp[kTile / 32 + 1];
@@ -301,7 +361,7 @@ __global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__
 	uint64_t f = 0;
 	if (i < n_items) {
 		Kids k;
-		gather_kids(nodes, cnt, items[i], max_leaf, k);
+		gather_kids(nodes, cnt, dp, items[i], max_leaf, k);
 		uint32_t ni = 0, np = 0;
 		for (int q = 0; q < k.n; ++q) {
 			const uint32_t c = cnt[k.id[q]];
@@ -340,7 +400,7 @@ __device__ __forceinline__ void write_prim(const int32_t prim, const int64_t nt,
 }
 
 struct EmitArgs {
-	const N2* nodes; const uint32_t* cnt; const int32_t* items; int n_items; uint32_t max_leaf;
+	const N2* nodes; const uint32_t* cnt; const Dp* dp; const int32_t* items; int n_items; uint32_t max_leaf;
 	const uint64_t* item_counts; const uint64_t* tile_offs;
 	uint32_t level_base, next_base, prim_base;
 	int32_t* next_items; Node8* out_nodes; float4* out_prims;
@@ -358,7 +418,7 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 	if (i >= A.n_items) return;
 	const int32_t self = A.items[i];
 	Kids k;
-	gather_kids(A.nodes, A.cnt, self, A.max_leaf, k);
+	gather_kids(A.nodes, A.cnt, A.dp, self, A.max_leaf, k);
 	float blo[3], bhi[3];
 	{
 		const float4* p = reinterpret_cast<const float4*>(&A.nodes[self]);
@@ -521,7 +581,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	// everything the build touches except its two outputs, in one arena; the sort buffers are dead once the sorted
 	// leaves are written, the collapse reuses the cluster arrays for its level queues
 	const size_t need = up256(n * sizeof(N2)) + up256(64) + 2 * up256(n * 8) + 2 * up256(n * 4) + up256(temp_bytes + 256)
-	                    + up256(2 * n * sizeof(N2)) + up256(2 * n * 4) + 3 * up256(n * 4) + up256(((size_t)tilesN + 1) * 8) + up256(64)
+	                    + up256(2 * n * sizeof(N2)) + up256(2 * n * sizeof(Dp)) + up256(2 * n * 4) + 3 * up256(n * 4) + up256(((size_t)tilesN + 1) * 8) + up256(64)
 	                    + up256((n / 2 + 2) * 8) + up256(64) + 4096;
 	int rc;
 	if ((rc = arena.reserve(need))) return rc;
@@ -548,6 +608,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	// 3: PLOC
 	N2* nodes = take<N2>(arena, 2 * n);
 	uint32_t* cnt = take<uint32_t>(arena, 2 * n);
+	Dp* dp = take<Dp>(arena, 2 * n);
 	uint32_t* cid[2] = {take<uint32_t>(arena, n), take<uint32_t>(arena, n)};
 	uint32_t* nn = take<uint32_t>(arena, n);
 	uint64_t* tile_sums = take<uint64_t>(arena, (size_t)tilesN + 1);
@@ -570,7 +631,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 		}
 		k_ploc_count<<<tiles, kTile, 0, st>>>(nn, cn, tile_sums);
 		k_scan_tiles<<<1, kTile, 0, st>>>(tile_sums, tiles, d_total);
-		k_ploc_merge<<<tiles, kTile, 0, st>>>(nodes, cnt, cid[cur], cid[cur ^ 1], nn, cn, tile_sums, node_base);
+		k_ploc_merge<<<tiles, kTile, 0, st>>>(nodes, cnt, cid[cur], cid[cur ^ 1], nn, cn, tile_sums, node_base, dp, (uint32_t)max_leaf);
 		CKB(cudaMemcpyAsync(h_total, d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
 		CKB(cudaStreamSynchronize(st));
 		const uint32_t valid = (uint32_t)*h_total, leaders = (uint32_t)(*h_total >> 32);
@@ -594,10 +655,10 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 		CKB(cudaMalloc(&out->prims, n * 48));
 		out->prims_capacity_bytes = n * 48;
 	}
-	if (out->nodes_capacity_bytes < (n / 3 + 1024) * sizeof(Node8)) {
+	if (out->nodes_capacity_bytes < (n / 4 + 64) * sizeof(Node8)) {
 		if (out->nodes) { CKB(cudaFree(out->nodes)); out->nodes = nullptr; out->nodes_capacity_bytes = 0; }
-		CKB(cudaMalloc(&out->nodes, (n / 3 + 1024) * sizeof(Node8)));
-		out->nodes_capacity_bytes = (n / 3 + 1024) * sizeof(Node8);
+		CKB(cudaMalloc(&out->nodes, (n / 4 + 64) * sizeof(Node8)));
+		out->nodes_capacity_bytes = (n / 4 + 64) * sizeof(Node8);
 	}
 	CKB(cudaMemcpyAsync(items[0], &root, sizeof(int32_t), cudaMemcpyHostToDevice, st));
 	int n_items = 1, lvl = 0, depth = 0;
@@ -605,7 +666,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	while (n_items > 0) {
 		++depth;
 		const size_t want = ((size_t)level_base + (size_t)n_items) * sizeof(Node8);
-		if (want > out->nodes_capacity_bytes) {   // rare (the first guess is N/3 nodes): grow the node array
+		if (want > out->nodes_capacity_bytes) {   // rare (the first guess is N/4 nodes; the optimal cut needs about N/9 at three primitives per leaf): grow the node array
 			const size_t ncap = std::max(out->nodes_capacity_bytes * 2, want);
 			void* bigger = nullptr;
 			CKB(cudaMalloc(&bigger, ncap));
@@ -615,10 +676,10 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 			out->nodes = bigger; out->nodes_capacity_bytes = ncap;
 		}
 		const int tiles = (n_items + kTile - 1) / kTile;
-		k_collapse_count<<<tiles, kTile, 0, st>>>(nodes, cnt, items[lvl], n_items, (uint32_t)max_leaf, item_counts, tile_sums);
+		k_collapse_count<<<tiles, kTile, 0, st>>>(nodes, cnt, dp, items[lvl], n_items, (uint32_t)max_leaf, item_counts, tile_sums);
 		k_scan_tiles<<<1, kTile, 0, st>>>(tile_sums, tiles, d_total);
 		EmitArgs A;
-		A.nodes = nodes; A.cnt = cnt; A.items = items[lvl]; A.n_items = n_items; A.max_leaf = (uint32_t)max_leaf;
+		A.nodes = nodes; A.cnt = cnt; A.dp = dp; A.items = items[lvl]; A.n_items = n_items; A.max_leaf = (uint32_t)max_leaf;
 		A.item_counts = item_counts; A.tile_offs = tile_sums;
 		A.level_base = level_base; A.next_base = level_base + (uint32_t)n_items; A.prim_base = prim_base;
 		A.next_items = items[lvl ^ 1]; A.out_nodes = static_cast<Node8*>(out->nodes); A.out_prims = static_cast<float4*>(out->prims);
