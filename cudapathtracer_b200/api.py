@@ -13,7 +13,7 @@ from typing import Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcupt.so")
+LIB_PATH = os.environ.get("CUPT_LIB") or os.path.join(_HERE, "libcupt.so")   # CUPT_LIB: an experiment build of the same library (tools/)
 
 # numpy views of the reference PODs (sizes pinned in tests/test_abi.py)
 VEC3 = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4")])
@@ -51,7 +51,7 @@ class RenderOpts(C.Structure):
     _fields_ = [("max_depth", C.c_int32), ("integrator", C.c_int32), ("traversal", C.c_int32), ("tri_test", C.c_int32),
                 ("seed", C.c_uint64), ("samples_per_pass", C.c_int32), ("collect_stats", C.c_int32),
                 ("time_stages", C.c_int32), ("fetch_threshold", C.c_int32), ("defer_pairs", C.c_int32),
-                ("reserved", C.c_int32)]
+                ("share_primary_hits", C.c_int32)]
 
 
 class Stats(C.Structure):

@@ -526,11 +526,23 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 			continue;
 		}
 		stage_begin(c, 0, ev);
-		k_raygen<<<grid, 256, 0, c->stream>>>(pp, c->pb);
+		// pinhole camera: the primary ray does not depend on the sample, so one trace per pixel serves the whole pass.
+		// Wide traversal only: the lens offset is radius * cos(theta) = +-0, and where the film offset is 0 too (the
+		// centre column / row) the ray direction comes out as +0 or -0 depending on the sample.  The wide traversal
+		// returns the same hit for both; the reference's slab test divides by it (BVH.h:61-79) and does not, and the
+		// reference-exact modes reproduce that.
+		const bool share = c->opts.share_primary_hits && c->cam.radius == 0.f && s_now > 1 && c->opts.traversal == CUPT_TRAVERSAL_WIDE;
+		k_raygen<<<grid, 256, 0, c->stream>>>(pp, c->pb, share);
 		stage_end(c, ev);
 		c->launches++;
 		for (int depth = 0; depth < pp.max_depth; ++depth) {
-			if ((rc = launch_extend(c, sc, depth, depth & 1))) return rc;
+			if (depth == 0 && share) {
+				if ((rc = launch_extend(c, sc, 63, 1))) return rc;       // queue[1] / counters[63]: the first sample's slots
+				stage_begin(c, 1, ev);
+				k_broadcast_primary<<<grid, 256, 0, c->stream>>>(pp, c->pb);
+				stage_end(c, ev);
+				c->launches++;
+			} else if ((rc = launch_extend(c, sc, depth, depth & 1))) return rc;
 			stage_begin(c, 2, ev);
 			k_shade<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb, depth, depth & 1);
 			stage_end(c, ev);

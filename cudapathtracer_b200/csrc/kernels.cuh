@@ -103,7 +103,8 @@ __device__ __forceinline__ uint32_t block_queue_reserve(bool push, uint32_t* cou
 }
 
 // ---- raygen --------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb)
+// share_primary: additionally list the slots of the pass's first sample in queue[1] / counters[63] (cupt_render_opts.share_primary_hits)
+__global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb, const bool share_primary = false)
 {
 	__shared__ uint32_t s_warp[9];
 	const uint32_t total = (uint32_t)pp.p_pad * (uint32_t)pp.samples;
@@ -131,9 +132,24 @@ __global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb)
 		}
 		const uint32_t pos = block_queue_reserve(valid, &pb.counters[0], s_warp);
 		if (valid) pb.queue[0][pos] = slot;
+		if (share_primary && base < (uint32_t)pp.p_pad) {   // (the condition is block-uniform; a block that straddles p_pad sorts its threads out with `first`)
+			const bool first = valid && slot < (uint32_t)pp.p_pad;
+			const uint32_t p1 = block_queue_reserve(first, &pb.counters[63], s_warp);
+			if (first) pb.queue[1][p1] = slot;
+		}
 	}
 	if (blockIdx.x == 0 && threadIdx.x == 0)
 		atomicAdd(&pb.stats[3], (unsigned long long)pp.cam.pxlWidth * pp.cam.pxlHeight * pp.samples);
+}
+
+// the hit of the pass's first sample of every pixel, copied to the other samples' records (share_primary_hits)
+__global__ void __launch_bounds__(256) k_broadcast_primary(PassParams pp, PathBuffers pb)
+{
+	const uint32_t total = (uint32_t)pp.p_pad * (uint32_t)pp.samples;
+	for (uint32_t slot = (uint32_t)pp.p_pad + blockIdx.x * blockDim.x + threadIdx.x; slot < total; slot += gridDim.x * blockDim.x) {
+		const uint32_t src = slot % (uint32_t)pp.p_pad;
+		reinterpret_cast<float2*>(&pb.rayB[slot])[1] = reinterpret_cast<const float2*>(&pb.rayB[src])[1];
+	}
 }
 
 // ---- extend: closest hit for every queued path ---------------------------------------------------------------
@@ -414,7 +430,10 @@ __device__ __forceinline__ f3 get_tangent(const f3 n)  // kernel.cu:44-54
 	return (rdot(c1, c1) > rdot(c2, c2)) ? c1 : c2;
 }
 
-__global__ void __launch_bounds__(256) k_shade(DevScene sc, PassParams pp, PathBuffers pb, int depth, int qsel)
+#ifndef CUPT_SHADE_MIN_BLOCKS
+#define CUPT_SHADE_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(256, CUPT_SHADE_MIN_BLOCKS) k_shade(DevScene sc, PassParams pp, PathBuffers pb, int depth, int qsel)
 {
 	__shared__ uint32_t s_warp[9];
 	const uint32_t count = pb.counters[depth];

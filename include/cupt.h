@@ -189,7 +189,11 @@ typedef struct cupt_render_opts {
 	int32_t time_stages;      /* 1: CUDA events around every stage launch */
 	int32_t fetch_threshold;  /* extend: refill idle lanes of a warp from the ray queue when <= this many are busy (0 = default 24) */
 	int32_t defer_pairs;      /* extend: hold primitive tests one traversal step while a warp has fewer (ray, primitive) pairs than this (0 = default 16, 1 = never) */
-	int32_t reserved;
+	int32_t share_primary_hits; /* 1: with a pinhole camera (radius == 0, the reference's setting, kernel.cu:646) every sample of a
+	                             * pixel has the same primary ray: trace it once per pixel and pass and reuse the hit.  Same image
+	                             * bit for bit, fewer rays traced (and counted).  Default 0; CUPT_INTEGRATOR_PT and CUPT_TRAVERSAL_WIDE
+	                             * only (the reference's slab test distinguishes the +0 / -0 direction components that
+	                             * different samples get on the centre column and row). */
 } cupt_render_opts;
 int cupt_default_render_opts(cupt_render_opts* o);
 int cupt_set_render_opts(cupt_context* c, const cupt_render_opts* o);

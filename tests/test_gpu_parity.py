@@ -539,3 +539,33 @@ def test_specular_materials_config5(ctx, get_case):
         assert close.mean() >= frac and rel <= rel_tol, (mode, close.mean(), rel)
         assert 0.3 * orays < ctx.stats()["rays"] <= orays
     ctx.set_options(collect_stats=0, max_depth=5)
+
+
+@pytest.mark.parametrize("name", ["cornell_lights", "atrium20k"])
+def test_shared_primary_hits(ctx, get_case, name):
+    """share_primary_hits: with the reference's pinhole camera (radius 0, kernel.cu:646) the primary ray is the same
+    for every sample of a pixel; tracing it once per pixel and pass gives the same image bit for bit with fewer rays.
+    With a lens (radius > 0) the option must switch itself off."""
+    c = get_case(name)
+    for mode in (api.TRAVERSAL_WIDE, api.TRAVERSAL_WIDE_STRICT):
+        # (the reference-exact modes do not share: on the centre column the direction's x is +0 or -0 depending on the
+        # sample's lens angle, and the reference's slab test, which divides by it, returns different hits for the two)
+        saved = 1 if mode == api.TRAVERSAL_WIDE else 0
+        load(ctx, c, mode, max_depth=5, seed=77, collect_stats=1, share_primary_hits=0)
+        ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 6); a = ctx.read_accum(False); ra = ctx.stats()["rays"]
+        ctx.set_options(share_primary_hits=1)
+        ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 6); b = ctx.read_accum(False); rb = ctx.stats()["rays"]
+        assert a.tobytes() == b.tobytes()
+        assert rb == ra - saved * 5 * c.w * c.h                                    # five of six primary rays per pixel saved
+        ctx.set_options(samples_per_pass=4)                                        # passes of 4 + 2 samples
+        ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 6); d = ctx.read_accum(False)
+        assert np.allclose(a, d, rtol=1e-6, atol=1e-6) and ctx.stats()["rays"] == ra - saved * 4 * c.w * c.h
+        ctx.set_options(samples_per_pass=0)
+    lens = api.make_camera(c.w, c.h, **dict(c.scene.camera, radius=0.05))
+    ctx.set_camera(lens)
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE, share_primary_hits=0)
+    ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 3); a = ctx.read_accum(False); ra = ctx.stats()["rays"]
+    ctx.set_options(share_primary_hits=1)
+    ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 3); b = ctx.read_accum(False)
+    assert a.tobytes() == b.tobytes() and ctx.stats()["rays"] == ra
+    ctx.set_options(share_primary_hits=0, collect_stats=0)
