@@ -268,6 +268,28 @@ def test_strict_mode_full_size(ctx, lib):
     ctx.reset_accum(); ctx.render(0, 2); r = ctx.read_accum(False)
     assert a.tobytes() == r.tobytes()
     ctx.set_options(traversal=api.TRAVERSAL_WIDE)
+    # the live integrator (BDPT) at full size: strict == reference-exact mode bit for bit, the plain wide mode within noise
+    ctx.set_options(integrator=api.INTEGRATOR_BDPT, traversal=api.TRAVERSAL_WIDE_STRICT, collect_stats=1)
+    ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 1); bs = ctx.read_accum(False); rays_s = ctx.stats()["rays"]
+    ctx.set_options(traversal=api.TRAVERSAL_REF_BVH2)
+    ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 1); br = ctx.read_accum(False); rays_r = ctx.stats()["rays"]
+    assert bs.tobytes() == br.tobytes() and rays_s == rays_r and 3.0 <= rays_r / (1024 * 1024) <= 7.0   # 3 sub-path rays + <= 4 connections
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE)
+    ctx.reset_accum(); ctx.render(0, 1); bw = ctx.read_accum(False)
+    assert (np.abs(bw - br).max(axis=1) > 1e-3 * (1 + np.abs(br).max(axis=1))).mean() < 1e-3 and abs(bw.mean() - br.mean()) < 0.01 * br.mean()
+    ctx.set_options(integrator=api.INTEGRATOR_PT, collect_stats=0)
+    # the device-built tree at full size: hits and image bit-identical to the host-built tree's; shared primary hits too
+    ctx.reset_accum(); ctx.render(0, 2); host_img = ctx.read_accum(False)
+    info = ctx.build_bvh_device(tie_rank=api.bvh2_leaf_order(n2, s.counts()[1]))
+    assert info["num_tri_records"] == 262144 and info["depth"] <= 12
+    di, dt = ctx.primary_hits()
+    assert hits_equal((di, dt), (wi, wt))
+    ctx.reset_accum(); ctx.render(0, 2)
+    assert ctx.read_accum(False).tobytes() == host_img.tobytes()
+    ctx.set_options(share_primary_hits=1)
+    ctx.reset_accum(); ctx.render(0, 2)
+    assert ctx.read_accum(False).tobytes() == host_img.tobytes()
+    ctx.set_options(share_primary_hits=0)
 
 
 def test_native_render_loop_example(ctx, lib, tmp_path):
