@@ -313,6 +313,12 @@ class Context:
         d.update(ms_total=ms[0], ms_sort=ms[1], ms_cluster=ms[2], ms_collapse=ms[3])
         return d
 
+    def debug_sort_pairs(self, keys: np.ndarray, vals: np.ndarray, passes: int = 8):
+        """test hook: the device builder's radix sort; returns sorted copies (stable, on the top 8 * passes of 63 bits)"""
+        k = np.array(keys, dtype=np.uint64, copy=True); v = np.array(vals, dtype=np.uint32, copy=True)
+        _check(self.lib.cupt_debug_sort_pairs(self.h, _ptr(k), _ptr(v), C.c_int64(len(k)), int(passes)))
+        return k, v
+
     def release_workspace(self):
         _check(self.lib.cupt_release_workspace(self.h))
 

@@ -3,7 +3,7 @@
 // write the Node8 / Prim48 arrays k_extend traverses, without a host round trip.
 //
 //   1. k_leaf_boxes     padded box per primitive (same 4-ulp padding as the host builder), centroid bounds
-//   2. k_morton         63-bit Morton code of the centroid, radix sort of (code, primitive)      [cub::DeviceRadixSort]
+//   2. k_morton         63-bit Morton code of the centroid, radix sort of (code, primitive)      [radix_sort.cuh]
 //   3. PLOC rounds      parallel locally-ordered clustering (Meister & Bittner, "Parallel Locally-Ordered Clustering
 //                       for Bounding Volume Hierarchy Construction", TVCG 2018): every cluster finds the neighbour
 //                       within +-R positions of the Morton order (R = 4 by default: measured best on config 2, DESIGN.md
@@ -21,7 +21,7 @@
 #include "host_common.h"
 #include "layout.h"
 #include "bvh_device.h"
-#include <cub/device/device_radix_sort.cuh>
+#include "radix_sort.cuh"
 #include <cuda_runtime.h>
 #include <algorithm>
 #include <cstring>
@@ -572,12 +572,11 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	const int tilesN = (int)((N + kTile - 1) / kTile);
 	const size_t n = (size_t)N;
 
-	size_t temp_bytes = 0;
-	{
-		cub::DoubleBuffer<uint64_t> dk(nullptr, nullptr);
-		cub::DoubleBuffer<uint32_t> dv(nullptr, nullptr);
-		CKB(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, dk, dv, (int)N, 0, 63, st));
-	}
+	const size_t temp_bytes = rsort::scratch_bytes((uint32_t)N);
+	// sort on the top log2(N) + 9 bits of the code, rounded up to whole 8-bit passes (radix_sort.cuh)
+	int log2n = 0;
+	while ((1ll << log2n) < N) ++log2n;
+	const int sort_passes = std::min(8, (log2n + 9 + 7) / 8);
 	// everything the build touches except its two outputs, in one arena; the sort buffers are dead once the sorted
 	// leaves are written, the collapse reuses the cluster arrays for its level queues
 	const size_t need = up256(n * sizeof(N2)) + up256(64) + 2 * up256(n * 8) + 2 * up256(n * 4) + up256(temp_bytes + 256)
@@ -600,9 +599,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	CKB(cudaMemcpyAsync(cbounds, cb_init, sizeof(cb_init), cudaMemcpyHostToDevice, st));
 	k_leaf_boxes<<<tilesN, kTile, 0, st>>>(verts, tris, nt, spheres, N, leaf, cbounds);
 	k_morton<<<tilesN, kTile, 0, st>>>(leaf, N, cbounds, keys[0], vals[0]);
-	cub::DoubleBuffer<uint64_t> dk(keys[0], keys[1]);
-	cub::DoubleBuffer<uint32_t> dv(vals[0], vals[1]);
-	CKB(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, dk, dv, (int)N, 0, 63, st));
+	const int sorted = rsort::sort_pairs(st, keys, vals, (uint32_t)N, sort_passes, reinterpret_cast<uint32_t*>(temp));
 	CKB(cudaEventRecord(ev[1], st));
 
 	// 3: PLOC
@@ -616,7 +613,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	uint64_t* item_counts = take<uint64_t>(arena, n / 2 + 2);
 	double* d_sah = take<double>(arena, 1);
 	if (arena.off > arena.cap) return set_error(CUPT_ERR_CUDA, "internal: BVH build workspace undersized (%zu > %zu)", arena.off, arena.cap);
-	k_sorted_leaves<<<tilesN, kTile, 0, st>>>(leaf, dv.Current(), N, nodes, cnt, cid[0]);
+	k_sorted_leaves<<<tilesN, kTile, 0, st>>>(leaf, vals[sorted], N, nodes, cnt, cid[0]);
 	int cn = (int)N, cur = 0, rounds = 0;
 	uint32_t node_base = (uint32_t)N;
 	while (cn > 1) {
@@ -707,6 +704,29 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	cudaEventElapsedTime(&out->ms_collapse, ev[2], ev[3]);
 	cudaEventElapsedTime(&out->ms_total, ev[0], ev[3]);
 	return CUPT_OK;
+}
+
+// test hook (cupt_debug_sort_pairs): the build's radix sort on caller-supplied pairs, in place
+int debug_sort_pairs(cudaStream_t st, uint64_t* h_keys, uint32_t* h_vals, int64_t n, int passes)
+{
+	if (n < 0 || n > (1ll << 27) || passes < 1 || passes > 8) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (n == 0) return CUPT_OK;
+	uint64_t* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr}; uint32_t* scratch = nullptr;
+	cudaError_t e = cudaSuccess;
+	for (int b = 0; b < 2 && e == cudaSuccess; ++b) { e = cudaMalloc((void**)&keys[b], (size_t)n * 8); if (e == cudaSuccess) e = cudaMalloc((void**)&vals[b], (size_t)n * 4); }
+	if (e == cudaSuccess) e = cudaMalloc((void**)&scratch, rsort::scratch_bytes((uint32_t)n));
+	if (e == cudaSuccess) e = cudaMemcpyAsync(keys[0], h_keys, (size_t)n * 8, cudaMemcpyHostToDevice, st);
+	if (e == cudaSuccess) e = cudaMemcpyAsync(vals[0], h_vals, (size_t)n * 4, cudaMemcpyHostToDevice, st);
+	if (e == cudaSuccess) {
+		const int r = rsort::sort_pairs(st, keys, vals, (uint32_t)n, passes, scratch);
+		e = cudaMemcpyAsync(h_keys, keys[r], (size_t)n * 8, cudaMemcpyDeviceToHost, st);
+		if (e == cudaSuccess) e = cudaMemcpyAsync(h_vals, vals[r], (size_t)n * 4, cudaMemcpyDeviceToHost, st);
+		if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+		if (e == cudaSuccess) e = cudaGetLastError();
+	}
+	for (int b = 0; b < 2; ++b) { cudaFree(keys[b]); cudaFree(vals[b]); }
+	cudaFree(scratch);
+	return e == cudaSuccess ? CUPT_OK : set_error(CUPT_ERR_CUDA, "debug_sort_pairs: %s", cudaGetErrorString(e));
 }
 
 }  // namespace cupt

@@ -34,4 +34,7 @@ int build_wide_bvh_device(cudaStream_t stream, BuildArena& arena, const float* v
                           const float4* spheres, int64_t num_spheres, const uint32_t* rank, int max_leaf,
                           int radius /* 1, 2, 4 (default), 8, 16, 32 */, DeviceBvh* out);
 
+// test hook: the build's radix sort on caller-supplied host pairs, in place (sorted on key bits [63 - 8 * passes, 63))
+int debug_sort_pairs(cudaStream_t stream, uint64_t* keys, uint32_t* vals, int64_t n, int passes);
+
 }  // namespace cupt

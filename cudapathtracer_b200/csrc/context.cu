@@ -432,6 +432,13 @@ int cupt_read_bvh(cupt_context* c, void* nodes80, void* tris48, int64_t* counts)
 	return CUPT_OK;
 }
 
+int cupt_debug_sort_pairs(cupt_context* c, uint64_t* keys, uint32_t* vals, int64_t n, int passes)
+{
+	if (!c || (n > 0 && (!keys || !vals))) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	CK(cudaSetDevice(c->device));
+	return debug_sort_pairs(c->stream, keys, vals, n, passes);
+}
+
 int cupt_release_workspace(cupt_context* c)
 {
 	if (!c) return set_error(CUPT_ERR_INVALID, "null context");

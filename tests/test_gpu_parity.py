@@ -591,3 +591,20 @@ def test_shared_primary_hits(ctx, get_case, name):
     ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 3); b = ctx.read_accum(False)
     assert a.tobytes() == b.tobytes() and ctx.stats()["rays"] == ra
     ctx.set_options(share_primary_hits=0, collect_stats=0)
+
+
+def test_device_radix_sort(ctx):
+    """the hand-written stable LSD radix sort behind the device BVH build (csrc/radix_sort.cuh) against numpy's stable
+    argsort: ragged sizes around the 4096-pair tile, heavy duplicates, partial-key sorts (top 8 * passes bits)"""
+    rng = np.random.default_rng(3)
+    for n in (1, 31, 4095, 4096, 4097, 100003, 1 << 20):
+        keys = rng.integers(0, 1 << 63, n, dtype=np.uint64)
+        keys[::3] = keys[0]                                                      # a third of the keys are equal
+        keys[1::7] &= np.uint64(0xFFFFFF0000000000)                              # and some differ only in the top bits
+        vals = np.arange(n, dtype=np.uint32)
+        for passes in (8, 5, 1):
+            shift = max(0, 63 - 8 * passes)
+            want = np.argsort(keys >> np.uint64(shift), kind="stable")
+            k, v = ctx.debug_sort_pairs(keys, vals, passes)
+            assert np.array_equal(v, want.astype(np.uint32)), (n, passes)
+            assert np.array_equal(k, keys[want])
