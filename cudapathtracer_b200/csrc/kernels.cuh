@@ -441,12 +441,25 @@ __global__ void __launch_bounds__(256, CUPT_SHADE_MIN_BLOCKS) k_shade(DevScene s
 	uint32_t* __restrict__ qout = pb.queue[qsel ^ 1];
 	const float kBrdf = (float)(1 / 3.14159);   // BRDF(): mul(albedo, 1 / 3.14159) with a float parameter (kernel.cu:101-104)
 	const float kPi = (float)3.14159;            // color::operator*(const float&) (kernel.cu:463)
+	// the queue entry of the NEXT iteration is fetched one iteration ahead: the kernel is bound by the chain of
+	// dependent loads queue -> path records -> triangle -> material (profiles/r1h_shade_metrics.md: 36 % long-scoreboard
+	// stalls at 34 % of the DRAM peak), and this takes the first link out of it (7.03 -> 6.86 ms per frame; prefetching the
+	// path records as well costs registers and gains nothing: 79 registers / 3 blocks per SM 7.55 ms, 64 with spills 6.92 ms;
+	// forcing 5 / 6 / 8 blocks per SM by spilling: 7.66 / 8.20 / 8.83 ms)
+	uint32_t slot_next = 0;
+	{
+		const uint32_t q0 = blockIdx.x * blockDim.x + threadIdx.x;
+		if (q0 < count) slot_next = qin[q0];
+	}
 	for (uint32_t base = blockIdx.x * blockDim.x; base < count; base += gridDim.x * blockDim.x) {
 		const uint32_t qi = base + threadIdx.x;
 		bool push = false;
-		uint32_t slot = 0;
+		uint32_t slot = slot_next;
+		{
+			const uint32_t qn = qi + gridDim.x * blockDim.x;
+			if (qn < count) slot_next = qin[qn];
+		}
 		if (qi < count) {
-			slot = qin[qi];
 			const float4 ra = pb.rayA[slot], rb = pb.rayB[slot], s0 = pb.st0[slot];
 			const f3 o = mk3(ra.x, ra.y, ra.z), d = mk3(ra.w, rb.x, rb.y);
 			float wr = s0.x, wg = s0.y, wb = s0.z;
