@@ -141,6 +141,8 @@ PassParams make_pass(const cupt_context* c, int first_sample, int samples, int f
 	pp.p_pad = pp.tiles_x * pp.tiles_y * 32;
 	pp.max_depth = c->opts.max_depth;
 	pp.fixed_lens = fixed_lens;
+	pp.inv_p_pad = ~0ull / (uint64_t)pp.p_pad + 1ull;                      // p_pad >= 32
+	pp.inv_tiles_x = pp.tiles_x > 1 ? ~0ull / (uint64_t)pp.tiles_x + 1ull : 0ull;
 	return pp;
 }
 
