@@ -42,7 +42,7 @@ struct cupt_context {
 	cupt_camera cam{}; bool have_cam = false;
 	cupt_render_opts opts{};
 	// wavefront state
-	PathBuffers pb{}; size_t path_capacity = 0;
+	PathBuffers pb{}; size_t path_capacity = 0, retrace_capacity = 0;
 	float* d_accum = nullptr; size_t accum_pixels = 0; uint64_t samples_accumulated = 0;
 	// bookkeeping
 	uint64_t launches = 0, extend_launches = 0;
@@ -211,12 +211,19 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
 	CK(cudaGetLastError());
 	c->launches++; c->extend_launches++;
 	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE_STRICT) {
+		if (c->retrace_capacity < c->path_capacity) {   // one slot index per path at worst; in practice a handful per launch
+			if (c->pb.retrace) { CK(cudaFree(c->pb.retrace)); c->pb.retrace = nullptr; c->retrace_capacity = 0; }
+			CK(cudaMalloc((void**)&c->pb.retrace, c->path_capacity * sizeof(uint32_t)));
+			c->retrace_capacity = c->path_capacity;
+		}
 		StageEvent ev2;
 		stage_begin(c, 1, ev2);
+		CK(cudaMemsetAsync(c->pb.counters + 126, 0, sizeof(uint32_t), c->stream));
 		k_verify_strict<<<c->num_sms * 8, 256, 0, c->stream>>>(sc, c->pb, depth, qsel);
+		k_retrace_strict<<<c->num_sms, 64, 0, c->stream>>>(sc, c->pb);
 		stage_end(c, ev2);
 		CK(cudaGetLastError());
-		c->launches++;
+		c->launches += 2;
 	}
 	return CUPT_OK;
 }
@@ -267,7 +274,7 @@ void cupt_destroy(cupt_context* c)
 	cudaFree(c->d_verts); cudaFree(c->d_tris); cudaFree(c->d_trishade); cudaFree(c->d_mats); cudaFree(c->d_lights); cudaFree(c->d_light_cdf); cudaFree(c->d_spheres);
 	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2); cudaFree(c->d_bvh2_up); cudaFree(c->d_bvh2_leaf_parent);
 	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
-	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats);
+	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats); cudaFree(c->pb.retrace);
 	cudaFree(c->d_accum); cudaFree(c->d_build_rank); cudaFree(c->d_rgb8); cudaFree(c->d_prims_wt); c->arena.destroy();
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;
@@ -477,7 +484,27 @@ int cupt_set_bvh2(cupt_context* c, const cupt_bvh2_node* nodes, int size, int de
 			} else if (ch < (uint32_t)size) parent[ch] = (uint32_t)i;
 		}
 	std::vector<cupt_bvh2_node> up(nodes, nodes + size);
-	for (int i = 0; i < size; ++i) { up[(size_t)i].left = parent[(size_t)i]; up[(size_t)i].right = 0u; }
+	// chain[i] = 1 when every ancestor's box contains the box of its child on the way up from node i.  Then the
+	// reference's slab test, whose comparisons are monotone in the box (IEEE rounding is monotone), accepts all of
+	// them as soon as it accepts node i: the strict check needs ONE test instead of a walk to the root (k_verify_strict).
+	std::vector<uint8_t> chain((size_t)size, 0);
+	{
+		std::vector<uint32_t> order;   // parents before children
+		order.reserve((size_t)size);
+		for (int i = 0; i < size; ++i) if (parent[(size_t)i] == 0xffffffffu) { chain[(size_t)i] = 1; order.push_back((uint32_t)i); }
+		for (size_t q = 0; q < order.size(); ++q) {
+			const cupt_bvh2_node& p = nodes[order[q]];
+			for (int k = 0; k < 2; ++k) {
+				const uint32_t ch = k ? p.right : p.left;
+				if ((ch & CUPT_BVH_LEAF_FLAG) || ch >= (uint32_t)size || parent[ch] != order[q]) continue;
+				const cupt_bvh2_node& n = nodes[ch];
+				const bool nested = n.lo.x >= p.lo.x && n.lo.y >= p.lo.y && n.lo.z >= p.lo.z && n.hi.x <= p.hi.x && n.hi.y <= p.hi.y && n.hi.z <= p.hi.z;
+				chain[ch] = (uint8_t)(nested && chain[order[q]]);
+				order.push_back(ch);
+			}
+		}
+	}
+	for (int i = 0; i < size; ++i) { up[(size_t)i].left = parent[(size_t)i]; up[(size_t)i].right = chain[(size_t)i]; }
 	if ((rc = upload(c, &c->d_bvh2_up, up.data(), up.size() * sizeof(cupt_bvh2_node)))) return rc;
 	if ((rc = upload(c, &c->d_bvh2_leaf_parent, leaf_parent.data(), leaf_parent.size() * sizeof(uint32_t)))) return rc;
 	c->bvh2_leaves = (int64_t)leaf_parent.size();

@@ -54,6 +54,7 @@ struct PathBuffers {
 	float4* st0;
 	float4* st1;
 	uint32_t* queue[2];
+	uint32_t* retrace;         // strict mode: slots whose hit the reference would not have reached (counter: counters[126])
 	uint32_t* counters;        // [0..63] queue sizes per depth, [64..127] extend fetch cursors per depth
 	unsigned long long* stats; // [0] rays, [1] nodes, [2] tris, [3] samples, [4] strict-mode re-traces
 };
@@ -375,48 +376,75 @@ __global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene
 // in the reference tree with the reference's slab arithmetic, and only when an ancestor rejects the ray (about one
 // ray in 40 000 on config 2) re-traces that ray with the reference's algorithm.  A miss needs no check (reached is a
 // subset of all).  One thread per queued ray.
+// Two kernels: k_verify_strict lists the rays whose hit the reference would not have reached (pb.retrace, counter
+// counters[126]); k_retrace_strict re-traces those few with the reference's algorithm.  Keeping the re-trace (and its
+// 256-byte stack) out of the checking kernel leaves that one small enough for full occupancy: it is bound by three
+// dependent loads per ray (queue -> ray record -> leaf parent -> node).
+__device__ __forceinline__ bool strict_reached(const DevScene& sc, const f3 o, const f3 d, const int32_t id)
+{
+	// Every comparison of rayAABBIntersect is monotone in the box, and IEEE rounding is monotone, so with no NaN in
+	// play (no zero direction component) a box that passes makes every box that contains it pass.  The reference's
+	// node boxes are nested (checked per node at upload: `right` = 1), so the test of the deepest ancestor decides;
+	// only otherwise the chain is walked to the root, where a division-free test with an explicit error margin proves
+	// "the reference accepts" for the ancestors that contain the hit point comfortably (quotients by multiplication
+	// with 1/d are within 2^-22 relative of the reference's correctly rounded divisions).
+	const bool no_nan = d.x != 0.0f && d.y != 0.0f && d.z != 0.0f;
+	const float ix = 1.0f / d.x, iy = 1.0f / d.y, iz = 1.0f / d.z;
+	for (uint32_t n = sc.bvh2_leaf_parent[id]; n != 0xffffffffu;) {
+		const uint4 w0 = ldg_nc_u4(reinterpret_cast<const uint4*>(sc.bvh2_up + n)), w1 = ldg_nc_u4(reinterpret_cast<const uint4*>(sc.bvh2_up + n) + 1);
+		cupt_bvh2_node nd;   // two 128-bit fetches (the struct itself is only 4-byte aligned and would load as eight words)
+		nd.lo.x = __uint_as_float(w0.x); nd.lo.y = __uint_as_float(w0.y); nd.lo.z = __uint_as_float(w0.z);
+		nd.hi.x = __uint_as_float(w0.w); nd.hi.y = __uint_as_float(w1.x); nd.hi.z = __uint_as_float(w1.y);
+		nd.left = w1.z; nd.right = w1.w;
+		if (no_nan && nd.right != 0u) return ref_slab_hit(o, d, nd);
+		n = nd.left;
+		const float x1 = rsub(nd.lo.x, o.x) * ix, x2 = rsub(nd.hi.x, o.x) * ix;
+		const float y1 = rsub(nd.lo.y, o.y) * iy, y2 = rsub(nd.hi.y, o.y) * iy;
+		const float z1 = rsub(nd.lo.z, o.z) * iz, z2 = rsub(nd.hi.z, o.z) * iz;
+		const float txn = fminf(x1, x2), txf = fmaxf(x1, x2), tyn = fminf(y1, y2), tyf = fmaxf(y1, y2);
+		const float tzn = fminf(z1, z2), tzf = fmaxf(z1, z2);
+		const float m = fmaxf(fmaxf(fmaxf(fabsf(x1), fabsf(x2)), fmaxf(fabsf(y1), fabsf(y2))), fmaxf(fabsf(z1), fabsf(z2))) * 9.5367431640625e-7f;
+		const bool sure = m < 1.0e30f && txn <= tyf - m && tyn <= txf - m && fmaxf(txn, tyn) <= tzf - m && tzn <= fminf(txf, tyf) - m;
+		if (!sure && !ref_slab_hit(o, d, nd)) return false;
+	}
+	return true;
+}
+
 __global__ void __launch_bounds__(256) k_verify_strict(DevScene sc, PathBuffers pb, int depth, int qsel)
 {
 	const uint32_t count = pb.counters[depth];
 	const uint32_t* __restrict__ queue = pb.queue[qsel];
-	uint32_t n_fallback = 0;
-	for (uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x; qi < count; qi += gridDim.x * blockDim.x) {
-		const uint32_t slot = queue[qi];
-		const float4 b = pb.rayB[slot];
-		const int32_t id = __float_as_int(b.w);
-		if (id < 0) continue;
-		const float4 a = pb.rayA[slot];
-		const f3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, b.x, b.y);
-		// Most ancestors contain the hit point comfortably; a division-free test with an explicit error margin proves
-		// "the reference accepts" for those (quotients by multiplication with 1/d are within 2^-22 relative of the
-		// reference's correctly rounded divisions), and only the rest run the reference's six divisions.
-		const float ix = 1.0f / d.x, iy = 1.0f / d.y, iz = 1.0f / d.z;
-		bool reached = true;
-		for (uint32_t n = sc.bvh2_leaf_parent[id]; n != 0xffffffffu;) {
-			const uint4 w0 = ldg_nc_u4(reinterpret_cast<const uint4*>(sc.bvh2_up + n)), w1 = ldg_nc_u4(reinterpret_cast<const uint4*>(sc.bvh2_up + n) + 1);
-			cupt_bvh2_node nd;   // two 128-bit fetches (the struct itself is only 4-byte aligned and would load as eight words)
-			nd.lo.x = __uint_as_float(w0.x); nd.lo.y = __uint_as_float(w0.y); nd.lo.z = __uint_as_float(w0.z);
-			nd.hi.x = __uint_as_float(w0.w); nd.hi.y = __uint_as_float(w1.x); nd.hi.z = __uint_as_float(w1.y);
-			nd.left = w1.z; nd.right = w1.w;
-			n = nd.left;
-			const float x1 = rsub(nd.lo.x, o.x) * ix, x2 = rsub(nd.hi.x, o.x) * ix;
-			const float y1 = rsub(nd.lo.y, o.y) * iy, y2 = rsub(nd.hi.y, o.y) * iy;
-			const float z1 = rsub(nd.lo.z, o.z) * iz, z2 = rsub(nd.hi.z, o.z) * iz;
-			const float txn = fminf(x1, x2), txf = fmaxf(x1, x2), tyn = fminf(y1, y2), tyf = fmaxf(y1, y2);
-			const float tzn = fminf(z1, z2), tzf = fmaxf(z1, z2);
-			const float m = fmaxf(fmaxf(fmaxf(fabsf(x1), fabsf(x2)), fmaxf(fabsf(y1), fabsf(y2))), fmaxf(fabsf(z1), fabsf(z2))) * 9.5367431640625e-7f;
-			const bool sure = m < 1.0e30f && txn <= tyf - m && tyn <= txf - m && fmaxf(txn, tyn) <= tzf - m && tzn <= fminf(txf, tyf) - m;
-			if (!sure && !ref_slab_hit(o, d, nd)) { reached = false; break; }
+	const uint32_t stride = gridDim.x * blockDim.x;
+	// two rays per iteration: their load chains overlap
+	for (uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x; qi < count; qi += 2u * stride) {
+		const uint32_t qj = qi + stride;
+		const bool two = qj < count;
+		const uint32_t s0 = queue[qi], s1 = two ? queue[qj] : s0;
+		const float4 b0 = pb.rayB[s0], b1 = pb.rayB[s1];
+		const int32_t id0 = __float_as_int(b0.w), id1 = two ? __float_as_int(b1.w) : -1;
+		if (id0 >= 0) {
+			const float4 a = pb.rayA[s0];
+			if (!strict_reached(sc, mk3(a.x, a.y, a.z), mk3(a.w, b0.x, b0.y), id0)) pb.retrace[atomicAdd(&pb.counters[126], 1u)] = s0;
 		}
-		if (!reached) {
-			Hit hit;
-			uint32_t nn = 0, nt = 0;
-			traverse_bvh2_ref<false>(sc.bvh2, sc.verts, sc.tris, o, d, hit, nn, nt);
-			reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(hit.t, __int_as_float(hit.id));
-			++n_fallback;
+		if (id1 >= 0) {
+			const float4 a = pb.rayA[s1];
+			if (!strict_reached(sc, mk3(a.x, a.y, a.z), mk3(a.w, b1.x, b1.y), id1)) pb.retrace[atomicAdd(&pb.counters[126], 1u)] = s1;
 		}
 	}
-	if (n_fallback) atomicAdd(&pb.stats[4], (unsigned long long)n_fallback);
+}
+
+__global__ void __launch_bounds__(64) k_retrace_strict(DevScene sc, PathBuffers pb)
+{
+	const uint32_t count = pb.counters[126];
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+		const uint32_t slot = pb.retrace[i];
+		const float4 a = pb.rayA[slot], b = pb.rayB[slot];
+		Hit hit;
+		uint32_t nn = 0, nt = 0;
+		traverse_bvh2_ref<false>(sc.bvh2, sc.verts, sc.tris, mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), hit, nn, nt);
+		reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(hit.t, __int_as_float(hit.id));
+	}
+	if (blockIdx.x == 0 && threadIdx.x == 0 && count) atomicAdd(&pb.stats[4], (unsigned long long)count);
 }
 
 // ---- shade: one iteration of radianceAlongSingleStep2 (kernel.cu:424-512) per queued path ----------------------
