@@ -215,24 +215,24 @@ def main():
 
     sc, s, cam = build_scene()
     mode = {"wide": api.TRAVERSAL_WIDE, "strict": api.TRAVERSAL_WIDE_STRICT, "ref": api.TRAVERSAL_REF_BVH2}[args.traversal]
-    n2 = None
-    if mode != api.TRAVERSAL_WIDE:   # reference-layout tree: the parity mode's structure and the tie-break ranks
-        n2, d2 = s.build_bvh2()
+    # reference-layout tree: the tie-break ranks of every mode (equal-t hits resolve like the reference's left-first
+    # visiting order) and the structure the strict / reference-exact modes check against
+    n2, d2 = s.build_bvh2()
     t0 = time.perf_counter()
-    bvh = s.build_bvh(tie_rank=None if n2 is None else api.bvh2_leaf_order(n2, s.counts()[1]))
+    bvh = s.build_bvh(tie_rank=api.bvh2_leaf_order(n2, s.counts()[1]))
     build_s = time.perf_counter() - t0
     info = bvh.info()
     ctx = api.Context(local)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
     ctx.set_scene(s); ctx.set_bvh(bvh); ctx.set_camera(cam)
-    dev_rank = None if n2 is None else api.bvh2_leaf_order(n2, s.counts()[1])
+    dev_rank = api.bvh2_leaf_order(n2, s.counts()[1])
     dev_info = None
     if args.bvh == "device":
         ctx.build_bvh_device(tie_rank=dev_rank)
         dev_info = ctx.build_bvh_device(tie_rank=dev_rank)
         info = dict(info, num_nodes=dev_info["num_nodes"], depth=dev_info["depth"])
-    if n2 is not None:
+    if mode != api.TRAVERSAL_WIDE:
         ctx.set_bvh2(n2, d2)
     ctx.set_options(max_depth=DEPTH, seed=SEED, traversal=mode, time_stages=1, collect_stats=0,
                     integrator=api.INTEGRATOR_BDPT if args.integrator == "bdpt" else api.INTEGRATOR_PT,
@@ -310,7 +310,7 @@ def main():
             ctx.build_bvh_device(tie_rank=dev_rank)      # the build itself is inside the e2e step
         else:
             ctx.set_bvh(bvh)
-        if n2 is not None:
+        if mode != api.TRAVERSAL_WIDE:
             ctx.set_bvh2(n2, d2)
         ctx.reset_accum(); ctx.render(first, spp_rank)
         if world > 1:
@@ -358,6 +358,24 @@ def main():
                          "launch_ms": ext_ms / n_ext, "launches": int(n_ext),
                          "bytes_per_ray": bytes_step / rays_step, "nodes_per_ray": nodes_step / rays_step, "tris_per_ray": tris_step / rays_step},
         }
+        if world == 1 and mode == api.TRAVERSAL_WIDE and not args.share_primary:
+            # the same step in the mode whose hits equal the reference's trace() on EVERY ray (the plain wide mode
+            # returns the nearest triangle also on the ~1 ray in 40 000 where the reference's slab test loses it)
+            ctx.set_bvh2(n2, d2)
+            ctx.set_options(traversal=api.TRAVERSAL_WIDE_STRICT)
+            step(); torch.cuda.synchronize()
+            ctx.reset_stats()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            flush_buf.fill_(1); e0.record(stream)
+            for _ in range(args.steps):
+                step()
+            e1.record(stream); torch.cuda.synchronize()
+            sst = ctx.stats()
+            ms_s = e0.elapsed_time(e1)
+            line["strict_mode"] = {"value": sst["rays"] / (ms_s * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms_s / args.steps,
+                                   "retraced_rays_per_step": sst["strict_retraces"] / args.steps,
+                                   "what": "CUPT_TRAVERSAL_WIDE_STRICT: hits bit-identical to the reference's on every ray"}
+            ctx.set_options(traversal=mode)
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             spp_cpu = 4

@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene
 // traversal returns the argmin over ALL triangles (ties by the reference's visiting order).  If that triangle is
 // reached by the reference, it is also the reference's answer; so this kernel walks the hit triangle's ancestor chain
 // in the reference tree with the reference's slab arithmetic, and only when an ancestor rejects the ray (about one
-// ray in 40 000 on config 2) re-traces that ray with the reference's algorithm.  A miss needs no check (reached is a
+// ray in 5 400 on config 2) re-traces that ray with the reference's algorithm.  A miss needs no check (reached is a
 // subset of all).  One thread per queued ray.
 // Two kernels: k_verify_strict lists the rays whose hit the reference would not have reached (pb.retrace, counter
 // counters[126]); k_retrace_strict re-traces those few with the reference's algorithm.  Keeping the re-trace (and its
