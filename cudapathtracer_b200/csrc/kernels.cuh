@@ -415,20 +415,40 @@ __global__ void __launch_bounds__(256) k_verify_strict(DevScene sc, PathBuffers 
 	const uint32_t count = pb.counters[depth];
 	const uint32_t* __restrict__ queue = pb.queue[qsel];
 	const uint32_t stride = gridDim.x * blockDim.x;
-	// two rays per iteration: their load chains overlap
-	for (uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x; qi < count; qi += 2u * stride) {
-		const uint32_t qj = qi + stride;
-		const bool two = qj < count;
-		const uint32_t s0 = queue[qi], s1 = two ? queue[qj] : s0;
-		const float4 b0 = pb.rayB[s0], b1 = pb.rayB[s1];
-		const int32_t id0 = __float_as_int(b0.w), id1 = two ? __float_as_int(b1.w) : -1;
-		if (id0 >= 0) {
-			const float4 a = pb.rayA[s0];
-			if (!strict_reached(sc, mk3(a.x, a.y, a.z), mk3(a.w, b0.x, b0.y), id0)) pb.retrace[atomicAdd(&pb.counters[126], 1u)] = s0;
+	// four rays per iteration, every link of the load chain (queue -> hit -> leaf parent -> node -> ray) issued for all
+	// four before the next one is used (one ray at a time: 7.8 ms per config 2 frame; two: 6.2; four, phased: 5.7)
+	constexpr int U = 4;
+	for (uint32_t q0 = blockIdx.x * blockDim.x + threadIdx.x; q0 < count; q0 += (uint32_t)U * stride) {
+		uint32_t sl[U], lp[U]; float4 rb[U], ra[U]; int32_t id[U]; uint4 w0[U], w1[U];
+#pragma unroll
+		for (int u = 0; u < U; ++u) { const uint32_t q = q0 + (uint32_t)u * stride; sl[u] = q < count ? queue[q] : 0xffffffffu; }
+#pragma unroll
+		for (int u = 0; u < U; ++u) { rb[u] = sl[u] != 0xffffffffu ? pb.rayB[sl[u]] : make_float4(0.f, 0.f, 0.f, __int_as_float(-1)); id[u] = __float_as_int(rb[u].w); }
+#pragma unroll
+		for (int u = 0; u < U; ++u) {
+			lp[u] = id[u] >= 0 ? sc.bvh2_leaf_parent[id[u]] : 0xffffffffu;
+			ra[u] = id[u] >= 0 ? pb.rayA[sl[u]] : make_float4(0.f, 0.f, 0.f, 0.f);
 		}
-		if (id1 >= 0) {
-			const float4 a = pb.rayA[s1];
-			if (!strict_reached(sc, mk3(a.x, a.y, a.z), mk3(a.w, b1.x, b1.y), id1)) pb.retrace[atomicAdd(&pb.counters[126], 1u)] = s1;
+#pragma unroll
+		for (int u = 0; u < U; ++u) {
+			w0[u] = w1[u] = make_uint4(0u, 0u, 0u, 0u);
+			if (lp[u] != 0xffffffffu) { w0[u] = ldg_nc_u4(reinterpret_cast<const uint4*>(sc.bvh2_up + lp[u])); w1[u] = ldg_nc_u4(reinterpret_cast<const uint4*>(sc.bvh2_up + lp[u]) + 1); }
+		}
+#pragma unroll
+		for (int u = 0; u < U; ++u) {
+			if (id[u] < 0) continue;
+			const f3 o = mk3(ra[u].x, ra[u].y, ra[u].z), d = mk3(ra[u].w, rb[u].x, rb[u].y);
+			bool reached;
+			if (w1[u].w != 0u && d.x != 0.0f && d.y != 0.0f && d.z != 0.0f) {   // nested chain, no NaN: this one box decides
+				cupt_bvh2_node nd;
+				nd.lo.x = __uint_as_float(w0[u].x); nd.lo.y = __uint_as_float(w0[u].y); nd.lo.z = __uint_as_float(w0[u].z);
+				nd.hi.x = __uint_as_float(w0[u].w); nd.hi.y = __uint_as_float(w1[u].x); nd.hi.z = __uint_as_float(w1[u].y);
+				nd.left = nd.right = 0u;
+				reached = ref_slab_hit(o, d, nd);
+			} else {
+				reached = strict_reached(sc, o, d, id[u]);
+			}
+			if (!reached) pb.retrace[atomicAdd(&pb.counters[126], 1u)] = sl[u];
 		}
 	}
 }
