@@ -210,6 +210,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 					const float4 a = pb.rayA[slot];
 					const float4 b = pb.rayB[slot];
 					wide_ray_init(r, mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y));
+					r.best = b.z;   // the producer's t limit: CUPT_MAX_FLOAT (kernel.cu:117) except for BDPT visibility rays
 					ngroup = make_uint2(0u, 0x80000000u); tgroup = make_uint2(0u, 0u);
 					pgroup = make_uint2(0u, 0u);
 					sp = 0;
