@@ -257,9 +257,11 @@ __global__ void __launch_bounds__(256) k_bdpt_connect(DevScene sc, PassParams pp
 						// The visibility test only asks whether the CLOSEST hit lies within 0.01 of `len` (kernel.cu:396-405),
 						// so the wide traversal may stop looking beyond len + 0.02: if nothing is hit up to there the extend
 						// reports t = that limit, which fails |t - len| <= 0.01 exactly like the farther hit (or the miss)
-						// the reference would have found.  The reference-exact mode ignores the limit.
+						// the reference would have found; and a hit nearer than len - 0.02 already decides "occluded" whatever
+						// else lies in front of it, so the traversal stops there (last component).  The reference-exact mode
+						// ignores both.
 						pb.rayA[r + c] = make_float4(x[i].x, x[i].y, x[i].z, ray.x);
-						pb.rayB[r + c] = make_float4(ray.y, ray.z, fminf(__fadd_ru(len, 0.02f), CUPT_MAX_FLOAT), __int_as_float(-1));
+						pb.rayB[r + c] = make_float4(ray.y, ray.z, fminf(__fadd_ru(len, 0.02f), CUPT_MAX_FLOAT), __fadd_rd(len, -0.02f));
 					}
 				}
 			const float4 me3 = sc.mats[2 * mat[3] + 1];   // accum += emission of the primary hit, four times (kernel.cu:409-410)

@@ -187,7 +187,7 @@ int check_ready(cupt_context* c, bool need_shading, bool need_cam = true)
 }
 
 // persistent launch of the extend stage for queue `depth`
-int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
+int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel, bool vis = false)
 {
 	const int mode = c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 ? 1 : 0;
 	const bool stats = c->opts.collect_stats != 0;
@@ -197,7 +197,8 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel)
 	tune.defer_pairs = c->opts.defer_pairs > 0 ? std::min(c->opts.defer_pairs, 64) : 16;
 	tune.qbias_bits = CUPT_QBIAS_BITS;
 	void (*kern)(DevScene, PathBuffers, int, int, ExtendTuning) =
-		mode == 0 ? (stats ? k_extend<0, true> : k_extend<0, false>) : (stats ? k_extend<1, true> : k_extend<1, false>);
+		mode == 0 ? (vis ? (stats ? k_extend<0, true, true> : k_extend<0, false, true>) : (stats ? k_extend<0, true, false> : k_extend<0, false, false>))
+		          : (stats ? k_extend<1, true, false> : k_extend<1, false, false>);
 	if (c->extend_blocks[mode] == 0 || mode == 0) {
 		if (smem > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 		int per_sm = 0;
@@ -551,7 +552,7 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 			stage_begin(c, 2, ev);
 			k_bdpt_connect<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb);
 			stage_end(c, ev);
-			if ((rc = launch_extend(c, sc, 2, 0))) return rc;
+			if ((rc = launch_extend(c, sc, 2, 0, true))) return rc;   // visibility rays: t limit + early stop
 			stage_begin(c, 3, ev);
 			k_bdpt_resolve<<<grid, 256, 0, c->stream>>>(c->pb);
 			k_bdpt_accumulate<<<(pp.p_pad + 255) / 256, 256, 0, c->stream>>>(pp, c->pb, c->d_accum);

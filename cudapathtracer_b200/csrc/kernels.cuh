@@ -177,7 +177,9 @@ struct ExtendTuning {
 #define CUPT_EXTEND_MIN_BLOCKS 7
 #endif
 
-template <bool STATS>
+// VIS: the rays are BDPT visibility rays whose record carries an early-stop distance (bdpt.cuh); a separate
+// instantiation because the extra register and compare cost the ordinary launches 3 % (measured)
+template <bool STATS, bool VIS>
 __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffers& pb, const uint32_t count, uint32_t* cursor,
                                             const uint32_t* __restrict__ queue, uint2* stack, const int stride,
                                             uint32_t* wlist, unsigned long long* wkeys, uint32_t* wids, const ExtendTuning tune, uint32_t& n_nodes, uint32_t& n_tris, uint32_t& n_rays)
@@ -191,6 +193,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 	uint2 ngroup = make_uint2(0u, 0u), tgroup = make_uint2(0u, 0u), pgroup = make_uint2(0u, 0u);
 	int sp = 0;
 	uint32_t slot = 0u;
+	float tstop = 0.0f;
 	for (;;) {
 		uint32_t act = __ballot_sync(FULL, active);
 		if (!exhausted && __popc(act) <= tune.fetch_thresh) {
@@ -211,6 +214,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 					const float4 b = pb.rayB[slot];
 					wide_ray_init(r, mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y));
 					r.best = b.z;   // the producer's t limit: CUPT_MAX_FLOAT (kernel.cu:117) except for BDPT visibility rays
+					if (VIS) tstop = b.w;   // stop as soon as a hit nearer than this is known
 					ngroup = make_uint2(0u, 0x80000000u); tgroup = make_uint2(0u, 0u);
 					pgroup = make_uint2(0u, 0u);
 					sp = 0;
@@ -311,6 +315,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 			}
 		}
 		// ---- pop / finish -------------------------------------------------------------------------------------------
+		if (VIS && active && r.best < tstop) { ngroup.y = 0u; tgroup.y = 0u; pgroup.y = 0u; sp = 0; }   // an occluder is known: whatever is nearer changes nothing
 		if (active && !group_has_node(ngroup)) {
 			if (sp == 0) {     // (a ray that ends has had its pending primitives flushed above)
 				reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(r.best, __int_as_float(r.best_id));
@@ -323,7 +328,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 	}
 }
 
-template <int MODE, bool STATS>
+template <int MODE, bool STATS, bool VIS>
 __global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene sc, PathBuffers pb, int depth, int qsel, ExtendTuning tune)
 {
 	extern __shared__ uint2 smem_stack[];
@@ -337,7 +342,7 @@ __global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene
 		unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_stack + (size_t)sc.stack_cap * blockDim.x);
 		uint32_t* lists = reinterpret_cast<uint32_t*>(keys + blockDim.x);
 		const uint32_t w = threadIdx.x >> 5;
-		extend_wide<STATS>(sc, pb, count, cursor, queue, smem_stack + threadIdx.x, blockDim.x, lists + 64u * w, keys + 32u * w,
+		extend_wide<STATS, VIS>(sc, pb, count, cursor, queue, smem_stack + threadIdx.x, blockDim.x, lists + 64u * w, keys + 32u * w,
 		                   lists + 64u * w + 32u, tune, n_nodes, n_tris, n_rays);
 	} else {
 		for (;;) {
