@@ -221,7 +221,9 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel, bool
 		stage_begin(c, 1, ev2);
 		CK(cudaMemsetAsync(c->pb.counters + 126, 0, sizeof(uint32_t), c->stream));
 		k_verify_strict<<<c->num_sms * 8, 256, 0, c->stream>>>(sc, c->pb, depth, qsel);
-		k_retrace_strict<<<c->num_sms, 64, 0, c->stream>>>(sc, c->pb);
+		const size_t rt_smem = (size_t)sc.stack_cap * 64 * sizeof(uint2);
+		if (rt_smem > 48 * 1024) CK(cudaFuncSetAttribute(k_retrace_strict, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rt_smem));
+		k_retrace_strict<<<c->num_sms * 4, 64, rt_smem, c->stream>>>(sc, c->pb);
 		stage_end(c, ev2);
 		CK(cudaGetLastError());
 		c->launches += 2;

@@ -459,16 +459,52 @@ __global__ void __launch_bounds__(256) k_verify_strict(DevScene sc, PathBuffers 
 	}
 }
 
+// The reference's answer for a listed ray = argmin over the triangles its traversal REACHES (it has no t range, so it
+// tests every triangle of every node whose box passes; equal t: the first visited, i.e. the lowest rank).  Instead of
+// repeating that traversal (hundreds of dependent node fetches per ray: 0.5 ms per launch for a few thousand rays),
+// walk the wide BVH and accept a hit only if the reference reaches its triangle (strict_reached).
 __global__ void __launch_bounds__(64) k_retrace_strict(DevScene sc, PathBuffers pb)
 {
+	extern __shared__ uint2 rt_stack[];
+	uint2* stack = rt_stack + threadIdx.x;
+	const int stride = (int)blockDim.x;
 	const uint32_t count = pb.counters[126];
 	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
 		const uint32_t slot = pb.retrace[i];
 		const float4 a = pb.rayA[slot], b = pb.rayB[slot];
-		Hit hit;
-		uint32_t nn = 0, nt = 0;
-		traverse_bvh2_ref<false>(sc.bvh2, sc.verts, sc.tris, mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), hit, nn, nt);
-		reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(hit.t, __int_as_float(hit.id));
+		const f3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, b.x, b.y);
+		WideRay r;
+		wide_ray_init(r, o, d);
+		uint2 ngroup = make_uint2(0u, 0x80000000u), tgroup = make_uint2(0u, 0u);
+		int sp = 0;
+		for (;;) {
+			if (group_has_node(ngroup)) {
+				uint2 rest;
+				wide_node_step(sc.nodes, r, ngroup, rest, tgroup);
+				if (group_has_node(rest)) { if (sp < sc.stack_cap) stack[sp * stride] = rest; ++sp; }
+			} else {
+				tgroup = ngroup;
+				ngroup = make_uint2(0u, 0u);
+			}
+			while (tgroup.y != 0u) {
+				const uint32_t k = __ffs(tgroup.y) - 1u;
+				tgroup.y &= tgroup.y - 1u;
+				const float4* pp = sc.prims + (size_t)(tgroup.x + k) * 3u;
+				const float4 r0 = ldg_nc_f4(pp + 0), r1 = ldg_nc_f4(pp + 1), r2 = ldg_nc_f4(pp + 2);
+				const float t = tri_refexact(o, d, r0, r1, r2);   // (strict mode: triangles only, the reference's own test)
+				const uint32_t rank = __float_as_uint(r2.z);
+				const int32_t id = (int32_t)__float_as_uint(r2.y);
+				if (0.0f < t && (t < r.best || (t == r.best && rank < r.best_rank)) && strict_reached(sc, o, d, id)) {
+					r.best = t; r.best_rank = rank; r.best_id = id;
+				}
+			}
+			if (!group_has_node(ngroup)) {
+				if (sp == 0) break;
+				--sp;
+				ngroup = stack[sp * stride];
+			}
+		}
+		reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(r.best, __int_as_float(r.best_id));
 	}
 	if (blockIdx.x == 0 && threadIdx.x == 0 && count) atomicAdd(&pb.stats[4], (unsigned long long)count);
 }
