@@ -302,6 +302,8 @@ def main():
     h2d = nv * 12 + nt * 28 + nt * 16 + nm * 32 + (nl + 1) * 48 + 32
     if args.bvh == "host":
         h2d += info["num_nodes"] * 80 + info["num_tri_records"] * 48      # the device builder uploads no tree
+    if mode != api.TRAVERSAL_WIDE:
+        h2d += len(n2) * 32 * 2 + nt * 4                                   # reference-layout tree, its parent-linked copy, leaf parents
     d2h = W * H * 12
 
     def e2e_step():
