@@ -176,13 +176,17 @@ struct ExtendTuning {
 #ifndef CUPT_EXTEND_MIN_BLOCKS
 #define CUPT_EXTEND_MIN_BLOCKS 7
 #endif
+#ifndef CUPT_NODE_FAST
+#define CUPT_NODE_FAST 1   // 0: the hot kernel uses wide_node_step (the definition) instead of wide_node_step_fast
+#endif
 
 // VIS: the rays are BDPT visibility rays whose record carries an early-stop distance (bdpt.cuh); a separate
 // instantiation because the extra register and compare cost the ordinary launches 3 % (measured)
 template <bool STATS, bool VIS>
 __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffers& pb, const uint32_t count, uint32_t* cursor,
                                             const uint32_t* __restrict__ queue, uint2* stack, const int stride,
-                                            uint32_t* wlist, unsigned long long* wkeys, uint32_t* wids, const ExtendTuning tune, uint32_t& n_nodes, uint32_t& n_tris, uint32_t& n_rays)
+                                            uint32_t* wlist, unsigned long long* wkeys, uint32_t* wids, const ExtendTuning tune, const uint8_t* perm,
+                                            uint32_t& n_nodes, uint32_t& n_tris, uint32_t& n_rays)
 {
 	const uint32_t FULL = 0xffffffffu;
 	const uint32_t lane = threadIdx.x & 31u;
@@ -231,7 +235,11 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 		// ---- node step ------------------------------------------------------------------------------------------
 		if (active && group_has_node(ngroup)) {   // (only node groups are ever pushed, so a popped group always has one)
 			uint2 rest;
+#if CUPT_NODE_FAST
+			wide_node_step_fast(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits, perm + (r.oct_inv << 8));
+#else
 			wide_node_step(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits);
+#endif
 			if (group_has_node(rest)) { stack[sp * stride] = rest; ++sp; }
 			if (STATS) ++n_nodes;
 		}
@@ -338,12 +346,21 @@ __global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene
 	const uint32_t* __restrict__ queue = pb.queue[qsel];
 	uint32_t n_nodes = 0, n_tris = 0, n_rays = 0;
 	if (MODE == 0) {
+		// front-to-back order of the hit inner children (wide_node_step_fast): perm[oct][mask] has bit (s ^ oct) set for every slot s in mask
+		__shared__ uint8_t s_perm[8 * 256];
+		for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) {
+			uint32_t v = 0u;
+			for (uint32_t sl = 0; sl < 8u; ++sl)
+				if ((i >> sl) & 1u) v |= 1u << (sl ^ (i >> 8));
+			s_perm[i] = (uint8_t)v;
+		}
+		__syncthreads();
 		// shared memory: per-thread stacks [stack_cap][128] uint2, then per warp: 32 keys (u64), 32 list entries, 32 ids
 		unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_stack + (size_t)sc.stack_cap * blockDim.x);
 		uint32_t* lists = reinterpret_cast<uint32_t*>(keys + blockDim.x);
 		const uint32_t w = threadIdx.x >> 5;
 		extend_wide<STATS, VIS>(sc, pb, count, cursor, queue, smem_stack + threadIdx.x, blockDim.x, lists + 64u * w, keys + 32u * w,
-		                   lists + 64u * w + 32u, tune, n_nodes, n_tris, n_rays);
+		                   lists + 64u * w + 32u, tune, s_perm, n_nodes, n_tris, n_rays);
 	} else {
 		for (;;) {
 			uint32_t base = 0;

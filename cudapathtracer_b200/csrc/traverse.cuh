@@ -221,6 +221,73 @@ __device__ __forceinline__ void wide_node_step(const uint4* __restrict__ nodes, 
 	tgroup = make_uint2(n1.y, hitmask & 0x00ffffffu);
 }
 
+// The node step of the hot kernel (k_extend).  Same boxes, same slack and same result groups as wide_node_step, but
+// the hit mask is built differently: wide_node_step spends an FSETP and five predicated ALU instructions per child on
+// `hitmask |= cb << bi` (profiles/r1i_extend_opcodes.md: the ALU pipe — PRMT, FMNMX, LOP3, SHF, SEL — carries 45 % of
+// the kernel's instructions and the FMA pipe 31 %).  Here
+//   * a child is hit iff none of  tmax - tmin,  best - tmin,  tmax  is negative (tmin/tmax over the three axes only):
+//     two FADDs on the FMA pipe, one LOP3 that ORs the three sign bits and one funnel shift that appends the sign to an
+//     8-bit miss mask — 4 ALU + 2 FMA instructions per child instead of 10 ALU;
+//   * the hit inner children are put in front-to-back order (slot XOR octant) by one look-up in a 2 KB shared-memory
+//     table `perm` (8 octants x 256 masks) instead of per-child variable shifts;
+//   * only the hit LEAF children are expanded to primitive bits, in a loop that runs once per hit leaf.
+// No value here can be an infinity or NaN (see wide_ray_init), and without flush-to-zero a - b is negative exactly
+// when a < b, so the decisions are those of `max(tmin, 0) <= min(tmax, best)`.
+__device__ __forceinline__ void wide_node_step_fast(const uint4* __restrict__ nodes, const WideRay& r, uint2& ngroup, uint2& rest, uint2& tgroup,
+                                                    const uint32_t bias_bits, const uint8_t* __restrict__ perm)
+{
+	const uint32_t hits = ngroup.y;
+	const uint32_t bit = 31u - __clz(hits);
+	rest = make_uint2(ngroup.x, hits & ~(1u << bit));
+	const uint32_t slot = (bit - 24u) ^ r.oct_inv;
+	const uint32_t rel = __popc(hits & 0xffu & ~(0xffffffffu << slot));
+	const uint4* np = nodes + (size_t)(ngroup.x + rel) * 5u;
+	const uint4 n0 = ldg_nc_u4(np + 0), n1 = ldg_nc_u4(np + 1), n2 = ldg_nc_u4(np + 2), n3 = ldg_nc_u4(np + 3), n4 = ldg_nc_u4(np + 4);
+	const bool negx = r.ix < 0.0f, negy = r.iy < 0.0f, negz = r.iz < 0.0f;
+	const float sx = __uint_as_float((n0.w & 0xffu) << 23) * r.ix;
+	const float sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * r.iy;
+	const float sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * r.iz;
+	const float ox = (__uint_as_float(n0.x) - r.o.x) * r.ix;
+	const float oy = (__uint_as_float(n0.y) - r.o.y) * r.iy;
+	const float oz = (__uint_as_float(n0.z) - r.o.z) * r.iz;
+	const float kx = fmaf(fabsf(sx), 0.015625f, fmaf(255.0f, fabsf(sx), fabsf(ox)) * 4.76837158203125e-7f);   // per-axis slack, see wide_node_step
+	const float ky = fmaf(fabsf(sy), 0.015625f, fmaf(255.0f, fabsf(sy), fabsf(oy)) * 4.76837158203125e-7f);
+	const float kz = fmaf(fabsf(sz), 0.015625f, fmaf(255.0f, fabsf(sz), fabsf(oz)) * 4.76837158203125e-7f);
+	const float bx = fmaf(-CUPT_QBIAS, sx, ox), by = fmaf(-CUPT_QBIAS, sy, oy), bz = fmaf(-CUPT_QBIAS, sz, oz);
+	const float onx = bx - kx, ony = by - ky, onz = bz - kz;
+	const float ofx = bx + kx, ofy = by + ky, ofz = bz + kz;
+	const uint32_t imask = n0.w >> 24;
+	uint32_t miss = 0u;
+#pragma unroll
+	for (int h = 1; h >= 0; --h) {   // slots 7..0, so that slot j ends up in bit j
+		const uint32_t qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
+		const uint32_t qhx = h ? n3.w : n3.z, qhy = h ? n4.y : n4.x, qhz = h ? n4.w : n4.z;
+		const uint32_t nx = negx ? qhx : qlx, fx = negx ? qlx : qhx;
+		const uint32_t ny = negy ? qhy : qly, fy = negy ? qly : qhy;
+		const uint32_t nz = negz ? qhz : qlz, fz = negz ? qlz : qhz;
+#pragma unroll
+		for (int j = 3; j >= 0; --j) {
+			const float tnx = fmaf(u8f_biased(nx, j, bias_bits), sx, onx), tny = fmaf(u8f_biased(ny, j, bias_bits), sy, ony), tnz = fmaf(u8f_biased(nz, j, bias_bits), sz, onz);
+			const float tfx = fmaf(u8f_biased(fx, j, bias_bits), sx, ofx), tfy = fmaf(u8f_biased(fy, j, bias_bits), sy, ofy), tfz = fmaf(u8f_biased(fz, j, bias_bits), sz, ofz);
+			const float tmin = fmaxf(fmaxf(tnx, tny), tnz);
+			const float tmax = fminf(fminf(tfx, tfy), tfz);
+			const uint32_t neg = __float_as_uint(tmax - tmin) | __float_as_uint(r.best - tmin) | __float_as_uint(tmax);
+			miss = __funnelshift_l(neg, miss, 1);
+		}
+	}
+	const uint32_t inner = ~miss & imask;
+	uint32_t leaf = ~miss & ~imask & 0xffu;   // (an empty slot has meta 0 and expands to nothing)
+	ngroup = make_uint2(n1.x, ((uint32_t)perm[inner] << 24) | imask);
+	uint32_t mask = 0u;
+	while (leaf != 0u) {
+		const uint32_t s = __ffs(leaf) - 1u;
+		leaf &= leaf - 1u;
+		const uint32_t m = __byte_perm(n1.z, n1.w, s) & 0xffu;
+		mask |= (m >> 5) << (m & 31u);
+	}
+	tgroup = make_uint2(n1.y, mask);
+}
+
 // Tests the lowest-numbered pending record of `tgroup` (three 128-bit fetches) and updates the closest hit with the
 // reference's acceptance rule `0 < t && t < closestT` (kernel.cu:127), equal t resolved by rank.
 __device__ __forceinline__ void wide_prim_step(const float4* __restrict__ prims, WideRay& r, uint2& tgroup)
