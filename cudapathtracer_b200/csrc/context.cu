@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <map>
 #include <cstring>
+#include <thread>
 
 using namespace cupt;
 
@@ -91,12 +92,26 @@ void* stage_alloc(cupt_context* c, size_t bytes)
 	return p;
 }
 
+// host threads for the staging copies: the machine's cores shared between the GPUs it drives (one process per GPU),
+// 2..8 each; set explicitly because launchers such as torchrun export OMP_NUM_THREADS=1
+__attribute__((unused)) int copy_threads()
+{
+	static int n = 0;
+	if (n == 0) {
+		int gpus = 1;
+		if (cudaGetDeviceCount(&gpus) != cudaSuccess || gpus < 1) gpus = 1;
+		const int hw = (int)std::thread::hardware_concurrency();
+		n = std::max(2, std::min(8, hw / gpus));
+	}
+	return n;
+}
+
 void parallel_copy(void* dst, const void* src, size_t bytes)
 {
 	const size_t chunk = (size_t)1 << 20;
 	if (bytes <= 2 * chunk) { memcpy(dst, src, bytes); return; }
 	const int64_t n = (int64_t)((bytes + chunk - 1) / chunk);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(copy_threads())
 	for (int64_t i = 0; i < n; ++i) {
 		const size_t o = (size_t)i * chunk;
 		memcpy((uint8_t*)dst + o, (const uint8_t*)src + o, std::min(chunk, bytes - o));
@@ -421,7 +436,7 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 		const bool staged = ts != nullptr;
 		if (!staged) { tmp.resize(nt); ts = tmp.data(); }
 		const cupt_triangle* tr = s->tris.data();
-#pragma omp parallel for schedule(static) if (nt > 65536)
+#pragma omp parallel for schedule(static) num_threads(copy_threads()) if (nt > 65536)
 		for (int64_t i = 0; i < (int64_t)nt; ++i) {
 			ts[i].n[0] = tr[i].norm.x; ts[i].n[1] = tr[i].norm.y; ts[i].n[2] = tr[i].norm.z;
 			ts[i].mat = tr[i].mat;
