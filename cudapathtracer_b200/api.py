@@ -233,8 +233,8 @@ def bvh2_leaf_order(nodes: np.ndarray, ntris: int) -> np.ndarray:
     return rank
 
 
-NODE8 = np.dtype([("p", "<f4", (3,)), ("e", "u1", (3,)), ("imask", "u1"), ("child_base", "<u4"), ("tri_base", "<u4"),
-                  ("meta", "u1", (8,)), ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])
+NODE8 = np.dtype([("p", "<f4", (3,)), ("e", "u1", (3,)), ("imask", "u1"), ("child_base", "<u4"), ("reserved", "<u4"), ("tri_base", "<u4"),
+                  ("pvalid", "<u4"), ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])
 PRIM48 = np.dtype([("a", "<f4", (3,)), ("b", "<f4", (3,)), ("c", "<f4", (3,)), ("id", "<u4"), ("rank", "<u4"), ("kind", "<u4")])
 assert NODE8.itemsize == 80 and PRIM48.itemsize == 48
 

@@ -333,11 +333,10 @@ int cupt_bvh_build(const cupt_scene* s, const cupt_bvh_opts* opts, cupt_bvh** ou
 			sah += c.box.area() / rootArea * (c.left < 0 ? c.count : 1.0);
 			if (c.left >= 0) {
 				nd.imask |= (uint8_t)(1u << sl);
-				nd.meta[sl] = (uint8_t)((1u << 5) | (24u + sl));
 				queue.push_back({kids[k], cur.depth + 1});
 			} else {
 				const uint32_t unary = c.count == 1 ? 1u : (c.count == 2 ? 3u : 7u);
-				nd.meta[sl] = (uint8_t)((unary << 5) | triOfs);
+				nd.pvalid |= unary << (4 * sl);
 				for (int32_t i = 0; i < c.count; ++i) {
 					const uint32_t p = B.idx[(size_t)c.first + i];
 					Prim48 r;

@@ -485,12 +485,11 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 		const double area2 = 2.0 * (double)half_area(clo[q][0], clo[q][1], clo[q][2], chi[q][0], chi[q][1], chi[q][2]);
 		if (cc > A.max_leaf) {
 			nd.imask |= (uint8_t)(1u << sl);
-			nd.meta[sl] = (uint8_t)((1u << 5) | (24u + sl));
 			A.next_items[child_off + ninner++] = c;
 			sah += area2 * A.inv_root_area;
 		} else {
 			const uint32_t unary = cc == 1 ? 1u : (cc == 2 ? 3u : 7u);
-			nd.meta[sl] = (uint8_t)((unary << 5) | triOfs);
+			nd.pvalid |= unary << (4 * sl);
 			int32_t stack[4]; int sp = 0;
 			stack[sp++] = c;
 			uint32_t w = 0;

@@ -185,7 +185,7 @@ struct ExtendTuning {
 template <bool STATS, bool VIS>
 __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffers& pb, const uint32_t count, uint32_t* cursor,
                                             const uint32_t* __restrict__ queue, uint2* stack, const int stride,
-                                            uint32_t* wlist, unsigned long long* wkeys, uint32_t* wids, const ExtendTuning tune, const uint8_t* perm,
+                                            uint32_t* wlist, unsigned long long* wkeys, uint32_t* wids, const ExtendTuning tune, const uint8_t* perm, const uint32_t* nib,
                                             uint32_t& n_nodes, uint32_t& n_tris, uint32_t& n_rays)
 {
 	const uint32_t FULL = 0xffffffffu;
@@ -236,7 +236,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 		if (active && group_has_node(ngroup)) {   // (only node groups are ever pushed, so a popped group always has one)
 			uint2 rest;
 #if CUPT_NODE_FAST
-			wide_node_step_fast(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits, perm + (r.oct_inv << 8));
+			wide_node_step_fast(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits, perm + (r.oct_inv << 8), nib);
 #else
 			wide_node_step(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits);
 #endif
@@ -272,6 +272,23 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 						const uint32_t total = __shfl_sync(FULL, incl, 31);
 						uint32_t pos = incl - cnt;
 						if (cnt != 0u) {
+#if CUPT_NODE_FAST
+							// groups are {node index, sparse record mask} (wide_node_step_fast): the entry names the node and the
+							// bit; the lane that TESTS the pair turns them into a record index (sparse_record), so this serial
+							// low-occupancy loop stays at one store per pair.  (The 64-bit entries overlay wlist + wids: wids
+							// is written only after every lane has read its entry.)
+							uint2* wl2 = reinterpret_cast<uint2*>(wlist);
+							while (pgroup.y != 0u && pos < 32u) {
+								const uint32_t k = __ffs(pgroup.y) - 1u;
+								pgroup.y &= pgroup.y - 1u;
+								wl2[pos++] = make_uint2(pgroup.x, (k << 5) | lane);
+							}
+							while (tgroup.y != 0u && pos < 32u) {
+								const uint32_t k = __ffs(tgroup.y) - 1u;
+								tgroup.y &= tgroup.y - 1u;
+								wl2[pos++] = make_uint2(tgroup.x, (k << 5) | lane);
+							}
+#else
 							while (pgroup.y != 0u && pos < 32u) {
 								const uint32_t k = __ffs(pgroup.y) - 1u;
 								pgroup.y &= pgroup.y - 1u;
@@ -282,20 +299,30 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 								tgroup.y &= tgroup.y - 1u;
 								wlist[pos++] = ((tgroup.x + k) << 5) | lane;
 							}
+#endif
 						}
 						const unsigned long long mykey = ((unsigned long long)__float_as_uint(r.best) << 32) | r.best_rank;
 						wkeys[lane] = mykey;
 						__syncwarp();
 						const bool work = lane < total;
+#if CUPT_NODE_FAST
+						const uint2 e2 = work ? reinterpret_cast<const uint2*>(wlist)[lane] : make_uint2(0u, 0u);
+						const uint32_t owner = e2.y & 31u;
+#else
 						const uint32_t e = work ? wlist[lane] : 0u;
 						const uint32_t owner = e & 31u;
+#endif
 						f3 po, pd;
 						po.x = __shfl_sync(FULL, r.o.x, owner); po.y = __shfl_sync(FULL, r.o.y, owner); po.z = __shfl_sync(FULL, r.o.z, owner);
 						pd.x = __shfl_sync(FULL, r.d.x, owner); pd.y = __shfl_sync(FULL, r.d.y, owner); pd.z = __shfl_sync(FULL, r.d.z, owner);
 						unsigned long long hkey = ~0ull;
 						uint32_t hid = 0u;
 						if (work) {
+#if CUPT_NODE_FAST
+							const float4* pp = sc.prims + (size_t)sparse_record(node_records(sc.nodes, e2.x), e2.y >> 5) * 3u;   // (the node is an L1 hit)
+#else
 							const float4* pp = sc.prims + (size_t)(e >> 5) * 3u;
+#endif
 							const float4 r0 = ldg_nc_f4(pp + 0), r1 = ldg_nc_f4(pp + 1), r2 = ldg_nc_f4(pp + 2);
 							const uint32_t kind = __float_as_uint(r2.w);
 							float t;
@@ -354,13 +381,21 @@ __global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene
 				if ((i >> sl) & 1u) v |= 1u << (sl ^ (i >> 8));
 			s_perm[i] = (uint8_t)v;
 		}
+		// nib[mask]: the nibbles of the slots in mask (layout.h: one nibble of valid-record bits per slot)
+		__shared__ uint32_t s_nib[256];
+		for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x) {
+			uint32_t v = 0u;
+			for (uint32_t sl = 0; sl < 8u; ++sl)
+				if ((i >> sl) & 1u) v |= 7u << (4u * sl);
+			s_nib[i] = v;
+		}
 		__syncthreads();
 		// shared memory: per-thread stacks [stack_cap][128] uint2, then per warp: 32 keys (u64), 32 list entries, 32 ids
 		unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_stack + (size_t)sc.stack_cap * blockDim.x);
 		uint32_t* lists = reinterpret_cast<uint32_t*>(keys + blockDim.x);
 		const uint32_t w = threadIdx.x >> 5;
 		extend_wide<STATS, VIS>(sc, pb, count, cursor, queue, smem_stack + threadIdx.x, blockDim.x, lists + 64u * w, keys + 32u * w,
-		                   lists + 64u * w + 32u, tune, s_perm, n_nodes, n_tris, n_rays);
+		                   lists + 64u * w + 32u, tune, s_perm, s_nib, n_nodes, n_tris, n_rays);
 	} else {
 		for (;;) {
 			uint32_t base = 0;

@@ -13,8 +13,13 @@ namespace cupt {
 //   word 0-2   origin p = node lo (f32 x3)
 //   word 3     ex | ey<<8 | ez<<16 | imask<<24      scale_a = 2^(e_a - 127); imask bit s = slot s is an inner child
 //   word 4     child_base   index of the first inner child node (inner children are consecutive, in slot order)
-//   word 5     tri_base     index of the first 48-byte primitive record of this node (records are consecutive)
-//   word 6-7   meta[8]      per slot: 0 = empty; inner: 0b001_11000 | slot; leaf: (unary count 1/3/7)<<5 | first record (0..23)
+//   word 5     0
+//   word 6     tri_base     index of the first 48-byte primitive record of this node (records are consecutive)
+//   word 7     pvalid       one nibble per slot: leaf = unary count of its records (1 / 3 / 7 for 1 / 2 / 3), inner or empty = 0.
+//                           The records of a node are consecutive in slot order, so the record of bit b of this word is
+//                           tri_base + popcount(pvalid below b): the traversal can keep a leaf hit mask in this sparse form
+//                           (pvalid & hit nibbles, no per-child shifts) until a primitive is actually listed for testing;
+//                           words 6-7 are one aligned 8-byte fetch
 //   word 8-9   qlo_x[8]     child box = p + q * scale, lo rounded down, hi rounded up (conservative in exact arithmetic)
 //   word 10-11 qlo_y[8]
 //   word 12-13 qlo_z[8]
@@ -28,8 +33,9 @@ struct alignas(16) Node8 {
 	uint8_t e[3];
 	uint8_t imask;
 	uint32_t child_base;
+	uint32_t reserved;
 	uint32_t tri_base;
-	uint8_t meta[8];
+	uint32_t pvalid;
 	uint8_t qlo[3][8];
 	uint8_t qhi[3][8];
 };

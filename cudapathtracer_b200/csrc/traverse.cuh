@@ -174,7 +174,6 @@ __device__ __forceinline__ void wide_node_step(const uint4* __restrict__ nodes, 
 	const uint4* np = nodes + (size_t)(ngroup.x + rel) * 5u;
 	const uint4 n0 = ldg_nc_u4(np + 0), n1 = ldg_nc_u4(np + 1), n2 = ldg_nc_u4(np + 2), n3 = ldg_nc_u4(np + 3), n4 = ldg_nc_u4(np + 4);
 	const bool negx = r.ix < 0.0f, negy = r.iy < 0.0f, negz = r.iz < 0.0f;
-	const uint32_t oct_inv4 = r.oct_inv * 0x01010101u;
 	const float sx = __uint_as_float((n0.w & 0xffu) << 23) * r.ix;
 	const float sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * r.iy;
 	const float sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * r.iz;
@@ -192,14 +191,10 @@ __device__ __forceinline__ void wide_node_step(const uint4* __restrict__ nodes, 
 	const float onx = bx - kx, ony = by - ky, onz = bz - kz;
 	const float ofx = bx + kx, ofy = by + ky, ofz = bz + kz;
 	const uint32_t imask = n0.w >> 24;
+	const uint32_t pvalid = n1.w;
 	uint32_t hitmask = 0u;
 #pragma unroll
 	for (int h = 0; h < 2; ++h) {
-		const uint32_t meta4 = h ? n1.w : n1.z;
-		const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-		const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-		const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
-		const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
 		const uint32_t qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
 		const uint32_t qhx = h ? n3.w : n3.z, qhy = h ? n4.y : n4.x, qhz = h ? n4.w : n4.z;
 		const uint32_t nx = negx ? qhx : qlx, fx = negx ? qlx : qhx;
@@ -212,13 +207,16 @@ __device__ __forceinline__ void wide_node_step(const uint4* __restrict__ nodes, 
 			const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
 			const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, r.best));
 			if (tmin <= tmax) {
-				const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu, bi = (bit_index4 >> (8 * j)) & 0xffu;
-				hitmask |= cb << bi;
+				// inner child: bit 24 + (slot ^ octant), i.e. front-to-back order from the top; leaf child: its unary record
+				// count at the position of its first record (records are consecutive in slot order: layout.h)
+				const uint32_t s = 4u * h + j;
+				if ((imask >> s) & 1u) hitmask |= 1u << (24u + (s ^ r.oct_inv));
+				else hitmask |= ((pvalid >> (4u * s)) & 7u) << __popc(pvalid & ((1u << (4u * s)) - 1u));
 			}
 		}
 	}
 	ngroup = make_uint2(n1.x, (hitmask & 0xff000000u) | imask);
-	tgroup = make_uint2(n1.y, hitmask & 0x00ffffffu);
+	tgroup = make_uint2(n1.z, hitmask & 0x00ffffffu);
 }
 
 // The node step of the hot kernel (k_extend).  Same boxes, same slack and same result groups as wide_node_step, but
@@ -230,18 +228,24 @@ __device__ __forceinline__ void wide_node_step(const uint4* __restrict__ nodes, 
 //     8-bit miss mask — 4 ALU + 2 FMA instructions per child instead of 10 ALU;
 //   * the hit inner children are put in front-to-back order (slot XOR octant) by one look-up in a 2 KB shared-memory
 //     table `perm` (8 octants x 256 masks) instead of per-child variable shifts;
-//   * only the hit LEAF children are expanded to primitive bits, in a loop that runs once per hit leaf.
+//   * the hit LEAF children are not expanded at all: the primitive group is the node's valid-record word (one nibble
+//     per slot) ANDed with the hit nibbles from a second 1 KB table `nib`, and it is `tgroup = {node index, sparse
+//     mask}` instead of {first record, compact mask}; the record index of a bit is tri_base + popcount(valid bits
+//     below it), computed when the pair is listed (sparse_record).  The first version of this function expanded the
+//     hit leaves in a loop (count << first record per leaf) and gained nothing on diffuse bounces: the loop ran at
+//     3-16 active lanes as often as the warp's worst lane had hit leaves (profiles/r1j_extend_lines.txt).
 // No value here can be an infinity or NaN (see wide_ray_init), and without flush-to-zero a - b is negative exactly
 // when a < b, so the decisions are those of `max(tmin, 0) <= min(tmax, best)`.
 __device__ __forceinline__ void wide_node_step_fast(const uint4* __restrict__ nodes, const WideRay& r, uint2& ngroup, uint2& rest, uint2& tgroup,
-                                                    const uint32_t bias_bits, const uint8_t* __restrict__ perm)
+                                                    const uint32_t bias_bits, const uint8_t* __restrict__ perm, const uint32_t* __restrict__ nib)
 {
 	const uint32_t hits = ngroup.y;
 	const uint32_t bit = 31u - __clz(hits);
 	rest = make_uint2(ngroup.x, hits & ~(1u << bit));
 	const uint32_t slot = (bit - 24u) ^ r.oct_inv;
 	const uint32_t rel = __popc(hits & 0xffu & ~(0xffffffffu << slot));
-	const uint4* np = nodes + (size_t)(ngroup.x + rel) * 5u;
+	const uint32_t node_index = ngroup.x + rel;
+	const uint4* np = nodes + (size_t)node_index * 5u;
 	const uint4 n0 = ldg_nc_u4(np + 0), n1 = ldg_nc_u4(np + 1), n2 = ldg_nc_u4(np + 2), n3 = ldg_nc_u4(np + 3), n4 = ldg_nc_u4(np + 4);
 	const bool negx = r.ix < 0.0f, negy = r.iy < 0.0f, negz = r.iz < 0.0f;
 	const float sx = __uint_as_float((n0.w & 0xffu) << 23) * r.ix;
@@ -276,17 +280,23 @@ __device__ __forceinline__ void wide_node_step_fast(const uint4* __restrict__ no
 		}
 	}
 	const uint32_t inner = ~miss & imask;
-	uint32_t leaf = ~miss & ~imask & 0xffu;   // (an empty slot has meta 0 and expands to nothing)
+	const uint32_t leaf = ~miss & ~imask & 0xffu;   // (an empty slot has no valid bits)
 	ngroup = make_uint2(n1.x, ((uint32_t)perm[inner] << 24) | imask);
-	uint32_t mask = 0u;
-	while (leaf != 0u) {
-		const uint32_t s = __ffs(leaf) - 1u;
-		leaf &= leaf - 1u;
-		const uint32_t m = __byte_perm(n1.z, n1.w, s) & 0xffu;
-		mask |= (m >> 5) << (m & 31u);
-	}
-	tgroup = make_uint2(n1.y, mask);
+	// the hit leaves' records as a SPARSE mask (one nibble per slot, layout.h): no per-child work at all; the record
+	// index of a bit is worked out by sparse_record() when the pair is listed
+	tgroup = make_uint2(node_index, n1.w & nib[leaf]);
 }
+
+// record index of bit b of a sparse primitive group; tv = {tri_base, pvalid} of its node (node_records)
+__device__ __forceinline__ uint2 node_records(const uint4* __restrict__ nodes, const uint32_t node_index)
+{
+#ifdef CUPT_HOST_EMUL
+	return *(reinterpret_cast<const uint2*>(nodes + (size_t)node_index * 5u + 1u) + 1);
+#else
+	return __ldg(reinterpret_cast<const uint2*>(nodes + (size_t)node_index * 5u + 1u) + 1);
+#endif
+}
+__device__ __forceinline__ uint32_t sparse_record(const uint2 tv, const uint32_t b) { return tv.x + (uint32_t)__popc(tv.y & ((1u << b) - 1u)); }
 
 // Tests the lowest-numbered pending record of `tgroup` (three 128-bit fetches) and updates the closest hit with the
 // reference's acceptance rule `0 < t && t < closestT` (kernel.cu:127), equal t resolved by rank.
@@ -336,6 +346,47 @@ __device__ __forceinline__ void traverse_wide(const uint4* __restrict__ nodes, c
 		while (tgroup.y != 0u) {
 			wide_prim_step(prims, r, tgroup);
 			if (STATS) ++n_tris;
+		}
+		if (!group_has_node(ngroup)) {
+			if (sp == 0) break;
+			--sp;
+			ngroup = stack[sp * stride];
+		}
+	}
+	hit.t = r.best; hit.id = r.best_id; hit.rank = r.best_rank;
+}
+
+// One ray through wide_node_step_fast and the sparse primitive groups: the single-ray definition of what k_extend's
+// warp-synchronous loop does per lane (host emulation harness; the kernel shares the two functions it calls).
+// perm: 8 x 256 bytes, perm[oct << 8 | mask] has bit (s ^ oct) set for every slot s in mask; nib: 256 words,
+// nib[mask] = the nibbles of the slots in mask (both built by k_extend in shared memory).
+template <bool STATS>
+__device__ __forceinline__ void traverse_wide_fast(const uint4* __restrict__ nodes, const float4* __restrict__ prims,
+                                                   const f3 o, const f3 d, Hit& hit, uint2* stack, const int stride,
+                                                   const int stack_cap, const uint8_t* __restrict__ perm, const uint32_t* __restrict__ nib,
+                                                   uint32_t& n_nodes, uint32_t& n_tris)
+{
+	WideRay r;
+	wide_ray_init(r, o, d);
+	uint2 ngroup = make_uint2(0u, 0x80000000u);
+	int sp = 0;
+	for (;;) {
+		uint2 rest, tgroup;
+		wide_node_step_fast(nodes, r, ngroup, rest, tgroup, CUPT_QBIAS_BITS, perm + (r.oct_inv << 8), nib);
+		if (group_has_node(rest)) {
+			if (sp < stack_cap) stack[sp * stride] = rest;
+			++sp;
+		}
+		if (STATS) ++n_nodes;
+		if (tgroup.y != 0u) {
+			const uint2 tv = node_records(nodes, tgroup.x);
+			while (tgroup.y != 0u) {
+				const uint32_t k = __ffs(tgroup.y) - 1u;
+				tgroup.y &= tgroup.y - 1u;
+				uint2 one = make_uint2(sparse_record(tv, k), 1u);
+				wide_prim_step(prims, r, one);
+				if (STATS) ++n_tris;
+			}
 		}
 		if (!group_has_node(ngroup)) {
 			if (sp == 0) break;

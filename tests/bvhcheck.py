@@ -21,11 +21,12 @@ def check_wide_bvh(c, nodes, prims, info, max_leaf):
     assert np.array_equal(prims["a"], v0)
     assert np.array_equal(prims["b"], pos[t["v1"]] - v0) and np.array_equal(prims["c"], pos[t["v2"]] - v0)   # e1, e2 as f32 subtractions
     lo, hi = decode_boxes(nodes)
-    meta = nodes["meta"]
-    inner = (meta & 0x1F) >= 24
-    leafc = (~inner) & (meta != 0)
-    assert np.array_equal(np.packbits(inner[:, ::-1], axis=1)[:, 0], nodes["imask"])
-    assert np.all((meta[inner] & 0x1F) - 24 == np.nonzero(inner)[1])              # inner meta carries its own slot
+    imask = nodes["imask"].astype(np.uint32)
+    pvalid = nodes["pvalid"].astype(np.uint64)
+    slots = np.arange(8)
+    inner = ((imask[:, None] >> slots) & 1).astype(bool)                          # [n,8]
+    nib = ((pvalid[:, None] >> (4 * slots).astype(np.uint64)) & np.uint64(0xF)).astype(np.int64)   # valid-record nibble per slot
+    assert np.all(np.isin(nib, (0, 1, 3, 7))) and np.all(nib[inner] == 0) and np.all(nodes["reserved"] == 0)
     # walk: inner children consecutive in slot order, every node reachable once, boxes nested and conservative
     seen = np.zeros(len(nodes), np.int32)
     tri_seen = np.zeros(n, np.int32)
@@ -38,9 +39,9 @@ def check_wide_bvh(c, nodes, prims, info, max_leaf):
         seen[i] += 1
         maxd = max(maxd, d)
         k = 0
+        ofs = 0
         for s in range(8):
-            m = int(meta[i, s])
-            if m == 0:
+            if not inner[i, s] and nib[i, s] == 0:
                 continue
             blo, bhi = lo[i, :, s], hi[i, :, s]
             assert np.all(blo <= bhi)
@@ -48,9 +49,10 @@ def check_wide_bvh(c, nodes, prims, info, max_leaf):
                 stack.append((int(nodes["child_base"][i]) + k, anc + [(blo, bhi)], d + 1))
                 k += 1
             else:
-                cnt = {1: 1, 3: 2, 7: 3}[m >> 5]
+                cnt = {1: 1, 3: 2, 7: 3}[int(nib[i, s])]
                 assert cnt <= max_leaf
-                first = int(nodes["tri_base"][i]) + (m & 0x1F)
+                first = int(nodes["tri_base"][i]) + ofs                             # records are consecutive in slot order
+                ofs += cnt
                 for r in range(first, first + cnt):
                     tri_seen[r] += 1
                     for alo, ahi in anc + [(blo, bhi)]:                            # every ancestor's decoded box is conservative

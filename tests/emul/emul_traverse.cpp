@@ -24,6 +24,7 @@ static inline uint32_t __float_as_uint(float f) { uint32_t u; memcpy(&u, &f, 4);
 static inline int __clz(uint32_t x) { return x ? __builtin_clz(x) : 32; }
 static inline int __popc(uint32_t x) { return __builtin_popcount(x); }
 static inline int __ffs(uint32_t x) { return __builtin_ffs((int)x); }
+static inline uint32_t __funnelshift_l(uint32_t lo, uint32_t hi, uint32_t s) { return (uint32_t)(((((uint64_t)hi << 32) | lo) << (s & 31u)) >> 32); }
 #include "../../cudapathtracer_b200/csrc/traverse.cuh"
 
 using namespace cupt;
@@ -45,6 +46,40 @@ extern "C" int emul_trace_wide(const void* nodes80, const void* prims48, int dep
 	}
 	if (counts) { counts[0] = nn; counts[1] = nt; }
 	return max_sp_ok ? 0 : -1;
+}
+
+// the same rays through the hot kernel's node step (wide_node_step_fast: sign-bit hit mask, order table, sparse
+// primitive groups) with the two look-up tables built the way k_extend builds them
+extern "C" int emul_trace_wide_fast(const void* nodes80, const void* prims48, int depth, const float* rays6, long long n,
+                                    int32_t* ids, float* ts, unsigned long long* counts)
+{
+	std::vector<uint8_t> perm(8 * 256);
+	std::vector<uint32_t> nib(256);
+	for (uint32_t i = 0; i < 8u * 256u; ++i) {
+		uint32_t v = 0u;
+		for (uint32_t sl = 0; sl < 8u; ++sl)
+			if ((i >> sl) & 1u) v |= 1u << (sl ^ (i >> 8));
+		perm[i] = (uint8_t)v;
+	}
+	for (uint32_t i = 0; i < 256u; ++i) {
+		uint32_t v = 0u;
+		for (uint32_t sl = 0; sl < 8u; ++sl)
+			if ((i >> sl) & 1u) v |= 7u << (4u * sl);
+		nib[i] = v;
+	}
+	unsigned long long nn = 0, nt = 0;
+#pragma omp parallel for schedule(dynamic, 256) reduction(+ : nn, nt)
+	for (long long i = 0; i < n; ++i) {
+		std::vector<uint2> stack((size_t)depth + 1);
+		Hit h;
+		uint32_t a = 0, b = 0;
+		traverse_wide_fast<true>((const uint4*)nodes80, (const float4*)prims48, mk3(rays6[6 * i], rays6[6 * i + 1], rays6[6 * i + 2]),
+		                         mk3(rays6[6 * i + 3], rays6[6 * i + 4], rays6[6 * i + 5]), h, stack.data(), 1, depth, perm.data(), nib.data(), a, b);
+		ids[i] = h.id; ts[i] = h.t;
+		nn += a; nt += b;
+	}
+	if (counts) { counts[0] = nn; counts[1] = nt; }
+	return 0;
 }
 
 extern "C" int emul_trace_bvh2(const void* nodes32, const float* verts, const void* tris28, const float* rays6, long long n,

@@ -24,11 +24,13 @@ def emul(lib):
     return C.CDLL(EMUL)
 
 
-def emul_trace(emul, nodes, prims, depth, rays):
+def emul_trace(emul, nodes, prims, depth, rays, fast=False):
+    """fast: through wide_node_step_fast and the sparse primitive groups (what k_extend runs) instead of the definition"""
     rays = np.ascontiguousarray(rays, dtype=np.float32)
     ids, ts = np.zeros(len(rays), np.int32), np.zeros(len(rays), np.float32)
     cnt = (C.c_ulonglong * 2)()
-    emul.emul_trace_wide(P(nodes), P(prims), depth, P(rays), C.c_longlong(len(rays)), P(ids), P(ts), cnt)
+    fn = emul.emul_trace_wide_fast if fast else emul.emul_trace_wide
+    fn(P(nodes), P(prims), depth, P(rays), C.c_longlong(len(rays)), P(ids), P(ts), cnt)
     return ids, ts, (cnt[0], cnt[1])
 
 
@@ -70,6 +72,9 @@ def test_wide_traversal_logic_matches_brute_force_and_reference(get_case, emul, 
     ids, ts, (nn, nt) = emul_trace(emul, nodes, prims, b.info()["depth"], rays)
     bi, bt = c.osc.brute_force(rays, c.rank)
     assert np.array_equal(ids, bi) and ts.tobytes() == bt.tobytes()               # == argmin over all triangles
+    fi, ft, (fn, fnt) = emul_trace(emul, nodes, prims, b.info()["depth"], rays, fast=True)
+    assert np.array_equal(fi, bi) and ft.tobytes() == bt.tobytes()                # the hot kernel's node step: same hits
+    assert fn == nn                                                                # ... through the same nodes
     ri, rt = c.osc.trace_rays(rays)
     differ = (ids != ri) | (ts.view(np.uint32) != rt.view(np.uint32))
     assert differ.sum() <= 4 and np.all(ts[differ] <= rt[differ])                 # only hits the reference dropped
