@@ -144,13 +144,26 @@ struct WideRay {
 	uint32_t best_rank;    // rank < 0 never holds: a tie can only replace an existing hit
 };
 
+// 1/x for the box tests only: MUFU.RCP (1 ulp) instead of the ~10-instruction IEEE division; the error scales every
+// plane distance of an axis by (1 + 2^-23) at most, a quarter of the 2^-21 relative slack of the node step
+__device__ __forceinline__ float box_rcp(float x)
+{
+#ifdef CUPT_HOST_EMUL
+	return 1.0f / x;
+#else
+	float y;
+	asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+	return y;
+#endif
+}
+
 __device__ __forceinline__ void wide_ray_init(WideRay& r, const f3 o, const f3 d)
 {
 	const float big = 1.0e20f;   // keeps 2^15 * scale / d finite for every scene inside the reference's +-1e4 world (BVH.h:21-25)
 	r.o = o; r.d = d;
-	r.ix = fabsf(d.x) > 1.0e-20f ? 1.0f / d.x : copysignf(big, d.x);
-	r.iy = fabsf(d.y) > 1.0e-20f ? 1.0f / d.y : copysignf(big, d.y);
-	r.iz = fabsf(d.z) > 1.0e-20f ? 1.0f / d.z : copysignf(big, d.z);
+	r.ix = fabsf(d.x) > 1.0e-20f ? box_rcp(d.x) : copysignf(big, d.x);
+	r.iy = fabsf(d.y) > 1.0e-20f ? box_rcp(d.y) : copysignf(big, d.y);
+	r.iz = fabsf(d.z) > 1.0e-20f ? box_rcp(d.z) : copysignf(big, d.z);
 	r.oct_inv = (r.ix < 0.0f ? 0u : 4u) | (r.iy < 0.0f ? 0u : 2u) | (r.iz < 0.0f ? 0u : 1u);
 	r.best = CUPT_MAX_FLOAT; r.best_id = -1; r.best_rank = 0u;
 }
