@@ -608,3 +608,43 @@ def test_device_radix_sort(ctx):
             k, v = ctx.debug_sort_pairs(keys, vals, passes)
             assert np.array_equal(v, want.astype(np.uint32)), (n, passes)
             assert np.array_equal(k, keys[want])
+
+
+def test_large_scene_upload_and_soup_hits(ctx, lib):
+    """a 1.5 M-triangle soup (config 4's generator): its arrays (42 MB of triangles, 72 MB of primitive records) outgrow the
+    32 MB pinned staging buffer of the uploads (context.cu: stage_alloc), so the grow / rewind / wait paths run; hits
+    through the host-built and the device-built tree against the oracle's brute force over ALL triangles, bit for bit,
+    then a small scene again on the same context (the buffer is reused)"""
+    import oraclebind
+    n = 1_500_000
+    sc = scenes.triangle_soup(n)
+    s = api.SceneHandle(); s.add_scene(sc)
+    v, t, mm, l = s.arrays()
+    rng = np.random.default_rng(5)
+    o = rng.uniform(-50, 50, size=(300, 3)); d = rng.normal(size=(300, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.concatenate([o, d], axis=1).astype(np.float32)
+    osc = oraclebind.OracleScene(v, t, mm, l, s.total_light_area, np.zeros(1, api.BVH2_NODE))
+    want = osc.brute_force(rays, None)
+    assert (want[0] >= 0).sum() > 30
+    ctx.set_options(traversal=api.TRAVERSAL_WIDE)
+    for _ in range(2):                                                           # twice: first use grows the buffer, second reuses it
+        ctx.set_scene(s)
+        b = s.build_bvh()
+        ctx.set_bvh(b)
+        assert hits_equal(ctx.trace_rays(rays), want)
+        b.close()
+    ctx.set_scene(s)
+    ctx.build_bvh_device()
+    assert hits_equal(ctx.trace_rays(rays), want)
+    s.close()
+    # and a 12-triangle scene right after it
+    small = scenes.cornell_box() if hasattr(scenes, "cornell_box") else None
+    if small is not None:
+        s2 = api.SceneHandle(); s2.add_scene(small)
+        v2, t2, m2, l2 = s2.arrays()
+        o2 = oraclebind.OracleScene(v2, t2, m2, l2, s2.total_light_area, np.zeros(1, api.BVH2_NODE))
+        r2 = np.concatenate([rng.uniform(-0.9, 0.9, size=(200, 3)) + [0, 1, 0], rng.normal(size=(200, 3))], axis=1).astype(np.float32)
+        ctx.set_scene(s2)
+        b2 = s2.build_bvh(); ctx.set_bvh(b2)
+        assert hits_equal(ctx.trace_rays(r2), o2.brute_force(r2, None))
+        b2.close(); s2.close()
