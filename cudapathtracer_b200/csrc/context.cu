@@ -295,6 +295,8 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel, bool
 		if (smem > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 		int per_sm = 0;
 		CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+		static const char* bps = getenv("CUPT_EXTEND_BLOCKS_PER_SM");   // experiment knob: fewer resident blocks than the occupancy allows
+		if (bps && atoi(bps) > 0) per_sm = std::min(per_sm, atoi(bps));
 		c->extend_blocks[mode] = std::max(1, per_sm) * c->num_sms;
 		// experiment knob (tools/): shared-memory carveout in percent.  Measured on config 2: 30 (64 KB: 4 resident blocks, 164 KB
 		// of L1) 33.9 ms of extend per frame, default / 44 / 50 (100 KB: 7 blocks, 128 KB of L1) 34.2, 58 34.5, 72 35.2

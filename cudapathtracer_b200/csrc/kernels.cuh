@@ -644,25 +644,32 @@ __global__ void __launch_bounds__(256, CUPT_SHADE_MIN_BLOCKS) k_shade(DevScene s
 				slot_to_pixel(pp, slot, x, y, sl);
 				PhiloxStream rng;
 				rng.init(pp.seed, (uint32_t)x, (uint32_t)y, (uint32_t)(pp.first_sample + sl));
-				f3 lDir;
+				// the (at most) four uniforms of this vertex, drawn BEFORE the 50/50 branch: they span at most two Philox
+				// blocks, and evaluating the second one inside both divergent sides ran its ~100 instructions twice per warp
+				const float ud = rng.draw(draw), ua = rng.draw(draw + 1u), ub = rng.draw(draw + 2u), uc = rng.draw(draw + 3u);
+				// every branch ends in `lDir = normalised(vdir)` and `weight *= albedo * k`: the branches only make vdir (and k)
+				// and the square root, three IEEE divisions and three products run once, after they have rejoined
+				f3 vdir;
+				float k = 1.0f;
+				bool light = false;
 				if (m1.w != 0.f && id >= 0) {
 					// perfect mirror (extension, config 5; no reference code): d - 2 (d.n) n, weight *= albedo, no random numbers
-					lDir = rnormalized(rsub3(d, rmul3(normal, rmul(2.0f, rdot(d, normal)))));
-					wr *= m0.x; wg *= m0.y; wb *= m0.z;
-				} else if (rng.draw(draw++) < 0.5f) {                                // kernel.cu:459
+					vdir = rsub3(d, rmul3(normal, rmul(2.0f, rdot(d, normal))));
+				} else if (ud < 0.5f) {                                              // kernel.cu:459
 					// cosineWeightedRay, kernel.cu:78-99
-					const float u1 = rng.draw(draw++), u2 = rng.draw(draw++);
+					draw += 3u;
+					const float u1 = ua, u2 = ub;
 					const float r = __fsqrt_rn(u1);
 					const float theta = (float)(2 * 3.14159 * (double)u2);
 					const float cx = rmul(r, cosf(theta)), cz = rmul(r, sinf(theta));
 					const float cy = __fsqrt_rn(fmaxf(0.0f, rsub(1.0f, u1)));
 					const f3 tangent = get_tangent(normal), bitangent = rcross(normal, tangent);
-					lDir = rnormalized(radd3(radd3(rmul3(normal, cy), rmul3(tangent, cx)), rmul3(bitangent, cz)));
-					const float k = kBrdf * kPi;
-					wr *= m0.x * k; wg *= m0.y * k; wb *= m0.z * k;                  // kernel.cu:463-464
+					vdir = radd3(radd3(rmul3(normal, cy), rmul3(tangent, cx)), rmul3(bitangent, cz));
+					k = kBrdf * kPi;                                                 // kernel.cu:463-464
 				} else {
 					// light-point sample, kernel.cu:468-507
-					float randArea = rmul(sc.totalLightArea, rng.draw(draw++));
+					draw += 4u;
+					float randArea = rmul(sc.totalLightArea, ua);
 					int sel = sc.numLights;   // fallback entry = triangle 0 (`selectedTri = 0`, kernel.cu:469)
 					if (sc.numLights <= CUPT_LIGHT_SCAN_MAX) {
 						for (int j = 0; j < sc.numLights; ++j) {   // the reference's linear scan, kernel.cu:470-481, op for op
@@ -682,22 +689,26 @@ __global__ void __launch_bounds__(256, CUPT_SHADE_MIN_BLOCKS) k_shade(DevScene s
 						}
 						sel = lo;   // == numLights (fallback) when randArea >= cdf[last]
 					}
-					float u = rng.draw(draw++), v = rng.draw(draw++);
+					float u = ub, v = uc;
 					const float4 l0 = sc.lights[3 * sel], l1 = sc.lights[3 * sel + 1], l2 = sc.lights[3 * sel + 2];
 					if (radd(u, v) > 1.0f) {                                          // kernel.cu:491-495
 						u = (float)((double)u + 2 * (0.5 - (double)u));
 						v = (float)((double)v + 2 * (0.5 - (double)v));
 					}
 					const f3 pos1 = radd3(radd3(mk3(l0.x, l0.y, l0.z), rmul3(mk3(l1.x, l1.y, l1.z), u)), rmul3(mk3(l2.x, l2.y, l2.z), v));
-					const f3 dd = rsub3(pos1, pos);
-					lDir = rnormalized(dd);
+					vdir = rsub3(pos1, pos);
+					light = true;
+				}
+				const f3 lDir = rnormalized(vdir);
+				if (light) {
 					const float cosL = fmaxf(0.0f, rdot(lDir, normal));
 					const float cosO1 = fmaxf(0.0f, rdot(mk3(0.f, -1.f, 0.f), rmul3(lDir, -1.f)));   // hard-coded light normal, kernel.cu:503
-					const float G = rdiv(rmul(cosL, cosO1), rdot(dd, dd));
-					const float k = kBrdf * G * sc.totalLightArea;
-					wr *= m0.x * k; wg *= m0.y * k; wb *= m0.z * k;                  // kernel.cu:506
+					const float G = rdiv(rmul(cosL, cosO1), rdot(vdir, vdir));
+					k = kBrdf * G * sc.totalLightArea;                               // kernel.cu:506
 					iter = max(iter, pp.max_depth - 2);                              // kernel.cu:507
 				}
+				if (m1.w != 0.f && id >= 0) { wr *= m0.x; wg *= m0.y; wb *= m0.z; }   // (mirror: the albedo alone, not albedo * 1.0f: same value, but keep the operation the test's restatement has)
+				else { wr *= m0.x * k; wg *= m0.y * k; wb *= m0.z * k; }
 				++iter;
 				push = (wr != 0.f || wg != 0.f || wb != 0.f);
 				if (push) {
