@@ -172,7 +172,9 @@ struct ExtendTuning {
 	uint32_t qbias_bits;    // CUPT_QBIAS_BITS, passed as a parameter on purpose (see u8f_biased)
 };
 #define CUPT_LIGHT_SCAN_MAX 64   // up to this many lights k_shade repeats the reference's linear scan exactly
+#ifndef CUPT_QUEUE_CHUNK
 #define CUPT_QUEUE_CHUNK 64u
+#endif
 #ifndef CUPT_EXTEND_MIN_BLOCKS
 #define CUPT_EXTEND_MIN_BLOCKS 7
 #endif
