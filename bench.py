@@ -191,6 +191,7 @@ def main():
     ap.add_argument("--config", type=int, default=2, choices=[2, 3], help="BASELINE.json config: 2 (default: 1024^2, 64 spp per GPU, weak scaling) or 3 (3840x2160, 1024 spp split over the GPUs, strong scaling)")
     ap.add_argument("--tri-test", default="refexact", choices=["refexact", "watertight"], help="refexact = the reference's triIntersect bit for bit (default); watertight = Woop et al. on exact vertices")
     ap.add_argument("--share-primary", action="store_true", help="trace the (sample-independent) pinhole primary ray once per pixel and pass; fewer rays are traced AND counted, so Mrays/s drops while Msamples/s rises")
+    ap.add_argument("--partition", default="samples", choices=["samples", "tiles"], help="multi-GPU split of a config 3 frame: sample ranges (default) or image tiles (8x4-pixel tiles, contiguous range per rank, every rank renders all samples of its tiles); both end in the same NCCL sum of the f32 accumulators")
     ap.add_argument("--bvh", default="host", choices=["host", "device"], help="host = binned-SAH builder (OpenMP), uploaded; device = cupt_build_bvh_device, rebuilt inside every e2e step")
     args = ap.parse_args()
     global W, H, SPP, WORKLOAD
@@ -241,7 +242,13 @@ def main():
     accum_t = torch.zeros(W * H * 3, dtype=torch.float32, device="cuda")
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
     from cudapathtracer_b200 import sharding
-    if args.config == 3:   # strong scaling: the frame's samples are split over the ranks
+    if args.partition == "tiles" and args.config != 3:
+        raise SystemExit("--partition tiles splits ONE frame over the ranks: use it with --config 3 (strong scaling)")
+    if args.config == 3 and args.partition == "tiles":   # strong scaling by image tiles: disjoint pixels, all samples each
+        first, spp_rank = 0, SPP
+        ctx.set_tile_window(*sharding.tile_range(rank, world, ctx.tile_count()))
+        samples_step = W * H * SPP
+    elif args.config == 3:   # strong scaling: the frame's samples are split over the ranks
         first, spp_rank = sharding.sample_range(rank, world, SPP)
         samples_step = W * H * SPP
     else:
@@ -344,7 +351,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong" if args.config == 3 else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "traversal": args.traversal, "integrator": args.integrator, "tri_test": args.tri_test, "share_primary_hits": bool(args.share_primary), "parallelism": f"sample ranges x{world}, replicated BVH, NCCL reduce of f32 accumulators",
+            "config": {"workload": WORKLOAD, "traversal": args.traversal, "integrator": args.integrator, "tri_test": args.tri_test, "share_primary_hits": bool(args.share_primary), "parallelism": f"{'image tiles' if args.partition == 'tiles' else 'sample ranges'} x{world}, replicated BVH, NCCL reduce of f32 accumulators",
                        "l2": "L2 flushed (256 MiB write) between timed steps; per-step path state (64 Mi paths x 72 B = 4.8 GB) exceeds the 126 MB L2, the 16 MB BVH is L2-resident within a step by design",
                        "bvh": {"builder": args.bvh, "nodes": info["num_nodes"], "prims": info["num_tri_records"], "depth": info["depth"], "build_s_host": build_s,
                                "build_ms_device": None if dev_info is None else {k: v for k, v in dev_info.items() if k.startswith("ms_")}}},

@@ -356,6 +356,16 @@ class Context:
     def sync(self):
         _check(self.lib.cupt_sync(self.h))
 
+    def set_tile_window(self, first_tile: int = 0, num_tiles: int = 0):
+        """render only tiles [first_tile, first_tile + num_tiles) of 8x4 pixels, row-major (0 tiles = whole image): the
+        image-tile partition of the multi-GPU path (sharding.tile_range)"""
+        _check(self.lib.cupt_set_tile_window(self.h, int(first_tile), int(num_tiles)))
+
+    def tile_count(self) -> int:
+        n = C.c_int(0)
+        _check(self.lib.cupt_tile_count(self.h, C.byref(n)))
+        return n.value
+
     def reset_accum(self):
         _check(self.lib.cupt_reset_accum(self.h))
 

@@ -54,6 +54,7 @@ struct cupt_context {
 	BuildArena arena; uint32_t* d_build_rank = nullptr; uint8_t* d_rgb8 = nullptr;
 	float4* d_prims_wt = nullptr; bool wt_valid = false;   // CUPT_TRI_WATERTIGHT: vertex records, same order as d_prims
 	float build_ms[4] = {0, 0, 0, 0}; int build_rounds = 0;   // last cupt_build_bvh_device: total, sort, PLOC, collapse
+	int tile_first = 0, tile_count = 0;   // cupt_set_tile_window (count 0 = the whole image)
 	// pinned staging for host -> device uploads (stage_alloc / upload)
 	uint8_t* h_stage = nullptr; size_t stage_cap = 0, stage_used = 0; cudaEvent_t stage_ev = nullptr; bool stage_pending = false;
 	bool pageable_upload = false;   // an upload of this call bypassed the staging buffer
@@ -221,7 +222,8 @@ void drain_events(cupt_context* c)
 	c->pending.clear();
 }
 
-PassParams make_pass(const cupt_context* c, int first_sample, int samples, int fixed_lens)
+// window: restrict the pass to the context's tile window (render passes); the parity hooks always cover the whole image
+PassParams make_pass(const cupt_context* c, int first_sample, int samples, int fixed_lens, bool window = false)
 {
 	PassParams pp;
 	pp.cam = c->cam;
@@ -230,7 +232,14 @@ PassParams make_pass(const cupt_context* c, int first_sample, int samples, int f
 	pp.samples = samples;
 	pp.tiles_x = (c->cam.pxlWidth + 7) / 8;
 	pp.tiles_y = (c->cam.pxlHeight + 3) / 4;
-	pp.p_pad = pp.tiles_x * pp.tiles_y * 32;
+	const int all_tiles = pp.tiles_x * pp.tiles_y;
+	pp.tile0 = 0;
+	int ntiles = all_tiles;
+	if (window && c->tile_count > 0) {
+		pp.tile0 = std::min(c->tile_first, all_tiles);
+		ntiles = std::max(0, std::min(c->tile_count, all_tiles - pp.tile0));
+	}
+	pp.p_pad = std::max(1, ntiles) * 32;   // (an empty window is rejected by cupt_render)
 	pp.max_depth = c->opts.max_depth;
 	pp.fixed_lens = fixed_lens;
 	pp.inv_p_pad = ~0ull / (uint64_t)pp.p_pad + 1ull;                      // p_pad >= 32
@@ -630,7 +639,8 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 	CK(cudaSetDevice(c->device));
 	if ((rc = ensure_accum(c))) return rc;
 	const DevScene sc = make_scene(c);
-	PassParams probe = make_pass(c, 0, 1, 0);
+	PassParams probe = make_pass(c, 0, 1, 0, true);
+	if (c->tile_count > 0 && c->tile_first >= probe.tiles_x * probe.tiles_y) return set_error(CUPT_ERR_INVALID, "tile window starts beyond the image (%d tiles)", probe.tiles_x * probe.tiles_y);
 	const bool bdpt = c->opts.integrator == CUPT_INTEGRATOR_BDPT;
 	if (bdpt && c->num_spheres > 0) return set_error(CUPT_ERR_INVALID, "the BDPT integrator (kernel.cu:217-415) has no sphere support");
 	int S = c->opts.samples_per_pass;
@@ -644,7 +654,7 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 	const int grid = c->num_sms * 8;
 	for (int done = 0; done < num_samples; done += S) {
 		const int s_now = std::min(S, num_samples - done);
-		const PassParams pp = make_pass(c, first_sample + done, s_now, 0);
+		const PassParams pp = make_pass(c, first_sample + done, s_now, 0, true);
 		CK(cudaMemsetAsync(c->pb.counters, 0, 128 * sizeof(uint32_t), c->stream));
 		StageEvent ev;
 		if (bdpt) {
@@ -700,6 +710,25 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 		CK(cudaGetLastError());
 		c->samples_accumulated += (uint64_t)s_now;
 	}
+	return CUPT_OK;
+}
+
+// Image-tile partition (the alternative to sample ranges): cupt_render then traces only the pixels of tiles
+// [first_tile, first_tile + num_tiles) — tiles of 8x4 pixels, numbered row-major, the order raygen lays warps out in —
+// and leaves the rest of the accumulator untouched, so that the ranks' images are disjoint and their sum (or a gather)
+// is the frame.  num_tiles <= 0 restores the whole image.
+int cupt_set_tile_window(cupt_context* c, int first_tile, int num_tiles)
+{
+	if (!c || first_tile < 0) return set_error(CUPT_ERR_INVALID, "bad tile window");
+	c->tile_first = num_tiles > 0 ? first_tile : 0;
+	c->tile_count = num_tiles > 0 ? num_tiles : 0;
+	return CUPT_OK;
+}
+
+int cupt_tile_count(const cupt_context* c, int* num_tiles)
+{
+	if (!c || !num_tiles || !c->have_cam) return set_error(CUPT_ERR_INVALID, "no camera set");
+	*num_tiles = ((c->cam.pxlWidth + 7) / 8) * ((c->cam.pxlHeight + 3) / 4);
 	return CUPT_OK;
 }
 

@@ -42,7 +42,8 @@ struct PassParams {
 	int32_t first_sample;      // global index of s_local = 0
 	int32_t samples;           // S
 	int32_t tiles_x, tiles_y;
-	int32_t p_pad;             // tiles_x * tiles_y * 32
+	int32_t tile0;             // first tile of the window this pass renders (cupt_set_tile_window; 0 = from the image's first tile)
+	int32_t p_pad;             // tiles in the window * 32
 	int32_t max_depth;         // NUM_BOUNCES made run-time
 	int32_t fixed_lens;        // 1: lens draws fixed at (0.5, 0.5) (primary-hit hook)
 	uint64_t inv_p_pad, inv_tiles_x;   // 2^64 / d + 1: n / d == umul64hi(inv, n) for every 32-bit n and d > 1 (Lemire & Kaser 2019)
@@ -64,7 +65,7 @@ __device__ __forceinline__ void slot_to_pixel(const PassParams& pp, uint32_t slo
 	// two integer divisions by run-time constants: a multiply-high each instead of ~20 instructions (4 % of k_shade)
 	s_local = (int)__umul64hi(pp.inv_p_pad, (uint64_t)slot);
 	const uint32_t r = slot - (uint32_t)s_local * (uint32_t)pp.p_pad;
-	const uint32_t tile = r >> 5, lane = r & 31u;
+	const uint32_t tile = (r >> 5) + (uint32_t)pp.tile0, lane = r & 31u;
 	const uint32_t ty = pp.tiles_x == 1 ? tile : (uint32_t)__umul64hi(pp.inv_tiles_x, (uint64_t)tile), tx = tile - ty * (uint32_t)pp.tiles_x;
 	x = (int)(tx * 8u + (lane & 7u));
 	y = (int)(ty * 4u + (lane >> 3));

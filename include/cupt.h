@@ -205,6 +205,11 @@ int cupt_set_render_opts(cupt_context* c, const cupt_render_opts* o);
  * pixel to the float sum accumulator.  Asynchronous on the context's stream. */
 int cupt_render(cupt_context* c, int first_sample, int num_samples);
 int cupt_sync(cupt_context* c);                                   /* cudaDeviceSynchronize, kernel.cu:716 */
+/* Multi-GPU by image tiles instead of sample ranges (the reference renders the whole image on device 0, kernel.cu:569,
+ * 709-736): cupt_render traces only the pixels of tiles [first_tile, first_tile + num_tiles) — 8x4-pixel tiles numbered
+ * row-major — and leaves the other pixels of the accumulator untouched.  num_tiles <= 0: the whole image again. */
+int cupt_set_tile_window(cupt_context* c, int first_tile, int num_tiles);
+int cupt_tile_count(const cupt_context* c, int* num_tiles);       /* tiles of the current camera's image */
 int cupt_reset_accum(cupt_context* c);                            /* setupImgBuffer, kernel.cu:520-526 */
 /* image readback, kernel.cu:760: row-major P*3 floats; normalise != 0 divides by the samples accumulated */
 int cupt_read_accum(cupt_context* c, float* rgb_host, int normalise);

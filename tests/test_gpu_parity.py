@@ -648,3 +648,40 @@ def test_large_scene_upload_and_soup_hits(ctx, lib):
         b2 = s2.build_bvh(); ctx.set_bvh(b2)
         assert hits_equal(ctx.trace_rays(r2), o2.brute_force(r2, None))
         b2.close(); s2.close()
+
+
+def test_tile_windows_compose(ctx, get_case):
+    """SURVEY §8e, the tile alternative to sample ranges: rendering the image as disjoint tile windows (8x4-pixel tiles,
+    split like sharding.tile_range does for 3 ranks) gives the whole-image render bit for bit — every pixel gets the
+    same Philox streams whichever window it is rendered in — and a window leaves the pixels outside it untouched;
+    both integrators"""
+    from cudapathtracer_b200 import sharding
+    c = get_case("cornell")
+    for integ in (api.INTEGRATOR_PT, api.INTEGRATOR_BDPT):
+        load(ctx, c, api.TRAVERSAL_WIDE, max_depth=5, seed=1234, integrator=integ)
+        ctx.set_tile_window(0, 0)
+        ctx.reset_accum(); ctx.render(0, 3)
+        whole = ctx.read_accum(False).copy()
+        n = ctx.tile_count()
+        w, h = int(c.cam["pxlWidth"][0]), int(c.cam["pxlHeight"][0])
+        assert n == ((w + 7) // 8) * ((h + 3) // 4)
+        ctx.reset_accum()
+        parts = []
+        for r in range(3):
+            first, cnt = sharding.tile_range(r, 3, n)
+            ctx.set_tile_window(first, cnt)
+            ctx.render(0, 3)
+            parts.append(ctx.read_accum(False).copy())
+        assert parts[-1].tobytes() == whole.tobytes()                             # the windows accumulate into one image
+        first, cnt = sharding.tile_range(0, 3, n)
+        touched = (parts[0].reshape(h, w, 3) != 0).any(axis=2)
+        ty, tx = np.divmod(np.arange(first, first + cnt), (w + 7) // 8)
+        inside = np.zeros((h, w), bool)
+        for y0, x0 in zip(ty * 4, tx * 8):
+            inside[y0:y0 + 4, x0:x0 + 8] = True
+        assert not touched[~inside].any() and touched[inside].mean() > 0.5        # nothing outside window 0 after the first part
+        ctx.set_tile_window(n + 5, 4)
+        with pytest.raises(Exception):
+            ctx.render(0, 1)
+        ctx.set_tile_window(0, 0)
+    ctx.set_options(integrator=api.INTEGRATOR_PT)
