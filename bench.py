@@ -304,7 +304,8 @@ def main():
     value = rays_all / (ms_total * 1e-3) / 1e6
 
     # e2e through the C-ABI with host buffers (scene + BVH H2D, render, image D2H), same step
-    host_img = np.empty((W * H, 3), dtype=np.float32)
+    host_t = torch.empty((W * H, 3), dtype=torch.float32, pin_memory=True)   # the caller's image buffer: pinned, so the read-back is one DMA
+    host_img = host_t.numpy()
     nv, nt, nm, nl, _ = s.counts()
     h2d = nv * 12 + nt * 28 + nt * 16 + nm * 32 + (nl + 1) * 48 + 32
     if args.bvh == "host":
@@ -326,7 +327,7 @@ def main():
             ctx.copy_accum_device(accum_t.data_ptr())
             dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
-                host_img[:] = accum_t.view(-1, 3).cpu().numpy()
+                host_t.copy_(accum_t.view(-1, 3))
         else:
             ctx.read_accum(False, out=host_img)
 
