@@ -48,13 +48,14 @@ __device__ __forceinline__ uint32_t f2ord(const float f) { const uint32_t u = __
 __host__ __device__ __forceinline__ float ord2f(const uint32_t o) { const uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o; float f; memcpy(&f, &u, 4); return f; }
 
 // ---- 1. primitive boxes ---------------------------------------------------------------------------------------
+// Grid-stride over the primitives with the centroid bounds kept in registers: one atomic pair per BLOCK and axis at the end
+// (one pair per warp — 5.6 M atomics on six addresses for 30 M primitives — made this kernel 4.7 ms where its 3 GB of
+// traffic need 0.5 ms).
 __global__ void __launch_bounds__(kTile) k_leaf_boxes(const float* __restrict__ verts, const cupt_triangle* __restrict__ tris, const int64_t nt,
                                                       const float4* __restrict__ spheres, const int64_t N, N2* __restrict__ leaf, uint32_t* __restrict__ cbounds)
 {
-	const int64_t i = (int64_t)blockIdx.x * kTile + threadIdx.x;
-	float c[3] = {0.f, 0.f, 0.f};
-	const bool valid = i < N;
-	if (valid) {
+	uint32_t mn[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, mx[3] = {0u, 0u, 0u};
+	for (int64_t i = (int64_t)blockIdx.x * kTile + threadIdx.x; i < N; i += (int64_t)gridDim.x * kTile) {
 		float lo[3], hi[3];
 		if (i < nt) {
 			const cupt_triangle t = tris[i];
@@ -69,7 +70,9 @@ __global__ void __launch_bounds__(kTile) k_leaf_boxes(const float* __restrict__ 
 		}
 		N2 n;
 		for (int a = 0; a < 3; ++a) {
-			c[a] = __fadd_rn(__fmul_rn(0.5f, lo[a]), __fmul_rn(0.5f, hi[a]));
+			const float c = __fadd_rn(__fmul_rn(0.5f, lo[a]), __fmul_rn(0.5f, hi[a]));
+			const uint32_t co = f2ord(c);
+			mn[a] = min(mn[a], co); mx[a] = max(mx[a], co);
 			const float m = fmaxf(fmaxf(fabsf(lo[a]), fabsf(hi[a])), 1e-30f);
 			const float pad = __fmul_rn(m, 4.8e-7f);   // 4 ulp, as bvh8_build.cpp: the reference's triangle test is plain f32
 			n.lo[a] = __fsub_rn(lo[a], pad); n.hi[a] = __fadd_rn(hi[a], pad);
@@ -77,11 +80,17 @@ __global__ void __launch_bounds__(kTile) k_leaf_boxes(const float* __restrict__ 
 		n.left = -1 - (int32_t)i; n.right = -1;
 		leaf[i] = n;
 	}
-	// centroid bounds: warp reduce, one atomic pair per warp and axis
+	// centroid bounds: warp reduce, block reduce through shared memory, one atomic pair per block and axis
+	__shared__ uint32_t s_mn[3][kTile / 32], s_mx[3][kTile / 32];
 	for (int a = 0; a < 3; ++a) {
-		uint32_t mn = valid ? f2ord(c[a]) : 0xffffffffu, mx = valid ? f2ord(c[a]) : 0u;
-		mn = __reduce_min_sync(0xffffffffu, mn); mx = __reduce_max_sync(0xffffffffu, mx);
-		if ((threadIdx.x & 31) == 0) { atomicMin(&cbounds[a], mn); atomicMax(&cbounds[3 + a], mx); }
+		const uint32_t wn = __reduce_min_sync(0xffffffffu, mn[a]), wx = __reduce_max_sync(0xffffffffu, mx[a]);
+		if ((threadIdx.x & 31) == 0) { s_mn[a][threadIdx.x >> 5] = wn; s_mx[a][threadIdx.x >> 5] = wx; }
+	}
+	__syncthreads();
+	if (threadIdx.x < 3) {
+		uint32_t bn = 0xffffffffu, bx = 0u;
+		for (int w = 0; w < kTile / 32; ++w) { bn = min(bn, s_mn[threadIdx.x][w]); bx = max(bx, s_mx[threadIdx.x][w]); }
+		atomicMin(&cbounds[threadIdx.x], bn); atomicMax(&cbounds[3 + threadIdx.x], bx);
 	}
 }
 
@@ -404,9 +413,21 @@ struct EmitArgs {
 	const uint64_t* item_counts; const uint64_t* tile_offs;
 	uint32_t level_base, next_base, prim_base;
 	int32_t* next_items; Node8* out_nodes; float4* out_prims;
+	int32_t* rec_prim;   // primitive of every record, in record order (k_emit_prims)
 	const float* verts; const cupt_triangle* tris; const float4* spheres; const uint32_t* rank; int64_t nt;
 	double inv_root_area; double* sah;
 };
+
+// The 48-byte records, one thread per record: gathers of the triangle and its vertices, consecutive stores.  (Written from
+// k_collapse_emit — one thread per WIDE NODE, up to 24 records in a row behind dependent gathers — this was most of that
+// kernel's 9 ms per 30 M primitives.)
+__global__ void __launch_bounds__(kTile) k_emit_prims(const int32_t* __restrict__ rec_prim, const int64_t N, const int64_t nt, const float* __restrict__ verts,
+                                                      const cupt_triangle* __restrict__ tris, const float4* __restrict__ spheres, const uint32_t* __restrict__ rank,
+                                                      float4* __restrict__ out_prims)
+{
+	const int64_t r = (int64_t)blockIdx.x * kTile + threadIdx.x;
+	if (r < N) write_prim(rec_prim[r], nt, verts, tris, spheres, rank, out_prims + 3 * (size_t)r);
+}
 
 __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 {
@@ -450,17 +471,23 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 	// quantisation grid: power-of-two cell per axis, at least 2^-24 of the coordinate magnitude
 	Node8 nd;
 	memset(&nd, 0, sizeof(nd));
-	double scale[3];
+	double scale[3], inv_scale[3];
 	for (int a = 0; a < 3; ++a) {
 		nd.p[a] = blo[a];
 		const double ext = (double)bhi[a] - (double)blo[a];
 		int e = -126;
-		if (ext > 0) { e = (int)ceil(log2(ext / 255.0)); while (ldexp(255.0, e) < ext) ++e; }
+		if (ext > 0) {
+			// smallest e with 255 * 2^e >= ext, from the exponent field (a double log2 per axis and node was a third of this
+			// kernel): 2^k <= ext < 2^(k+1) gives 255 * 2^(k-8) < ext, so start there; at most two steps
+			e = ((__double2hiint(ext) >> 20) & 0x7ff) - 1023 - 8;
+			while (ldexp(255.0, e) < ext) ++e;
+		}
 		const float m = fmaxf(fabsf(blo[a]), fabsf(bhi[a]));
 		e = max(e, dev_float_exponent(m) - 24);
 		e = max(-126, min(127, e));
 		nd.e[a] = (uint8_t)(e + 127);
 		scale[a] = ldexp(1.0, e);
+		inv_scale[a] = ldexp(1.0, -e);   // exact: the divisions below become multiplications with the same result
 	}
 	const uint32_t child_off = (uint32_t)ex, prim_off = (uint32_t)(ex >> 32);
 	nd.child_base = A.next_base + child_off;
@@ -473,8 +500,8 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 		const int32_t c = k.id[q];
 		for (int a = 0; a < 3; ++a) {
 			const double p = nd.p[a];
-			double ql = floor(((double)clo[q][a] - p) / scale[a]);
-			double qh = ceil(((double)chi[q][a] - p) / scale[a]);
+			double ql = floor(((double)clo[q][a] - p) * inv_scale[a]);
+			double qh = ceil(((double)chi[q][a] - p) * inv_scale[a]);
 			while (ql > 0 && p + ql * scale[a] > (double)clo[q][a]) ql -= 1;
 			while (p + qh * scale[a] < (double)chi[q][a]) qh += 1;
 			ql = fmax(0.0, fmin(255.0, ql));
@@ -497,7 +524,7 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 				const int32_t x = stack[--sp];
 				const int32_t l = A.nodes[x].left;
 				if (l < 0) {
-					write_prim(-1 - l, A.nt, A.verts, A.tris, A.spheres, A.rank, A.out_prims + 3 * (size_t)(nd.tri_base + triOfs + w));
+					A.rec_prim[nd.tri_base + triOfs + w] = -1 - l;   // the record itself is written by k_emit_prims
 					++w;
 				} else {
 					stack[sp++] = A.nodes[x].right; stack[sp++] = l;
@@ -596,7 +623,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	static const uint32_t cb_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
 	CKB(cudaEventRecord(ev[0], st));
 	CKB(cudaMemcpyAsync(cbounds, cb_init, sizeof(cb_init), cudaMemcpyHostToDevice, st));
-	k_leaf_boxes<<<tilesN, kTile, 0, st>>>(verts, tris, nt, spheres, N, leaf, cbounds);
+	k_leaf_boxes<<<std::min(tilesN, 148 * 16), kTile, 0, st>>>(verts, tris, nt, spheres, N, leaf, cbounds);
 	k_morton<<<tilesN, kTile, 0, st>>>(leaf, N, cbounds, keys[0], vals[0]);
 	const int sorted = rsort::sort_pairs(st, keys, vals, (uint32_t)N, sort_passes, reinterpret_cast<uint32_t*>(temp));
 	CKB(cudaEventRecord(ev[1], st));
@@ -679,6 +706,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 		A.item_counts = item_counts; A.tile_offs = tile_sums;
 		A.level_base = level_base; A.next_base = level_base + (uint32_t)n_items; A.prim_base = prim_base;
 		A.next_items = items[lvl ^ 1]; A.out_nodes = static_cast<Node8*>(out->nodes); A.out_prims = static_cast<float4*>(out->prims);
+		A.rec_prim = reinterpret_cast<int32_t*>(nn);   // (the PLOC neighbour array is free by now)
 		A.verts = verts; A.tris = tris; A.spheres = spheres; A.rank = rank; A.nt = nt;
 		A.inv_root_area = 1.0 / root_area; A.sah = d_sah;
 		k_collapse_emit<<<tiles, kTile, 0, st>>>(A);
@@ -690,6 +718,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 		lvl ^= 1;
 		if (depth > 255) return set_error(CUPT_ERR_LIMIT, "wide BVH deeper than 255 levels");
 	}
+	k_emit_prims<<<tilesN, kTile, 0, st>>>(reinterpret_cast<const int32_t*>(nn), N, nt, verts, tris, spheres, rank, static_cast<float4*>(out->prims));
 	CKB(cudaEventRecord(ev[3], st));
 	double sah = 0;
 	CKB(cudaMemcpyAsync(&sah, d_sah, sizeof(double), cudaMemcpyDeviceToHost, st));

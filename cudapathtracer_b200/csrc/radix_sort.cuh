@@ -7,7 +7,9 @@
 //   k_radix_scatter  one block per tile, each warp owns 512 consecutive pairs: __match_any_sync ranks equal digits
 //                    inside a round of 32, a warp-private counter array carries the rank across the 16 rounds, a
 //                    prefix over the 8 warps per digit gives the place inside the tile's run.  Order inside a run is
-//                    (warp, round, lane) = memory order, so the sort is stable.
+//                    (warp, round, lane) = memory order, so the sort is stable.  The tile is put in sorted order in
+//                    shared memory first and written out from there, so that a warp's stores are consecutive
+//                    addresses inside the digits' runs.
 //
 // Only the top `bits` bits of the 63-bit code are sorted (the caller asks for log2(N) + 9 rounded up to a multiple of
 // 8): finer Morton cells than 512 per primitive cannot change a clustering window of +-4.
@@ -114,11 +116,20 @@ __global__ void __launch_bounds__(kThreads) k_scan32_apply(uint32_t* __restrict_
 	}
 }
 
+// Dynamic shared memory of k_radix_scatter: the tile's pairs in sorted order (keys, values), then per digit the offset that
+// turns a position inside the sorted tile into a global position.
+constexpr size_t kScatterSmem = (size_t)kTileN * (sizeof(uint64_t) + sizeof(uint32_t)) + 256 * sizeof(uint32_t);
+
 __global__ void __launch_bounds__(kThreads) k_radix_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                             uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, const uint32_t n,
                                                             const int shift, const uint32_t* __restrict__ offs, const uint32_t ntiles)
 {
-	__shared__ uint32_t s_cnt[kWarps][256];   // per warp: pairs seen so far per digit; later: the warp's start inside the tile's run
+	extern __shared__ uint64_t s_dyn[];
+	uint64_t* s_key = s_dyn;                                                   // [kTileN] the tile in sorted order
+	uint32_t* s_val = reinterpret_cast<uint32_t*>(s_dyn + kTileN);             // [kTileN]
+	uint32_t* s_gofs = s_val + kTileN;                                         // [256] global start of the digit's run - its start inside the sorted tile
+	__shared__ uint32_t s_cnt[kWarps][256];   // per warp: pairs seen so far per digit; later: the warp's start inside the sorted tile
+	__shared__ uint32_t s_w[kWarps + 1];
 	const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
 	const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
@@ -142,21 +153,40 @@ __global__ void __launch_bounds__(kThreads) k_radix_scatter(const uint64_t* __re
 		__syncwarp();
 	}
 	__syncthreads();
-	{   // thread t = digit t: exclusive prefix of the warps' counts, plus the global start of this tile's run of that digit
-		uint32_t run = offs[(size_t)threadIdx.x * ntiles + blockIdx.x];
+	{   // thread t = digit t: the digit's start inside the sorted tile (exclusive scan of the tile's digit counts), the warps'
+		// starts behind it, and the offset to the global run of this (digit, tile)
+		uint32_t c[kWarps], tot = 0u;
 #pragma unroll
-		for (int i = 0; i < kWarps; ++i) { const uint32_t c = s_cnt[i][threadIdx.x]; s_cnt[i][threadIdx.x] = run; run += c; }
+		for (int i = 0; i < kWarps; ++i) { c[i] = s_cnt[i][threadIdx.x]; tot += c[i]; }
+		uint32_t all;
+		uint32_t run = block_excl32(tot, s_w, &all);
+		s_gofs[threadIdx.x] = offs[(size_t)threadIdx.x * ntiles + blockIdx.x] - run;
+#pragma unroll
+		for (int i = 0; i < kWarps; ++i) { s_cnt[i][threadIdx.x] = run; run += c[i]; }
 	}
 	__syncthreads();
+	// the tile in sorted order in shared memory: order inside a digit is (warp, round, lane) = memory order, so the sort is stable
 #pragma unroll
 	for (int i = 0; i < kItems; ++i) {
 		const uint32_t idx = wbase + (uint32_t)i * 32u + lane;
 		if (idx < n) {
 			const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
 			const uint32_t pos = s_cnt[w][d] + rank[i];
-			keys_out[pos] = key[i];
-			vals_out[pos] = vals_in[idx];
+			s_key[pos] = key[i];
+			s_val[pos] = vals_in[idx];
 		}
+	}
+	__syncthreads();
+	// ... and out to global memory in that order: consecutive threads write consecutive addresses inside every digit's run
+	// (the first version scattered straight from registers, 32 different runs per warp store: 6.9 ms per pass for 100 M
+	// pairs, 350 GB/s)
+	const uint32_t tile_n = min((uint32_t)kTileN, n - blockIdx.x * (uint32_t)kTileN);
+#pragma unroll 4
+	for (uint32_t j = threadIdx.x; j < tile_n; j += kThreads) {
+		const uint64_t k = s_key[j];
+		const uint32_t pos = s_gofs[(uint32_t)(k >> shift) & 255u] + j;
+		keys_out[pos] = k;
+		vals_out[pos] = s_val[j];
 	}
 }
 
@@ -177,6 +207,8 @@ inline int sort_pairs(cudaStream_t st, uint64_t* keys[2], uint32_t* vals[2], con
 	const uint32_t stiles = (hist_n + kScanTile - 1) / kScanTile;
 	uint32_t* hist = scratch;
 	uint32_t* tile_sums = scratch + hist_n;
+	static bool attr_set = false;   // 50 KB of dynamic shared memory: above the 48 KB default
+	if (!attr_set) { cudaFuncSetAttribute(k_radix_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem); attr_set = true; }
 	int cur = 0;
 	for (int p = 0; p < passes; ++p) {
 		const int shift = 63 - 8 * (passes - p);
@@ -184,7 +216,7 @@ inline int sort_pairs(cudaStream_t st, uint64_t* keys[2], uint32_t* vals[2], con
 		k_scan32_reduce<<<stiles, kThreads, 0, st>>>(hist, hist_n, tile_sums);
 		k_scan32_tiles<<<1, kThreads, 0, st>>>(tile_sums, stiles);
 		k_scan32_apply<<<stiles, kThreads, 0, st>>>(hist, hist_n, tile_sums);
-		k_radix_scatter<<<ntiles, kThreads, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift < 0 ? 0 : shift, hist, ntiles);
+		k_radix_scatter<<<ntiles, kThreads, kScatterSmem, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift < 0 ? 0 : shift, hist, ntiles);
 		cur ^= 1;
 	}
 	return cur;
