@@ -181,22 +181,22 @@ __global__ void __launch_bounds__(kTile) k_scan_tiles(uint64_t* __restrict__ til
 // Nearest neighbour of cluster i among positions i-R..i+R by the half-area of the union box.  Ties are broken by a
 // strict total order on UNORDERED pairs — (area, |i-j|, min(i,j) odd, min(i,j)) — so the globally smallest pair is
 // always mutual (progress every round) and a run of identical boxes pairs up as (0,1)(2,3)... instead of chaining.
-template <int kRadius>
-__global__ void __launch_bounds__(kTile) k_ploc_nearest(const N2* __restrict__ nodes, const uint32_t* __restrict__ cid, const int n, uint32_t* __restrict__ nn)
+// TAIL = called from k_ploc_tail, which reads what it wrote itself a round earlier: plain loads instead of ld.global.nc
+template <int kRadius, bool TAIL>
+__device__ __forceinline__ void ploc_nearest_block(const N2* nodes, const uint32_t* cid, const int n, uint32_t* nn, const int block, float (*s_box)[kTile + 2 * kRadius])
 {
-	__shared__ float s_box[6][kTile + 2 * kRadius];
-	const int base = (int)blockIdx.x * kTile - kRadius;
+	const int base = block * kTile - kRadius;
 	for (int k = threadIdx.x; k < kTile + 2 * kRadius; k += kTile) {
 		const int g = base + k;
 		if (g >= 0 && g < n) {
 			const float4* p = reinterpret_cast<const float4*>(&nodes[cid[g]]);
-			const float4 a = __ldg(p), b = __ldg(p + 1);
+			const float4 a = TAIL ? p[0] : __ldg(p), b = TAIL ? p[1] : __ldg(p + 1);
 			s_box[0][k] = a.x; s_box[1][k] = a.y; s_box[2][k] = a.z;
 			s_box[3][k] = b.x; s_box[4][k] = b.y; s_box[5][k] = b.z;
 		}
 	}
 	__syncthreads();
-	const int i = (int)blockIdx.x * kTile + threadIdx.x;
+	const int i = block * kTile + threadIdx.x;
 	if (i >= n) return;
 	const int li = threadIdx.x + kRadius;
 	const float lx = s_box[0][li], ly = s_box[1][li], lz = s_box[2][li], hx = s_box[3][li], hy = s_box[4][li], hz = s_box[5][li];
@@ -220,8 +220,15 @@ __global__ void __launch_bounds__(kTile) k_ploc_nearest(const N2* __restrict__ n
 	nn[i] = (uint32_t)bj;
 }
 
+template <int kRadius>
+__global__ void __launch_bounds__(kTile) k_ploc_nearest(const N2* __restrict__ nodes, const uint32_t* __restrict__ cid, const int n, uint32_t* __restrict__ nn)
+{
+	__shared__ float s_box[6][kTile + 2 * kRadius];
+	ploc_nearest_block<kRadius, false>(nodes, cid, n, nn, (int)blockIdx.x, s_box);
+}
+
 // valid = the slot survives the round (everything but the higher half of a mutual pair); leader = lower half
-__device__ __forceinline__ uint64_t ploc_flags(const uint32_t* __restrict__ nn, const int i, const int n, int* partner)
+__device__ __forceinline__ uint64_t ploc_flags(const uint32_t* nn, const int i, const int n, int* partner)
 {
 	if (i >= n) { *partner = -1; return 0ull; }
 	const int j = (int)nn[i];
@@ -249,7 +256,7 @@ __global__ void __launch_bounds__(kTile) k_ploc_count(const uint32_t* __restrict
 struct alignas(16) Dp { float c[7]; uint32_t splits; };
 constexpr float kCostNode = 1.0f, kCostPrim = 0.3f;
 
-__device__ __forceinline__ void dp_of(const Dp* __restrict__ dp, const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt,
+__device__ __forceinline__ void dp_of(const Dp* dp, const N2* nodes, const uint32_t* cnt,
                                       const uint32_t id, const uint32_t max_leaf, float c[8])
 {
 	const uint32_t n = cnt[id];
@@ -266,16 +273,18 @@ __device__ __forceinline__ void dp_of(const Dp* __restrict__ dp, const N2* __res
 	}
 }
 
-__global__ void __launch_bounds__(kTile) k_ploc_merge(N2* __restrict__ nodes, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ cid_in,
-                                                      uint32_t* __restrict__ cid_out, const uint32_t* __restrict__ nn, const int n,
-                                                      const uint64_t* __restrict__ tile_offs, const uint32_t node_base, Dp* __restrict__ dp, const uint32_t max_leaf)
+// one tile of a PLOC round: order-preserving compaction of the surviving clusters, creation of the merged nodes and their
+// collapse costs.  *tile_total = (survivors, leaders << 32) of this tile.
+__device__ __forceinline__ void ploc_merge_block(N2* nodes, uint32_t* cnt, const uint32_t* cid_in, uint32_t* cid_out, const uint32_t* nn, const int n,
+                                                 const uint64_t tile_off, const uint32_t node_base, Dp* dp, const uint32_t max_leaf, const int block,
+                                                 uint64_t* s_warp, uint64_t* tile_total)
 {
-	__shared__ uint64_t s_warp[kTile / 32 + 1];
-	const int i = (int)blockIdx.x * kTile + threadIdx.x;
+	const int i = block * kTile + threadIdx.x;
 	int partner;
 	const uint64_t f = ploc_flags(nn, i, n, &partner);
 	uint64_t tot;
-	const uint64_t pos = tile_offs[blockIdx.x] + block_scan_excl(f, s_warp, &tot);
+	const uint64_t pos = tile_off + block_scan_excl(f, s_warp, &tot);
+	*tile_total = tot;
 	if (!(f & 1ull)) return;
 	const uint32_t out = (uint32_t)pos;
 	if (f >> 32) {
@@ -320,6 +329,39 @@ __global__ void __launch_bounds__(kTile) k_ploc_merge(N2* __restrict__ nodes, ui
 	} else {
 		cid_out[out] = cid_in[i];
 	}
+}
+
+__global__ void __launch_bounds__(kTile) k_ploc_merge(N2* __restrict__ nodes, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ cid_in,
+                                                      uint32_t* __restrict__ cid_out, const uint32_t* __restrict__ nn, const int n,
+                                                      const uint64_t* __restrict__ tile_offs, const uint32_t node_base, Dp* __restrict__ dp, const uint32_t max_leaf)
+{
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	uint64_t tot;
+	ploc_merge_block(nodes, cnt, cid_in, cid_out, nn, n, tile_offs[blockIdx.x], node_base, dp, max_leaf, (int)blockIdx.x, s_warp, &tot);
+}
+
+// The last rounds in ONE launch: once at most kTile clusters are left, a single block runs nearest / merge round after round
+// with block barriers in between (no launches, no host read-back): about log_1.5(256) = 14 of the ~30 rounds of a 262 k-triangle
+// build.  state[0] = node_base afterwards, state[1] = rounds run here, state[2] = which cid buffer holds the root.
+template <int kRadius>
+__global__ void __launch_bounds__(kTile) k_ploc_tail(N2* nodes, uint32_t* cnt, uint32_t* cid0, uint32_t* cid1, uint32_t* nn, int n, uint32_t node_base,
+                                                     Dp* dp, const uint32_t max_leaf, int cur, uint32_t* state)
+{
+	__shared__ float s_box[6][kTile + 2 * kRadius];
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	uint32_t rounds = 0u;
+	while (n > 1) {
+		uint32_t* cin = cur ? cid1 : cid0;
+		uint32_t* cout = cur ? cid0 : cid1;
+		ploc_nearest_block<kRadius, true>(nodes, cin, n, nn, 0, s_box);
+		__syncthreads();
+		uint64_t tot;
+		ploc_merge_block(nodes, cnt, cin, cout, nn, n, 0ull, node_base, dp, max_leaf, 0, s_warp, &tot);
+		__syncthreads();
+		n = (int)(uint32_t)tot; node_base += (uint32_t)(tot >> 32); cur ^= 1; ++rounds;
+		if ((tot >> 32) == 0ull) break;   // (no mutual pair: cannot happen, see k_ploc_nearest; the host checks n)
+	}
+	if (threadIdx.x == 0) { state[0] = node_base; state[1] = rounds; state[2] = (uint32_t)cur; state[3] = (uint32_t)n; }
 }
 
 // ---- 4. collapse to 8-wide + emission ----------------------------------------------------------------------------
@@ -550,7 +592,7 @@ using namespace devbuild;
 int BuildArena::reserve(size_t bytes)
 {
 	if (!h_total) {
-		if (cudaMallocHost((void**)&h_total, sizeof(uint64_t)) != cudaSuccess) return set_error(CUPT_ERR_CUDA, "cudaMallocHost failed");
+		if (cudaMallocHost((void**)&h_total, 2 * sizeof(uint64_t)) != cudaSuccess) return set_error(CUPT_ERR_CUDA, "cudaMallocHost failed");
 		for (auto& e : ev)
 			if (cudaEventCreate(&e) != cudaSuccess) return set_error(CUPT_ERR_CUDA, "cudaEventCreate failed");
 	}
@@ -642,7 +684,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	k_sorted_leaves<<<tilesN, kTile, 0, st>>>(leaf, vals[sorted], N, nodes, cnt, cid[0]);
 	int cn = (int)N, cur = 0, rounds = 0;
 	uint32_t node_base = (uint32_t)N;
-	while (cn > 1) {
+	while (cn > kTile) {
 		const int tiles = (cn + kTile - 1) / kTile;
 		switch (radius) {
 		case 32: k_ploc_nearest<32><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
@@ -661,6 +703,23 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 		if (leaders == 0 || (int)valid + (int)leaders != cn)
 			return set_error(CUPT_ERR_CUDA, "internal: PLOC round made no progress (n %d, valid %u, merged %u)", cn, valid, leaders);
 		cn = (int)valid; node_base += leaders; cur ^= 1; ++rounds;
+	}
+	if (cn > 1) {   // the remaining rounds in one launch (k_ploc_tail)
+		uint32_t* state = reinterpret_cast<uint32_t*>(tile_sums);
+		switch (radius) {
+		case 32: k_ploc_tail<32><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
+		case 16: k_ploc_tail<16><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
+		case 8: k_ploc_tail<8><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
+		case 2: k_ploc_tail<2><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
+		case 1: k_ploc_tail<1><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
+		default: k_ploc_tail<4><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
+		}
+		CKB(cudaMemcpyAsync(h_total, state, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		CKB(cudaStreamSynchronize(st));
+		const uint32_t* hs = reinterpret_cast<const uint32_t*>(h_total);
+		if (hs[3] != 1u || hs[0] != node_base + (uint32_t)cn - 1u)
+			return set_error(CUPT_ERR_CUDA, "internal: PLOC tail did not reach one root (n %d -> %u, nodes %u -> %u)", cn, hs[3], node_base, hs[0]);
+		node_base = hs[0]; rounds += (int)hs[1]; cur = (int)hs[2]; cn = 1;
 	}
 	CKB(cudaEventRecord(ev[2], st));
 	const int32_t root = N == 1 ? 0 : (int32_t)node_base - 1;
