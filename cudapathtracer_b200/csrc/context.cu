@@ -35,6 +35,7 @@ struct cupt_context {
 	float* d_verts = nullptr; cupt_triangle* d_tris = nullptr; float4* d_trishade = nullptr; float4* d_mats = nullptr;
 	float4* d_lights = nullptr; float* d_light_cdf = nullptr; float4* d_spheres = nullptr; int num_spheres = 0;
 	int64_t num_tris = 0; int num_lights = 0; float total_light_area = 0.f;
+	float emis_lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, emis_hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};   // bounds of the emissive primitives (cupt_set_scene)
 	// acceleration structures
 	uint4* d_nodes = nullptr; float4* d_prims = nullptr; int bvh_depth = 0; int64_t num_nodes = 0, num_prims = 0;
 	cupt_bvh2_node* d_bvh2 = nullptr; int bvh2_size = 0, bvh2_depth = 0;
@@ -244,6 +245,11 @@ PassParams make_pass(const cupt_context* c, int first_sample, int samples, int f
 	pp.fixed_lens = fixed_lens;
 	pp.inv_p_pad = ~0ull / (uint64_t)pp.p_pad + 1ull;                      // p_pad >= 32
 	pp.inv_tiles_x = pp.tiles_x > 1 ? ~0ull / (uint64_t)pp.tiles_x + 1ull : 0ull;
+	// last segments stop at the first hit in front of every emitter (k_shade): wide traversal only — the strict mode promises the
+	// reference's hit on EVERY ray — and not in stats runs, whose node / primitive counts describe full closest-hit searches
+	static const char* ts_env = getenv("CUPT_TERMINAL_STOP");
+	pp.term_stop = (c->opts.traversal == CUPT_TRAVERSAL_WIDE && c->opts.collect_stats == 0 && !(ts_env && atoi(ts_env) == 0)) ? 1 : 0;
+	for (int a = 0; a < 3; ++a) { pp.emis_lo[a] = c->emis_lo[a]; pp.emis_hi[a] = c->emis_hi[a]; }
 	return pp;
 }
 
@@ -451,11 +457,26 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 		const bool staged = ts != nullptr;
 		if (!staged) { tmp.resize(nt); ts = tmp.data(); }
 		const cupt_triangle* tr = s->tris.data();
-#pragma omp parallel for schedule(static) num_threads(copy_threads()) if (nt > 65536)
-		for (int64_t i = 0; i < (int64_t)nt; ++i) {
-			ts[i].n[0] = tr[i].norm.x; ts[i].n[1] = tr[i].norm.y; ts[i].n[2] = tr[i].norm.z;
-			ts[i].mat = tr[i].mat;
+		// the same pass bounds the emissive triangles (k_shade's early stop for last segments, DevScene::emis_lo / emis_hi)
+		float elo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, ehi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+#pragma omp parallel num_threads(copy_threads()) if (nt > 65536)
+		{
+			float tlo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, thi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+#pragma omp for schedule(static) nowait
+			for (int64_t i = 0; i < (int64_t)nt; ++i) {
+				ts[i].n[0] = tr[i].norm.x; ts[i].n[1] = tr[i].norm.y; ts[i].n[2] = tr[i].norm.z;
+				ts[i].mat = tr[i].mat;
+				if ((size_t)tr[i].mat < nm && s->mats[tr[i].mat].emission[0] != 0) {
+					for (const int32_t vi : {tr[i].v0, tr[i].v1, tr[i].v2}) {
+						const float pv[3] = {s->verts[vi].x, s->verts[vi].y, s->verts[vi].z};
+						for (int a = 0; a < 3; ++a) { tlo[a] = std::min(tlo[a], pv[a]); thi[a] = std::max(thi[a], pv[a]); }
+					}
+				}
+			}
+#pragma omp critical
+			for (int a = 0; a < 3; ++a) { elo[a] = std::min(elo[a], tlo[a]); ehi[a] = std::max(ehi[a], thi[a]); }
 		}
+		for (int a = 0; a < 3; ++a) { c->emis_lo[a] = elo[a]; c->emis_hi[a] = ehi[a]; }
 		if ((rc = staged ? upload_staged(c, &c->d_trishade, ts, nt * sizeof(TriShade)) : upload(c, &c->d_trishade, ts, nt * sizeof(TriShade)))) return rc;
 		if (!staged) CK(cudaStreamSynchronize(c->stream));
 	}
@@ -492,6 +513,11 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 		for (int k = 0; k < 3; ++k) { ss[i].diffuse[k] = (float)sp.diffuse[k]; ss[i].emm[k] = (float)sp.emm[k]; }
 		ss[i].emissive_flag = sp.emm[0] != 0 ? 1.f : 0.f;
 		ss[i].pad = 0.f;
+		if (sp.emm[0] != 0) {
+			const float cc[3] = {sp.pos.x, sp.pos.y, sp.pos.z};
+			const float rr = std::fabs(sp.rad) * 1.001f;
+			for (int a = 0; a < 3; ++a) { c->emis_lo[a] = std::min(c->emis_lo[a], cc[a] - rr); c->emis_hi[a] = std::max(c->emis_hi[a], cc[a] + rr); }
+		}
 	}
 	if ((rc = upload(c, &c->d_spheres, ss.data(), ss.size() * sizeof(SphereShade)))) return rc;
 	c->num_spheres = (int)ss.size();
@@ -697,7 +723,7 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 				k_broadcast_primary<<<grid, 256, 0, c->stream>>>(pp, c->pb);
 				stage_end(c, ev);
 				c->launches++;
-			} else if ((rc = launch_extend(c, sc, depth, depth & 1))) return rc;
+			} else if ((rc = launch_extend(c, sc, depth, depth & 1, depth > 0 && pp.term_stop))) return rc;
 			stage_begin(c, 2, ev);
 			k_shade<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb, depth, depth & 1);
 			stage_end(c, ev);

@@ -47,6 +47,10 @@ struct PassParams {
 	int32_t max_depth;         // NUM_BOUNCES made run-time
 	int32_t fixed_lens;        // 1: lens draws fixed at (0.5, 0.5) (primary-hit hook)
 	uint64_t inv_p_pad, inv_tiles_x;   // 2^64 / d + 1: n / d == umul64hi(inv, n) for every 32-bit n and d > 1 (Lemire & Kaser 2019)
+	// (kept out of DevScene: k_extend takes that struct by value, and its register allocation moved with the struct's size —
+	// 28 more bytes cost 1 ms of extend per frame)
+	int32_t term_stop;             // 1: rays of a path's LAST segment carry an early-stop distance (k_shade, k_extend<.., VIS>)
+	float emis_lo[3], emis_hi[3];  // bounds of every emissive primitive (empty box: lo > hi)
 };
 
 struct PathBuffers {
@@ -564,6 +568,22 @@ __global__ void __launch_bounds__(64) k_retrace_strict(DevScene sc, PathBuffers 
 	if (blockIdx.x == 0 && threadIdx.x == 0 && count) atomicAdd(&pb.stats[4], (unsigned long long)count);
 }
 
+// Early stop for the LAST segment of a path.  All the next k_shade does with such a ray's hit is add the emission of the
+// primitive it meets (kernel.cu:453-457), so a hit in front of every emitter ends the search: whatever is nearer is not an
+// emitter either.  Returns a distance d such that no emissive primitive is met before d along the ray: the entry distance
+// of the emitters' bounding box, shortened by 0.1 % + 0.001 against the rounding of the box test and of triIntersect
+// (<= 0: no early stop possible; CUPT_MAX_FLOAT: the scene has no emitter).  k_extend<.., VIS> stops once best < d.
+__device__ __forceinline__ float emitter_entry_distance(const PassParams& pp, const f3 o, const f3 d)
+{
+	if (pp.emis_lo[0] > pp.emis_hi[0]) return CUPT_MAX_FLOAT;
+	float tin = 0.0f;
+	// (an axis the ray runs along is left out: that only lowers the bound)
+	if (fabsf(d.x) > 1.0e-20f) { const float inv = __frcp_rn(d.x); tin = fmaxf(tin, fminf((pp.emis_lo[0] - o.x) * inv, (pp.emis_hi[0] - o.x) * inv)); }
+	if (fabsf(d.y) > 1.0e-20f) { const float inv = __frcp_rn(d.y); tin = fmaxf(tin, fminf((pp.emis_lo[1] - o.y) * inv, (pp.emis_hi[1] - o.y) * inv)); }
+	if (fabsf(d.z) > 1.0e-20f) { const float inv = __frcp_rn(d.z); tin = fmaxf(tin, fminf((pp.emis_lo[2] - o.z) * inv, (pp.emis_hi[2] - o.z) * inv)); }
+	return fminf(tin * 0.999f - 0.001f, CUPT_MAX_FLOAT);
+}
+
 // ---- shade: one iteration of radianceAlongSingleStep2 (kernel.cu:424-512) per queued path ----------------------
 // Consumes the hit, adds emission, draws the 50/50 choice (kernel.cu:459-460) between a cosine-weighted bounce
 // (kernel.cu:462-464) and a light-point sample (kernel.cu:468-507), writes the next segment and pushes the path
@@ -716,7 +736,9 @@ __global__ void __launch_bounds__(256, CUPT_SHADE_MIN_BLOCKS) k_shade(DevScene s
 				push = (wr != 0.f || wg != 0.f || wb != 0.f);
 				if (push) {
 					pb.rayA[slot] = make_float4(pos.x, pos.y, pos.z, lDir.x);
-					pb.rayB[slot] = make_float4(lDir.y, lDir.z, CUPT_MAX_FLOAT, __int_as_float(-1));
+					// .w: early-stop distance of a last segment (NaN bits = none: `best < NaN` is never true)
+					const float stop = (pp.term_stop && iter >= pp.max_depth - 1) ? emitter_entry_distance(pp, pos, lDir) : __int_as_float(-1);
+					pb.rayB[slot] = make_float4(lDir.y, lDir.z, CUPT_MAX_FLOAT, stop);
 					pb.st0[slot] = make_float4(wr, wg, wb, __uint_as_float((uint32_t)iter | (draw << 8)));
 				}
 			}
