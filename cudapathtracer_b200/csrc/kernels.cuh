@@ -572,16 +572,28 @@ __global__ void __launch_bounds__(64) k_retrace_strict(DevScene sc, PathBuffers 
 // primitive it meets (kernel.cu:453-457), so a hit in front of every emitter ends the search: whatever is nearer is not an
 // emitter either.  Returns a distance d such that no emissive primitive is met before d along the ray: the entry distance
 // of the emitters' bounding box, shortened by 0.1 % + 0.001 against the rounding of the box test and of triIntersect
-// (<= 0: no early stop possible; CUPT_MAX_FLOAT: the scene has no emitter).  k_extend<.., VIS> stops once best < d.
+// (<= 0: no early stop possible), or CUPT_MAX_FLOAT — any hit ends the search — when the ray passes the box by at least that
+// margin or the scene has no emitter.  k_extend<.., VIS> stops once best < d.
 __device__ __forceinline__ float emitter_entry_distance(const PassParams& pp, const f3 o, const f3 d)
 {
 	if (pp.emis_lo[0] > pp.emis_hi[0]) return CUPT_MAX_FLOAT;
-	float tin = 0.0f;
-	// (an axis the ray runs along is left out: that only lowers the bound)
-	if (fabsf(d.x) > 1.0e-20f) { const float inv = __frcp_rn(d.x); tin = fmaxf(tin, fminf((pp.emis_lo[0] - o.x) * inv, (pp.emis_hi[0] - o.x) * inv)); }
-	if (fabsf(d.y) > 1.0e-20f) { const float inv = __frcp_rn(d.y); tin = fmaxf(tin, fminf((pp.emis_lo[1] - o.y) * inv, (pp.emis_hi[1] - o.y) * inv)); }
-	if (fabsf(d.z) > 1.0e-20f) { const float inv = __frcp_rn(d.z); tin = fmaxf(tin, fminf((pp.emis_lo[2] - o.z) * inv, (pp.emis_hi[2] - o.z) * inv)); }
-	return fminf(tin * 0.999f - 0.001f, CUPT_MAX_FLOAT);
+	float tin = 0.0f, tout = CUPT_MAX_FLOAT;
+	// (an axis the ray runs along is left out: that only widens [tin, tout])
+	if (fabsf(d.x) > 1.0e-20f) {
+		const float inv = box_rcp(d.x), t1 = (pp.emis_lo[0] - o.x) * inv, t2 = (pp.emis_hi[0] - o.x) * inv;
+		tin = fmaxf(tin, fminf(t1, t2)); tout = fminf(tout, fmaxf(t1, t2));
+	}
+	if (fabsf(d.y) > 1.0e-20f) {
+		const float inv = box_rcp(d.y), t1 = (pp.emis_lo[1] - o.y) * inv, t2 = (pp.emis_hi[1] - o.y) * inv;
+		tin = fmaxf(tin, fminf(t1, t2)); tout = fminf(tout, fmaxf(t1, t2));
+	}
+	if (fabsf(d.z) > 1.0e-20f) {
+		const float inv = box_rcp(d.z), t1 = (pp.emis_lo[2] - o.z) * inv, t2 = (pp.emis_hi[2] - o.z) * inv;
+		tin = fmaxf(tin, fminf(t1, t2)); tout = fminf(tout, fmaxf(t1, t2));
+	}
+	const float near = tin * 0.999f - 0.001f;
+	if (fmaf(fabsf(tout), 0.001f, tout) + 0.001f < near) return CUPT_MAX_FLOAT;   // the box is behind the ray or beside it
+	return fminf(near, CUPT_MAX_FLOAT);
 }
 
 // ---- shade: one iteration of radianceAlongSingleStep2 (kernel.cu:424-512) per queued path ----------------------

@@ -685,3 +685,29 @@ def test_tile_windows_compose(ctx, get_case):
             ctx.render(0, 1)
         ctx.set_tile_window(0, 0)
     ctx.set_options(integrator=api.INTEGRATOR_PT)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["cornell_lights", "atrium20k", "soup5k", "cornell_spheres", "cornell_specular"])
+def test_last_segment_early_stop_changes_nothing(ctx, get_case, name):
+    """The ray of a path's last segment may stop at the first hit in front of the emitters' bounding box (k_shade:
+    emitter_entry_distance, k_extend's visibility variant): the next k_shade only asks that hit for its emission
+    (kernel.cu:453-457), so the image must not move.  CUPT_TERMINAL_STOP=0 turns the early stop off; the few pixels
+    allowed to differ are rays grazing an emitter, where triIntersect's own rounding decides which side of the
+    shortened distance its t falls on."""
+    import os
+    c = get_case(name)
+    load(ctx, c, api.TRAVERSAL_WIDE, max_depth=5, seed=11, samples_per_pass=0, integrator=api.INTEGRATOR_PT, collect_stats=0)
+    try:
+        os.environ["CUPT_TERMINAL_STOP"] = "0"
+        ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 8); a = ctx.read_accum(False)
+        ra = ctx.stats()["rays"]
+        os.environ["CUPT_TERMINAL_STOP"] = "1"
+        ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 8); b = ctx.read_accum(False)
+        rb = ctx.stats()["rays"]
+    finally:
+        os.environ.pop("CUPT_TERMINAL_STOP", None)
+    same = np.all(a == b, axis=-1)
+    assert same.mean() >= 0.999, (name, same.mean())
+    assert ra == rb > 0   # every ray is still traced, only some of them less far
+    assert a.sum() > 0 and abs(float(a.sum()) - float(b.sum())) <= 1e-3 * float(a.sum())
