@@ -362,7 +362,7 @@ def main():
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": n_e2e},
             "gpu_launches": int(st["kernel_launches"]),
             "stage_ms_per_step": {k: st["ms_" + k] / args.steps for k in ("raygen", "extend", "shade", "accum")},
-            "roofline": {"bound": "hbm", "kernel": "k_extend<0,false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "k_extend<0,false,*>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": (achieved / peak) if achieved else None, "peak_source": peak_src, "traffic": ncu_traffic(),
                          "algorithmic_bytes_per_launch": bytes_step / (n_ext / args.steps) if n_ext else None,
                          "launch_ms": ext_ms / n_ext, "launches": int(n_ext),

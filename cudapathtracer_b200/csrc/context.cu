@@ -246,9 +246,9 @@ PassParams make_pass(const cupt_context* c, int first_sample, int samples, int f
 	pp.inv_p_pad = ~0ull / (uint64_t)pp.p_pad + 1ull;                      // p_pad >= 32
 	pp.inv_tiles_x = pp.tiles_x > 1 ? ~0ull / (uint64_t)pp.tiles_x + 1ull : 0ull;
 	// last segments stop at the first hit in front of every emitter (k_shade): wide traversal only — the strict mode promises the
-	// reference's hit on EVERY ray — and not in stats runs, whose node / primitive counts describe full closest-hit searches
+	// reference's hit on EVERY ray.  Stats runs do the same, so that their node / primitive counts are those of the timed kernels.
 	const char* ts_env = getenv("CUPT_TERMINAL_STOP");   // (read per pass: tests/test_gpu_parity.py switches it within one process)
-	pp.term_stop = (c->opts.traversal == CUPT_TRAVERSAL_WIDE && c->opts.collect_stats == 0 && !(ts_env && atoi(ts_env) == 0)) ? 1 : 0;
+	pp.term_stop = (c->opts.traversal == CUPT_TRAVERSAL_WIDE && !(ts_env && atoi(ts_env) == 0)) ? 1 : 0;
 	for (int a = 0; a < 3; ++a) { pp.emis_lo[a] = c->emis_lo[a]; pp.emis_hi[a] = c->emis_hi[a]; }
 	return pp;
 }
