@@ -171,6 +171,10 @@ int cupt_set_camera(cupt_context* c, const cupt_camera* cam);     /* kernel.cu:6
 
 enum { CUPT_INTEGRATOR_PT = 2 /* radianceAlongSingleStep2, kernel.cu:417-515 */,
        CUPT_INTEGRATOR_BDPT = 1 /* radianceAlongSingleStep, kernel.cu:217-415: what drawPixel calls at HEAD (kernel.cu:549); max_depth is ignored */ };
+/* CUPT_TRAVERSAL_WIDE: closest hit = argmin over all primitives (ties by the reference's visiting order).  Inside cupt_render
+ * the LAST segment of a path — whose hit is only asked for its emission, kernel.cu:453-457 — may end at the first hit known to
+ * lie in front of every emitter; the image is the same, cupt_read_primary_hits / cupt_trace_rays always return the closest hit.
+ * (environment: CUPT_TERMINAL_STOP=0 switches that early stop off.) */
 enum { CUPT_TRAVERSAL_WIDE = 0, CUPT_TRAVERSAL_REF_BVH2 = 1 /* trace(), kernel.cu:112-161 op for op */,
        /* wide traversal, then every hit is checked against the reference tree's ancestor boxes with the reference's
         * slab arithmetic and re-traced the reference's way if the reference would not have reached it: results equal
