@@ -368,7 +368,7 @@ def main():
                          "launch_ms": ext_ms / n_ext, "launches": int(n_ext),
                          "bytes_per_ray": bytes_step / rays_step, "nodes_per_ray": nodes_step / rays_step, "tris_per_ray": tris_step / rays_step},
         }
-        if world == 1 and mode == api.TRAVERSAL_WIDE and not args.share_primary:
+        if world == 1 and mode == api.TRAVERSAL_WIDE and not args.share_primary and args.tri_test == "refexact":
             # the same step in the mode whose hits equal the reference's trace() on EVERY ray (the plain wide mode
             # returns the nearest triangle also on the ~1 ray in 40 000 where the reference's slab test loses it)
             ctx.set_bvh2(n2, d2)
