@@ -9,9 +9,14 @@ indices, replicated BVH) and the f32 accumulators are summed on rank 0 with one 
   value      counted Mrays/s (one ray = one extend invocation) of the whole job, scene + BVH resident in HBM
   e2e        the same through the C-ABI with HOST buffers: cupt_set_scene + cupt_set_bvh (H2D of the scene arrays
              and the BVH image), cupt_render, cupt_read_accum (D2H of the image) inside the timed region
-  roofline   extend kernel: algorithmic bytes (node visits x 80 B + triangle tests x 48 B + 44 B of ray/hit/queue
-             records per ray, counted by a stats pass of the same step) / its CUDA-event time, against the measured
-             HBM copy bandwidth
+  roofline   extend kernel: ALGORITHMIC BVH bytes (node visits x 80 B + triangle tests x 48 B, SURVEY 8d, counted by a
+             stats pass of the same step) / its CUDA-event time, against the measured HBM copy bandwidth; the 44 B per
+             ray of ray / hit / queue records and ncu's DRAM bytes are separate fields.  `bound` says what ncu shows
+             limits the kernel (instruction issue: the 16 MB BVH is L1/L2-resident), not what the fraction is taken of
+  strong     (every line) BASELINE config 3's 3840x2160 frame with a FIXED total of 128 spp split over the ranks by sample
+             ranges: device ms and e2e ms, so that the per-N lines give a strong-scaling curve next to the weak one
+  multi_gpu_check  (N > 1) rank 0 re-renders every other rank's sample range for a band of image tiles on top of its own
+             and compares with the NCCL-summed image
   cpu_baseline  the reference's own integrator (oracle/_ref, else the oracle port) on the host cores, bounded sample
   --impl reference   times that CPU implementation as the reference arm
 """
@@ -99,41 +104,73 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic():
-    """per-launch DRAM bytes of the extend kernel from the committed ncu --set full summary, if there is one"""
+def ncu_summary():
+    """the committed ncu --set full summary of the extend kernel (profiles/extend_ncu_summary.json, written by
+    tools/ncu_summarise.py from one capture of this same command): per-launch DRAM bytes and what limits the kernel"""
     p = os.path.join(ROOT, "profiles", "extend_ncu_summary.json")
-    if os.path.exists(p):
-        try:
-            return json.load(open(p)).get("dram_bytes_per_launch")
-        except Exception:
-            return None
-    return None
+    try:
+        d = json.load(open(p))
+    except Exception:
+        return {}
+    la = d.get("launches") or []
+    w = [x.get("ms", 0.0) for x in la]
+    def avg(key):
+        v = [(x[key], m) for x, m in zip(la, w) if x.get(key) is not None]
+        return sum(a * m for a, m in v) / sum(m for _, m in v) if v and sum(m for _, m in v) > 0 else None
+    return {"dram_bytes_per_launch": d.get("dram_bytes_per_launch"), "generation": d.get("generation"),
+            "threads_per_inst": avg("threads_per_inst"), "issue_active_pct": avg("issue_active_pct"),
+            "warps_active_pct": avg("warps_active_pct"), "l1_hit_pct": avg("l1_hit_pct"), "l2_hit_pct": avg("l2_hit_pct"),
+            "ms_per_launch_under_ncu": (sum(w) / len(w)) if w else None}
 
 
-def cpu_reference(scene_handle, cam, spp, threads):
-    """the reference's integrator on host cores: (rays, seconds, kind).  oracle/_ref when it was built, else the port."""
-    import oraclebind
+class _Quiet:
+    """the reference printf()s while it loads and builds (modelLoader.h:134-209, BVH.h:379-380,445,464)"""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.devnull, self.saved = os.open(os.devnull, os.O_WRONLY), os.dup(1)
+        os.dup2(self.devnull, 1)
+
+    def __exit__(self, *a):
+        os.dup2(self.saved, 1); os.close(self.devnull); os.close(self.saved)
+
+
+_ref_loaded = [None]
+
+
+def cpu_reference(cam, spp, threads):
+    """the reference's integrator on host cores: (rays, seconds, kind, BVH build seconds).
+
+    oracle/_ref (the real reference compiled for the host) when it was built: the scene goes in through the reference's
+    OWN loadOBJ (modelLoader.h:125) from the OBJ/MTL text of the procedural atrium and its own buildBVH() — nothing of
+    libcupt.so is on this path.  Only without oracle/_ref: the oracle's C port, which needs the reference-layout BVH2
+    and therefore the product's host builder of it (cupt_bvh2_build, pinned bit for bit in tests/test_bvh2.py)."""
     import refbind
-    v, t, m, l = scene_handle.arrays()
-    area = scene_handle.total_light_area
+    from cudapathtracer_b200 import scenes
     if refbind.available():
-        refbind.reset()
-        refbind.set_arrays(v, t, m, l, area)
-        devnull = os.open(os.devnull, os.O_WRONLY)
-        saved = os.dup(1)
-        os.dup2(devnull, 1)   # buildBVH() printf()s (BVH.h:379-380,445,464)
-        try:
-            t0 = time.perf_counter(); refbind.build_bvh(); tb = time.perf_counter() - t0
-        finally:
-            os.dup2(saved, 1); os.close(devnull); os.close(saved)
+        if _ref_loaded[0] is None:
+            obj, mtl = scenes.to_obj(scenes.atrium(NTRIS))
+            with _Quiet():
+                refbind.reset()
+                refbind.load_obj_text(obj, mtl)
+                t0 = time.perf_counter(); refbind.build_bvh(); _ref_loaded[0] = time.perf_counter() - t0
         t0 = time.perf_counter()
         _, _, rays = refbind.render(cam, integrator=2, num_bounces=DEPTH, rng=1, seed=SEED, first_sample=0, num_samples=spp, nthreads=threads)
-        return rays, time.perf_counter() - t0, "reference", tb
-    n2, d2 = scene_handle.build_bvh2()
-    osc = oraclebind.OracleScene(v, t, m, l, area, n2)
+        return rays, time.perf_counter() - t0, "reference", _ref_loaded[0]
+    import oraclebind
+    _, sh, _ = build_scene()
+    v, t, m, l = sh.arrays()
+    n2, d2 = sh.build_bvh2()
+    osc = oraclebind.OracleScene(v, t, m, l, sh.total_light_area, n2)
     t0 = time.perf_counter()
     _, _, rays = osc.render_pt(cam, DEPTH, SEED, 0, spp)
     return rays, time.perf_counter() - t0, "port", 0.0
+
+
+def make_camera_np(width, height):
+    """the reference's camera POD (camera.h:26-35) without the product library: same fields as api.make_camera"""
+    from cudapathtracer_b200 import api, scenes   # (importing the binding module does not load libcupt.so)
+    return api.make_camera(width, height, **scenes.atrium_camera())
 
 
 def legacy_gpu(scene_handle, cam, spp=16):
@@ -156,13 +193,13 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    sc, s, cam = build_scene()
+    cam = make_camera_np(W, H)
     threads = os.cpu_count() or 1
     spp = 1   # bounded sample per step: 1024x1024 x 1 spp of the same frame
     times, rays_total = [], 0
     kind = "port"
     for i in range(args.warmup + args.steps):
-        rays, dt, kind, _ = cpu_reference(s, cam, spp, threads)
+        rays, dt, kind, _ = cpu_reference(cam, spp, threads)
         if i >= args.warmup:
             times.append(dt); rays_total += rays
     total = sum(times)
@@ -170,13 +207,120 @@ def run_reference_arm(args):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / max(1, args.steps), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64/f32 (reference: f32 geometry, f64 colour)", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "step": f"{W}x{H} x {spp} spp of the frame on host cores"},
+            "config": {"workload": WORKLOAD},
+            "step": f"{W}x{H} x {spp} spp of the frame on host cores, scene through the reference's own loadOBJ + buildBVH",
             "msamples_per_s": W * H * spp * args.steps / total / 1e6,
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": threads, "kind": kind,
                              "sample": f"{W}x{H} x {spp} spp per step, radianceAlongSingleStep2 depth {DEPTH}, keyed Philox"},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
+
+STRONG_W, STRONG_H, STRONG_SPP = 3840, 2160, 128
+
+
+def multi_gpu_check(ctx, api, sharding, dist, torch, rank, world, ranges, accum_t, cam_w, cam_h):
+    """Does the NCCL-summed image of ranks rendering their own sample ranges equal ONE GPU rendering all of them?
+    Every rank renders its range and the accumulators are reduced to rank 0 (exactly the timed step); rank 0 then
+    renders every OTHER rank's range on top of its own accumulator for a band of image tiles (cupt_set_tile_window)
+    and compares that band with the reduced image.  Philox is keyed by the global sample index, so the two differ
+    only by the f32 summation order: required <= 1e-6 relative."""
+    first, n = ranges[rank]
+    ctx.set_tile_window(0, 0)
+    ctx.reset_accum(); ctx.render(first, n)
+    ctx.copy_accum_device(accum_t.data_ptr())
+    torch.cuda.synchronize()
+    dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+    torch.cuda.synchronize()
+    out = None
+    if rank == 0:
+        reduced = accum_t.view(cam_h, cam_w, 3).cpu().numpy()
+        ntiles = ctx.tile_count()
+        tiles_x = (cam_w + 7) // 8
+        rows = max(1, (cam_h // 4) // 16)                       # a band of 1/16 of the tile rows, in the middle of the image
+        row0 = (cam_h // 4) // 2 - rows // 2
+        ctx.set_tile_window(row0 * tiles_x, rows * tiles_x)
+        for r in range(1, world):
+            ctx.render(*ranges[r])
+        ctx.set_tile_window(0, 0)
+        own = ctx.read_accum(False).reshape(cam_h, cam_w, 3)
+        y0, y1 = row0 * 4, (row0 + rows) * 4
+        a, b = own[y0:y1].astype(np.float64), reduced[y0:y1].astype(np.float64)
+        denom = np.maximum(np.maximum(np.abs(a), np.abs(b)), 1e-3)
+        rel = np.abs(a - b) / denom
+        out = {"max_abs_diff": float(np.abs(a - b).max()), "max_rel_diff": float(rel.max()), "pixels": int((y1 - y0) * cam_w),
+               "band_rows": [int(y0), int(y1)], "mean_radiance_sum": float(b.mean()), "ranks_rerendered": world - 1,
+               "ok": bool(rel.max() <= 1e-6 and b.mean() > 0),
+               "what": "rank 0: own accumulator + every other rank's sample range re-rendered for the band, vs the NCCL-reduced image"}
+        assert ntiles == tiles_x * ((cam_h + 3) // 4)
+    dist.barrier()
+    return out
+
+
+def strong_record(ctx, api, sharding, dist, torch, s, bvh, sc, rank, world, stream, steps):
+    """BASELINE config 3's frame (3840x2160) with a FIXED total of STRONG_SPP samples split over the ranks by sample
+    ranges: device ms (CUDA events, max over ranks) and e2e ms (host buffers: scene + BVH H2D on every rank, render,
+    NCCL reduce, image D2H on rank 0)."""
+    cam = api.make_camera(STRONG_W, STRONG_H, **sc.camera)
+    ctx.set_camera(cam)
+    ranges = [sharding.sample_range(r, world, STRONG_SPP) for r in range(world)]
+    first, n = ranges[rank]
+    accum = torch.zeros(STRONG_W * STRONG_H * 3, dtype=torch.float32, device="cuda")
+    host_t = torch.empty((STRONG_W * STRONG_H, 3), dtype=torch.float32, pin_memory=True)
+
+    def step():
+        ctx.reset_accum(); ctx.render(first, n)
+        if world > 1:
+            ctx.copy_accum_device(accum.data_ptr())
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+
+    def e2e_step():
+        ctx.set_scene(s); ctx.set_camera(cam); ctx.set_bvh(bvh)
+        ctx.reset_accum(); ctx.render(first, n)
+        if world > 1:
+            ctx.copy_accum_device(accum.data_ptr())
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                host_t.copy_(accum.view(-1, 3))
+        else:
+            ctx.read_accum(False, out=host_t.numpy())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ctx.reset_stats(); step(); barrier()              # warm-up (allocates the 4K path buffers) + ray count of one step
+    rays = torch.tensor([float(ctx.stats()["rays"])], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(rays, op=dist.ReduceOp.SUM)
+    step(); barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in ev:
+        a.record(stream); step(); b.record(stream)
+    barrier()
+    tms = torch.tensor([sum(a.elapsed_time(b) for a, b in ev) / steps], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    e2e_step(); barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        e2e_step()
+    barrier()
+    te = torch.tensor([(time.perf_counter() - t0) / steps * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    check = multi_gpu_check(ctx, api, sharding, dist, torch, rank, world, ranges, accum, STRONG_W, STRONG_H) if world > 1 else None
+    ms, e2e_ms, r = float(tms.item()), float(te.item()), float(rays.item())
+    rec = {"workload": f"atrium {NTRIS} tris, {STRONG_W}x{STRONG_H}, {STRONG_SPP} spp in total split over {world} GPU(s) by sample ranges, max depth {DEPTH}",
+           "scaling": "strong", "ms": ms, "e2e_ms": e2e_ms, "steps": steps, "rays_per_step": r,
+           "value": r / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "e2e_value": r / (e2e_ms * 1e-3) / 1e6,
+           "msamples_per_s": STRONG_W * STRONG_H * STRONG_SPP / (ms * 1e-3) / 1e6,
+           "samples_per_rank": [int(x[1]) for x in ranges], "reduce_bytes": STRONG_W * STRONG_H * 12 if world > 1 else 0}
+    if check is not None:
+        rec["multi_gpu_check"] = check
+    del accum, host_t
+    return rec
 
 
 def main():
@@ -186,6 +330,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="skip the `strong` sub-record (config 3's 4K frame, 128 spp split over the GPUs)")
     ap.add_argument("--traversal", default="wide", choices=["wide", "strict", "ref"], help="wide (default), strict = wide + reference-equality check, ref = the reference algorithm on its own BVH2")
     ap.add_argument("--integrator", default="pt", choices=["pt", "bdpt"], help="pt = radianceAlongSingleStep2 with max depth 5 (the metric's config); bdpt = the reference's live radianceAlongSingleStep (what the legacy kernel.cu runs)")
     ap.add_argument("--config", type=int, default=2, choices=[2, 3], help="BASELINE.json config: 2 (default: 1024^2, 64 spp per GPU, weak scaling) or 3 (3840x2160, 1024 spp split over the GPUs, strong scaling)")
@@ -342,12 +487,29 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_val = rays_step * world * n_e2e / float(te.item()) / 1e6
 
+    # collective extras (every rank takes part): correctness of the N-GPU sum, and the strong-scaling record
+    mgc = None
+    plain = mode == api.TRAVERSAL_WIDE and args.integrator == "pt" and args.partition == "samples"
+    if world > 1 and plain:
+        ranges = [(sharding.weak_sample_range(r, SPP) if args.config == 2 else sharding.sample_range(r, world, SPP)) for r in range(world)]
+        mgc = multi_gpu_check(ctx, api, sharding, dist, torch, rank, world, ranges, accum_t, W, H)
+    strong = None
+    if args.config == 2 and plain and not args.no_strong and args.bvh == "host":
+        strong = strong_record(ctx, api, sharding, dist, torch, s, bvh, sc, rank, world, stream, max(1, min(args.steps, 2)))
+        ctx.set_camera(cam)
+
     if rank == 0:
         peak, peak_src = measured_peak()
         n_ext = max(1, st["extend_launches"])
         ext_ms = st["ms_extend"]
-        bytes_step = nodes_step * 80 + tris_step * 48 + rays_step * 44
+        # ALGORITHMIC bytes per ray = node visits x 80 B + primitive tests x 48 B (the layout shipped, csrc/layout.h);
+        # the wavefront's ray / hit / queue records (32 B ray read + 8 B hit write + 4 B queue entry) are a separate term
+        bytes_step = nodes_step * 80 + tris_step * 48
+        queue_bytes_per_ray = 44
         achieved = bytes_step * args.steps / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None
+        ncu = ncu_summary()
+        traffic = ncu.get("dram_bytes_per_launch")
+        launch_ms = ext_ms / n_ext
         line = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong" if args.config == 3 else "weak", "vs_baseline": None,
@@ -362,12 +524,21 @@ def main():
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": n_e2e},
             "gpu_launches": int(st["kernel_launches"]),
             "stage_ms_per_step": {k: st["ms_" + k] / args.steps for k in ("raygen", "extend", "shade", "accum")},
-            "roofline": {"bound": "hbm", "kernel": "k_extend<0,false,*>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": (achieved / peak) if achieved else None, "peak_source": peak_src, "traffic": ncu_traffic(),
+            "roofline": {"bound": "issue", "bound_note": "instruction issue / L1-L2 latency: the 16 MB BVH is cache-resident, DRAM carries the path records only "
+                                  "(ncu fields below); `achieved` / `frac` are SURVEY 8d's ALGORITHMIC BVH-fetch bytes against the HBM copy peak, not DRAM traffic",
+                         "roofline_of": "hbm", "kernel": "k_extend<0,false,*>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": (achieved / peak) if achieved else None, "peak_source": peak_src, "traffic": traffic,
+                         "dram_frac": (traffic / (launch_ms * 1e-3) / 1e9 / peak) if traffic and launch_ms > 0 else None,
                          "algorithmic_bytes_per_launch": bytes_step / (n_ext / args.steps) if n_ext else None,
-                         "launch_ms": ext_ms / n_ext, "launches": int(n_ext),
-                         "bytes_per_ray": bytes_step / rays_step, "nodes_per_ray": nodes_step / rays_step, "tris_per_ray": tris_step / rays_step},
+                         "launch_ms": launch_ms, "launches": int(n_ext),
+                         "bytes_per_ray": bytes_step / rays_step, "nodes_per_ray": nodes_step / rays_step, "tris_per_ray": tris_step / rays_step,
+                         "node_bytes": 80, "prim_bytes": 48, "queue_bytes_per_ray": queue_bytes_per_ray,
+                         "ncu": {k: ncu.get(k) for k in ("generation", "issue_active_pct", "threads_per_inst", "warps_active_pct", "l1_hit_pct", "l2_hit_pct", "ms_per_launch_under_ncu")}},
         }
+        if mgc is not None:
+            line["multi_gpu_check"] = mgc
+        if strong is not None:
+            line["strong"] = strong
         if world == 1 and mode == api.TRAVERSAL_WIDE and not args.share_primary and args.tri_test == "refexact":
             # the same step in the mode whose hits equal the reference's trace() on EVERY ray (the plain wide mode
             # returns the nearest triangle also on the ~1 ray in 40 000 where the reference's slab test loses it)
@@ -389,7 +560,7 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             spp_cpu = 4
-            rays, dt, kind, tb = cpu_reference(s, cam, spp_cpu, threads)
+            rays, dt, kind, tb = cpu_reference(cam, spp_cpu, threads)
             line["cpu_baseline"] = {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
                                     "sample": f"{W}x{H} x {spp_cpu} spp of the same frame ({rays} rays in {dt:.1f} s; reference BVH build {tb:.1f} s not included)"}
         if world == 1 and not args.no_cpu_baseline:

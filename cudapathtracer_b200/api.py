@@ -38,7 +38,7 @@ class CuptError(RuntimeError):
 
 
 class BvhOpts(C.Structure):
-    _fields_ = [("sah_bins", C.c_int), ("max_leaf_tris", C.c_int), ("threads", C.c_int), ("tie_rank", C.c_void_p), ("ploc_radius", C.c_int)]
+    _fields_ = [("sah_bins", C.c_int), ("max_leaf_tris", C.c_int), ("threads", C.c_int), ("tie_rank", C.c_void_p), ("ploc_radius", C.c_int), ("greedy_collapse", C.c_int)]
 
 
 class BvhInfo(C.Structure):
@@ -51,7 +51,7 @@ class RenderOpts(C.Structure):
     _fields_ = [("max_depth", C.c_int32), ("integrator", C.c_int32), ("traversal", C.c_int32), ("tri_test", C.c_int32),
                 ("seed", C.c_uint64), ("samples_per_pass", C.c_int32), ("collect_stats", C.c_int32),
                 ("time_stages", C.c_int32), ("fetch_threshold", C.c_int32), ("defer_pairs", C.c_int32),
-                ("share_primary_hits", C.c_int32)]
+                ("share_primary_hits", C.c_int32), ("no_terminal_stop", C.c_int32), ("record_retraces", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -221,8 +221,8 @@ class SceneHandle:
             self.lib.cupt_bvh2_free(p)
         return nodes, depth.value
 
-    def build_bvh(self, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None) -> "BvhHandle":
-        return BvhHandle(self, sah_bins, max_leaf_tris, threads, tie_rank)
+    def build_bvh(self, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None, greedy_collapse=False) -> "BvhHandle":
+        return BvhHandle(self, sah_bins, max_leaf_tris, threads, tie_rank, greedy_collapse)
 
 
 def bvh2_leaf_order(nodes: np.ndarray, ntris: int) -> np.ndarray:
@@ -242,11 +242,11 @@ assert NODE8.itemsize == 80 and PRIM48.itemsize == 48
 class BvhHandle:
     """cupt_bvh: host image of the 8-wide quantised BVH (replaces buildBVH, BVH.h:443-474)."""
 
-    def __init__(self, scene: SceneHandle, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None):
+    def __init__(self, scene: SceneHandle, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None, greedy_collapse=False):
         self.h = None
         self.lib = load_library()
         self._rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, dtype=np.uint32)
-        opts = BvhOpts(sah_bins, max_leaf_tris, threads, None if self._rank is None else self._rank.ctypes.data)
+        opts = BvhOpts(sah_bins, max_leaf_tris, threads, None if self._rank is None else self._rank.ctypes.data, 0, int(greedy_collapse))
         h = C.c_void_p()
         _check(self.lib.cupt_bvh_build(scene.h, C.byref(opts), C.byref(h)))
         self.h = h
@@ -401,6 +401,13 @@ class Context:
         ids, ts = np.empty(h * w, dtype=np.int32), np.empty(h * w, dtype=np.float32)
         _check(self.lib.cupt_read_primary_hits(self.h, _ptr(ids), _ptr(ts)))
         return ids, ts
+
+    def read_retrace_counts(self) -> np.ndarray:
+        """strict mode with record_retraces=1: per pixel, the rays since reset_accum whose wide hit the reference would not have reached"""
+        h, w = self.shape
+        out = np.empty(h * w, dtype=np.uint32)
+        _check(self.lib.cupt_read_retrace_counts(self.h, _ptr(out)))
+        return out
 
     def camera_rays(self):
         h, w = self.shape

@@ -797,7 +797,8 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 		prim_base += (uint32_t)(*h_total >> 32);
 		n_items = (int)(uint32_t)*h_total;
 		lvl ^= 1;
-		if (depth > 255) return set_error(CUPT_ERR_LIMIT, "wide BVH deeper than 255 levels");
+		// the same bound cupt_set_bvh applies: the extend kernel's shared-memory stack holds `depth` entries per thread
+		if (depth > 64) return set_error(CUPT_ERR_LIMIT, "wide BVH deeper than 64 levels (the traversal stack's limit, as for cupt_set_bvh)");
 	}
 	k_emit_prims<<<tilesN, kTile, 0, st>>>(reinterpret_cast<const int32_t*>(nn), N, nt, verts, tris, spheres, rank, static_cast<float4*>(out->prims));
 	CKB(cudaEventRecord(ev[3], st));

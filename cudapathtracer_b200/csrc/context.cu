@@ -51,7 +51,9 @@ struct cupt_context {
 	double ms[4] = {0, 0, 0, 0};
 	std::vector<StageEvent> pending, pool;
 	std::map<void**, size_t> capacity;   // bytes behind each uploaded device pointer (upload())
-	int extend_blocks[2] = {0, 0};
+	// persistent grid of the extend stage per kernel instantiation (mode, stats, vis): blocks, and the dynamic shared memory it was sized for
+	int extend_blocks[2][2][2] = {}; size_t extend_smem[2][2][2] = {};
+	uint32_t* d_retrace_counts = nullptr; size_t retrace_pixels = 0;   // cupt_render_opts.record_retraces
 	BuildArena arena; uint32_t* d_build_rank = nullptr; uint8_t* d_rgb8 = nullptr;
 	float4* d_prims_wt = nullptr; bool wt_valid = false;   // CUPT_TRI_WATERTIGHT: vertex records, same order as d_prims
 	float build_ms[4] = {0, 0, 0, 0}; int build_rounds = 0;   // last cupt_build_bvh_device: total, sort, PLOC, collapse
@@ -198,6 +200,19 @@ int ensure_accum(cupt_context* c)
 	return CUPT_OK;
 }
 
+// per-pixel re-trace counters of the strict mode (cupt_render_opts.record_retraces)
+int ensure_retrace_counts(cupt_context* c)
+{
+	if (!c->opts.record_retraces || c->opts.traversal != CUPT_TRAVERSAL_WIDE_STRICT) return CUPT_OK;
+	const size_t P = (size_t)c->cam.pxlWidth * c->cam.pxlHeight;
+	if (c->d_retrace_counts && c->retrace_pixels == P) return CUPT_OK;
+	if (c->d_retrace_counts) { CK(cudaFree(c->d_retrace_counts)); c->d_retrace_counts = nullptr; }
+	CK(cudaMalloc((void**)&c->d_retrace_counts, P * sizeof(uint32_t)));
+	CK(cudaMemsetAsync(c->d_retrace_counts, 0, P * sizeof(uint32_t), c->stream));
+	c->retrace_pixels = P;
+	return CUPT_OK;
+}
+
 void stage_begin(cupt_context* c, int stage, StageEvent& ev)
 {
 	if (!c->opts.time_stages) return;
@@ -233,7 +248,7 @@ PassParams make_pass(const cupt_context* c, int first_sample, int samples, int f
 	pp.samples = samples;
 	pp.tiles_x = (c->cam.pxlWidth + 7) / 8;
 	pp.tiles_y = (c->cam.pxlHeight + 3) / 4;
-	const int all_tiles = pp.tiles_x * pp.tiles_y;
+	const int all_tiles = pp.tiles_x * pp.tiles_y;   // <= 8192 x 16384 = 2^27 for the 65535 x 65535 limit of cupt_set_camera
 	pp.tile0 = 0;
 	int ntiles = all_tiles;
 	if (window && c->tile_count > 0) {
@@ -247,8 +262,7 @@ PassParams make_pass(const cupt_context* c, int first_sample, int samples, int f
 	pp.inv_tiles_x = pp.tiles_x > 1 ? ~0ull / (uint64_t)pp.tiles_x + 1ull : 0ull;
 	// last segments stop at the first hit in front of every emitter (k_shade): wide traversal only — the strict mode promises the
 	// reference's hit on EVERY ray.  Stats runs do the same, so that their node / primitive counts are those of the timed kernels.
-	const char* ts_env = getenv("CUPT_TERMINAL_STOP");   // (read per pass: tests/test_gpu_parity.py switches it within one process)
-	pp.term_stop = (c->opts.traversal == CUPT_TRAVERSAL_WIDE && !(ts_env && atoi(ts_env) == 0)) ? 1 : 0;
+	pp.term_stop = (c->opts.traversal == CUPT_TRAVERSAL_WIDE && !c->opts.no_terminal_stop) ? 1 : 0;
 	for (int a = 0; a < 3; ++a) { pp.emis_lo[a] = c->emis_lo[a]; pp.emis_hi[a] = c->emis_hi[a]; }
 	return pp;
 }
@@ -293,11 +307,23 @@ int check_ready(cupt_context* c, bool need_shading, bool need_cam = true)
 	return CUPT_OK;
 }
 
-// persistent launch of the extend stage for queue `depth`
-int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel, bool vis = false)
+// strict mode, record_retraces: one count per pixel and re-traced ray (slots_per_path: 4 ray records per BDPT path)
+__global__ void __launch_bounds__(256) k_record_retraces(PassParams pp, PathBuffers pb, uint32_t* __restrict__ counts, uint32_t slots_per_path)
+{
+	const uint32_t n = pb.counters[126];
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		int x, y, sl;
+		slot_to_pixel(pp, pb.retrace[i] / slots_per_path, x, y, sl);
+		if (x < pp.cam.pxlWidth && y < pp.cam.pxlHeight) atomicAdd(&counts[(size_t)y * pp.cam.pxlWidth + x], 1u);
+	}
+}
+
+// persistent launch of the extend stage for queue `depth`; pp (render passes only): where the strict mode records its re-traces
+int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel, bool vis = false, const PassParams* pp = nullptr, uint32_t slots_per_path = 1)
 {
 	const int mode = c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 ? 1 : 0;
 	const bool stats = c->opts.collect_stats != 0;
+	if (mode == 1) vis = false;
 	const size_t smem = mode == 0 ? (size_t)sc.stack_cap * 128 * sizeof(uint2) + 128 * 16 : 0;   // stacks + per-warp keys/list/ids
 	ExtendTuning tune;
 	tune.fetch_thresh = c->opts.fetch_threshold > 0 ? std::min(c->opts.fetch_threshold, 31) : 24;
@@ -306,21 +332,19 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel, bool
 	void (*kern)(DevScene, PathBuffers, int, int, ExtendTuning) =
 		mode == 0 ? (vis ? (stats ? k_extend<0, true, true> : k_extend<0, false, true>) : (stats ? k_extend<0, true, false> : k_extend<0, false, false>))
 		          : (stats ? k_extend<1, true, false> : k_extend<1, false, false>);
-	if (c->extend_blocks[mode] == 0 || mode == 0) {
+	int& blocks = c->extend_blocks[mode][stats ? 1 : 0][vis ? 1 : 0];
+	size_t& sized_for = c->extend_smem[mode][stats ? 1 : 0][vis ? 1 : 0];
+	if (blocks == 0 || sized_for != smem) {   // once per instantiation and stack size (cupt_set_bvh / cupt_build_bvh_device change the latter)
 		if (smem > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 		int per_sm = 0;
 		CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
-		static const char* bps = getenv("CUPT_EXTEND_BLOCKS_PER_SM");   // experiment knob: fewer resident blocks than the occupancy allows
-		if (bps && atoi(bps) > 0) per_sm = std::min(per_sm, atoi(bps));
-		c->extend_blocks[mode] = std::max(1, per_sm) * c->num_sms;
-		// experiment knob (tools/): shared-memory carveout in percent.  Measured on config 2: 30 (64 KB: 4 resident blocks, 164 KB
-		// of L1) 33.9 ms of extend per frame, default / 44 / 50 (100 KB: 7 blocks, 128 KB of L1) 34.2, 58 34.5, 72 35.2
-		static const char* cv = getenv("CUPT_CARVEOUT");
-		if (cv) CK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(cv)));
+		if (per_sm < 1) return set_error(CUPT_ERR_LIMIT, "the extend kernel does not fit an SM with a traversal stack of %d entries (%zu bytes of shared memory per block)", sc.stack_cap, smem);
+		blocks = per_sm * c->num_sms;
+		sized_for = smem;
 	}
 	StageEvent ev;
 	stage_begin(c, 1, ev);
-	kern<<<c->extend_blocks[mode], 128, smem, c->stream>>>(sc, c->pb, depth, qsel, tune);
+	kern<<<blocks, 128, smem, c->stream>>>(sc, c->pb, depth, qsel, tune);
 	stage_end(c, ev);
 	CK(cudaGetLastError());
 	c->launches++; c->extend_launches++;
@@ -340,6 +364,11 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel, bool
 		stage_end(c, ev2);
 		CK(cudaGetLastError());
 		c->launches += 2;
+		if (pp && c->opts.record_retraces && c->d_retrace_counts) {
+			k_record_retraces<<<c->num_sms, 256, 0, c->stream>>>(*pp, c->pb, c->d_retrace_counts, slots_per_path);
+			CK(cudaGetLastError());
+			c->launches++;
+		}
 	}
 	return CUPT_OK;
 }
@@ -391,7 +420,7 @@ void cupt_destroy(cupt_context* c)
 	cudaFree(c->d_nodes); cudaFree(c->d_prims); cudaFree(c->d_bvh2); cudaFree(c->d_bvh2_up); cudaFree(c->d_bvh2_leaf_parent);
 	cudaFree(c->pb.rayA); cudaFree(c->pb.rayB); cudaFree(c->pb.st0); cudaFree(c->pb.st1);
 	cudaFree(c->pb.queue[0]); cudaFree(c->pb.queue[1]); cudaFree(c->pb.counters); cudaFree(c->pb.stats); cudaFree(c->pb.retrace);
-	cudaFree(c->d_accum); cudaFree(c->d_build_rank); cudaFree(c->d_rgb8); cudaFree(c->d_prims_wt); c->arena.destroy();
+	cudaFree(c->d_accum); cudaFree(c->d_retrace_counts); cudaFree(c->d_build_rank); cudaFree(c->d_rgb8); cudaFree(c->d_prims_wt); c->arena.destroy();
 	if (c->h_stage) cudaFreeHost(c->h_stage);
 	if (c->stage_ev) cudaEventDestroy(c->stage_ev);
 	if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -437,6 +466,9 @@ int cupt_set_camera(cupt_context* c, const cupt_camera* cam)
 	if (!c || !cam) return set_error(CUPT_ERR_INVALID, "bad arguments");
 	if (cam->pxlWidth < 1 || cam->pxlHeight < 1 || cam->pxlWidth > 65535 || cam->pxlHeight > 65535)
 		return set_error(CUPT_ERR_INVALID, "image size %dx%d outside 1..65535 (pixel coordinates are uint16_t, camera.h:36)", cam->pxlWidth, cam->pxlHeight);
+	// pixel and path-slot indices are 32-bit on the device (k_raygen, k_accumulate, k_tonemap_rgb8, k_heatmap)
+	if ((int64_t)((cam->pxlWidth + 7) / 8) * ((cam->pxlHeight + 3) / 4) * 32 > 0x7fffffff)
+		return set_error(CUPT_ERR_LIMIT, "image of %d x %d pixels exceeds 2^31 - 1 pixel slots (8x4-pixel tiles)", cam->pxlWidth, cam->pxlHeight);
 	c->cam = *cam;
 	c->have_cam = true;
 	return CUPT_OK;
@@ -537,7 +569,7 @@ int cupt_set_bvh(cupt_context* c, const cupt_bvh* b)
 	if ((rc = upload(c, &c->d_nodes, b->nodes.data(), b->nodes.size() * sizeof(Node8)))) return rc;
 	if ((rc = upload(c, &c->d_prims, b->prims.data(), b->prims.size() * sizeof(Prim48)))) return rc;
 	c->bvh_depth = b->depth; c->num_nodes = (int64_t)b->nodes.size(); c->num_prims = (int64_t)b->prims.size();
-	c->extend_blocks[0] = 0; c->wt_valid = false;
+	c->wt_valid = false;
 	return uploads_done(c);   // the caller may destroy the cupt_bvh right after this call
 }
 
@@ -562,7 +594,6 @@ int cupt_build_bvh_device(cupt_context* c, const cupt_bvh_opts* opts, cupt_bvh_i
 	c->wt_valid = false;
 	if (rc) { c->num_nodes = c->num_prims = 0; return rc; }
 	c->bvh_depth = r.depth; c->num_nodes = r.num_nodes; c->num_prims = r.num_prims;
-	c->extend_blocks[0] = 0;
 	if (info) {
 		info->num_nodes = r.num_nodes; info->num_tri_records = r.num_prims;
 		info->num_tris = c->num_tris; info->num_spheres = c->num_spheres;
@@ -675,7 +706,12 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 	if (S <= 0) S = (int)std::max<int64_t>(1, (int64_t)((bdpt ? 16 : 64) << 20) / probe.p_pad);
 	S = std::min(S, std::max(1, num_samples));
 	const int64_t per_path = bdpt ? 4 : 1;
-	if ((int64_t)probe.p_pad * S * per_path > 0x7fffffff) S = (int)(0x7fffffff / (probe.p_pad * per_path));
+	// slot indices are 32-bit: a pass holds at most 2^31 - 1 ray records.  An image too large for even one sample per pass
+	// (about 23 000 x 23 000 pixels with BDPT's four records per path) is refused rather than rendered with S = 0 passes.
+	if ((int64_t)probe.p_pad * per_path > 0x7fffffff)
+		return set_error(CUPT_ERR_LIMIT, "image of %d x %d pixels needs more than 2^31 - 1 ray records per sample (render it in tile windows: cupt_set_tile_window)", c->cam.pxlWidth, c->cam.pxlHeight);
+	if ((int64_t)probe.p_pad * S * per_path > 0x7fffffff) S = (int)(0x7fffffff / ((int64_t)probe.p_pad * per_path));
+	if ((rc = ensure_retrace_counts(c))) return rc;
 	if ((rc = ensure_paths(c, (size_t)probe.p_pad * S * per_path))) return rc;
 	const int grid = c->num_sms * 8;
 	for (int done = 0; done < num_samples; done += S) {
@@ -688,15 +724,15 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 			stage_begin(c, 0, ev);
 			k_bdpt_gen<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb);
 			stage_end(c, ev);
-			if ((rc = launch_extend(c, sc, 0, 0))) return rc;
+			if ((rc = launch_extend(c, sc, 0, 0, false, &pp, 4))) return rc;
 			stage_begin(c, 2, ev);
 			k_bdpt_mid<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb);
 			stage_end(c, ev);
-			if ((rc = launch_extend(c, sc, 1, 1))) return rc;
+			if ((rc = launch_extend(c, sc, 1, 1, false, &pp, 4))) return rc;
 			stage_begin(c, 2, ev);
 			k_bdpt_connect<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb);
 			stage_end(c, ev);
-			if ((rc = launch_extend(c, sc, 2, 0, true))) return rc;   // visibility rays: t limit + early stop
+			if ((rc = launch_extend(c, sc, 2, 0, true, &pp, 4))) return rc;   // visibility rays: t limit + early stop
 			stage_begin(c, 3, ev);
 			k_bdpt_resolve<<<grid, 256, 0, c->stream>>>(c->pb);
 			k_bdpt_accumulate<<<(pp.p_pad + 255) / 256, 256, 0, c->stream>>>(pp, c->pb, c->d_accum);
@@ -723,7 +759,7 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 				k_broadcast_primary<<<grid, 256, 0, c->stream>>>(pp, c->pb);
 				stage_end(c, ev);
 				c->launches++;
-			} else if ((rc = launch_extend(c, sc, depth, depth & 1, depth > 0 && pp.term_stop))) return rc;
+			} else if ((rc = launch_extend(c, sc, depth, depth & 1, depth > 0 && pp.term_stop, &pp))) return rc;
 			stage_begin(c, 2, ev);
 			k_shade<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb, depth, depth & 1);
 			stage_end(c, ev);
@@ -761,6 +797,7 @@ int cupt_tile_count(const cupt_context* c, int* num_tiles)
 int cupt_sync(cupt_context* c)
 {
 	if (!c) return set_error(CUPT_ERR_INVALID, "null context");
+	CK(cudaSetDevice(c->device));
 	CK(cudaStreamSynchronize(c->stream));
 	drain_events(c);
 	return CUPT_OK;
@@ -773,7 +810,20 @@ int cupt_reset_accum(cupt_context* c)
 	int rc = ensure_accum(c);
 	if (rc) return rc;
 	CK(cudaMemsetAsync(c->d_accum, 0, c->accum_pixels * 3 * sizeof(float), c->stream));
+	if (c->d_retrace_counts) CK(cudaMemsetAsync(c->d_retrace_counts, 0, c->retrace_pixels * sizeof(uint32_t), c->stream));
 	c->samples_accumulated = 0;
+	return CUPT_OK;
+}
+
+int cupt_read_retrace_counts(cupt_context* c, uint32_t* counts)
+{
+	if (!c || !counts || !c->have_cam) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	const size_t P = (size_t)c->cam.pxlWidth * c->cam.pxlHeight;
+	if (!c->d_retrace_counts || c->retrace_pixels != P)
+		return set_error(CUPT_ERR_INVALID, "no re-trace counts: render in CUPT_TRAVERSAL_WIDE_STRICT with record_retraces = 1 first");
+	CK(cudaSetDevice(c->device));
+	CK(cudaMemcpyAsync(counts, c->d_retrace_counts, P * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
 	return CUPT_OK;
 }
 
@@ -795,6 +845,7 @@ int cupt_read_accum(cupt_context* c, float* rgb_host, int normalise)
 int cupt_copy_accum_device(cupt_context* c, float* dst_device)
 {
 	if (!c || !dst_device || !c->d_accum) return set_error(CUPT_ERR_INVALID, "nothing rendered");
+	CK(cudaSetDevice(c->device));
 	CK(cudaMemcpyAsync(dst_device, c->d_accum, c->accum_pixels * 3 * sizeof(float), cudaMemcpyDeviceToDevice, c->stream));
 	return CUPT_OK;
 }
@@ -804,6 +855,7 @@ int cupt_add_accum_device(cupt_context* c, const float* src_device, int samples)
 	if (!c || !src_device || samples < 0) return set_error(CUPT_ERR_INVALID, "bad arguments");
 	int rc = check_ready(c, false);
 	if (rc) return rc;
+	CK(cudaSetDevice(c->device));
 	if ((rc = ensure_accum(c))) return rc;
 	const size_t n = c->accum_pixels * 3;
 	k_add<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->d_accum, src_device, n);
@@ -827,7 +879,8 @@ static int primary_pass(cupt_context* c, int32_t* tri_id, float* t, float* rays6
 	CK(cudaMemsetAsync(c->pb.counters, 0, 128 * sizeof(uint32_t), c->stream));
 	k_raygen<<<c->num_sms * 8, 256, 0, c->stream>>>(pp, c->pb);
 	c->launches++;
-	if (tri_id) { const DevScene sc = make_scene(c); if ((rc = launch_extend(c, sc, 0, 0))) return rc; }
+	if ((rc = ensure_retrace_counts(c))) return rc;
+	if (tri_id) { const DevScene sc = make_scene(c); if ((rc = launch_extend(c, sc, 0, 0, false, &pp))) return rc; }
 	k_gather_primary<<<(pp.p_pad + 255) / 256, 256, 0, c->stream>>>(pp, c->pb, d_ids, d_t, d_r);
 	c->launches++;
 	CK(cudaGetLastError());

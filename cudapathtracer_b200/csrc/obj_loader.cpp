@@ -10,6 +10,24 @@
 //     first-use order (tiny_obj_loader.cc:305-339,341-411)
 //   * `mtllib` read from <mtl_dir><name>; materials flushed on `newmtl` and at end of file, a nameless default
 //     material appended when the file ends (tiny_obj_loader.cc:413-615); `Kd`, `Ke` are the fields loadOBJ reads
+//
+// ATTRIBUTION.  parse_number, fix_index and next_corner below follow tiny_obj_loader's tryParseDouble, fixIndex and
+// parseTriple step by step (same accumulation order, same `ldexp(mant * pow(5, e), e)` assembly) because bit-identical
+// floats and the same vertex numbering are the point; they are derived from that third-party code, which is
+//     Copyright 2012-2015, Syoyo Fujita.  Licensed under the 2-clause BSD license:
+//     Redistribution and use in source and binary forms, with or without modification, are permitted provided that
+//     the following conditions are met: 1. Redistributions of source code must retain the above copyright notice,
+//     this list of conditions and the following disclaimer.  2. Redistributions in binary form must reproduce the
+//     above copyright notice, this list of conditions and the following disclaimer in the documentation and/or other
+//     materials provided with the distribution.
+//     THIS SOFTWARE IS PROVIDED BY THE COPYRIGHT HOLDERS AND CONTRIBUTORS "AS IS" AND ANY EXPRESS OR IMPLIED
+//     WARRANTIES, INCLUDING, BUT NOT LIMITED TO, THE IMPLIED WARRANTIES OF MERCHANTABILITY AND FITNESS FOR A
+//     PARTICULAR PURPOSE ARE DISCLAIMED.  IN NO EVENT SHALL THE COPYRIGHT OWNER OR CONTRIBUTORS BE LIABLE FOR ANY
+//     DIRECT, INDIRECT, INCIDENTAL, SPECIAL, EXEMPLARY, OR CONSEQUENTIAL DAMAGES (INCLUDING, BUT NOT LIMITED TO,
+//     PROCUREMENT OF SUBSTITUTE GOODS OR SERVICES; LOSS OF USE, DATA, OR PROFITS; OR BUSINESS INTERRUPTION) HOWEVER
+//     CAUSED AND ON ANY THEORY OF LIABILITY, WHETHER IN CONTRACT, STRICT LIABILITY, OR TORT (INCLUDING NEGLIGENCE OR
+//     OTHERWISE) ARISING IN ANY WAY OUT OF THE USE OF THIS SOFTWARE, EVEN IF ADVISED OF THE POSSIBILITY OF SUCH DAMAGE.
+// The rest of this file is an independent parser.
 #include "host_common.h"
 #include <cctype>
 #include <cstdlib>

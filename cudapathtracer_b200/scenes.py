@@ -187,6 +187,13 @@ def cornell_box(extra_lights: int = 0, spheres: bool = False, specular: bool = F
     return Scene(mats, shapes, dict(REFERENCE_CAMERA), sph, [6, 2] if specular else [])
 
 
+ATRIUM_CAMERA = dict(pos=(0.0, 2.2, 17.5), distFromFilm=1.0, focalLength=3.0, radius=0.0)
+
+
+def atrium_camera() -> dict:
+    return dict(ATRIUM_CAMERA)
+
+
 def atrium(n_tris: int = 262144, seed: int = 1) -> Scene:
     """Two-storey colonnaded hall, 23 x 15 x 37 units (x, y, z), long axis z, camera at the +z end looking
     down -z (the reference camera has no orientation, camera.h:77-97).  Exactly `n_tris` triangles: the
@@ -254,7 +261,7 @@ def atrium(n_tris: int = 262144, seed: int = 1) -> Scene:
     if k > 0:  # a thin strip just under the far wall takes the remainder so the count is exact
         floor_parts.append(quad_grid((-X, 0.0, -Z - 0.25), (0, 0, 0.25), (2 * X, 0, 0), 1, k))
     shapes.append(Shape("floor", *merge(floor_parts), 0))
-    sc = Scene(mats, shapes, dict(pos=(0.0, 2.2, 17.5), distFromFilm=1.0, focalLength=3.0, radius=0.0))
+    sc = Scene(mats, shapes, atrium_camera())
     assert sc.num_triangles == n_tris, (sc.num_triangles, n_tris)
     return sc
 

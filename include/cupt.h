@@ -130,6 +130,8 @@ typedef struct cupt_bvh_opts {
 	int threads;           /* host threads, 0 = all */
 	const uint32_t* tie_rank;  /* optional rank per triangle (cupt_bvh2_leaf_order); NULL = triangle index */
 	int ploc_radius;       /* cupt_build_bvh_device only: neighbour search radius of the clustering: 1, 2, 4 (default, also for any other value), 8, 16 or 32 */
+	int greedy_collapse;   /* cupt_bvh_build only: 1 = open the largest child until there are eight (the first collapse rule, kept for
+	                          comparison: tools/build_compare.py); default 0 = cost-optimal cut */
 } cupt_bvh_opts;
 typedef struct cupt_bvh_info {
 	int64_t num_nodes;       /* 80-byte BVH8 nodes */
@@ -174,7 +176,7 @@ enum { CUPT_INTEGRATOR_PT = 2 /* radianceAlongSingleStep2, kernel.cu:417-515 */,
 /* CUPT_TRAVERSAL_WIDE: closest hit = argmin over all primitives (ties by the reference's visiting order).  Inside cupt_render
  * the LAST segment of a path — whose hit is only asked for its emission, kernel.cu:453-457 — may end at the first hit known to
  * lie in front of every emitter; the image is the same, cupt_read_primary_hits / cupt_trace_rays always return the closest hit.
- * (environment: CUPT_TERMINAL_STOP=0 switches that early stop off.) */
+ * (cupt_render_opts.no_terminal_stop = 1 switches that early stop off.) */
 enum { CUPT_TRAVERSAL_WIDE = 0, CUPT_TRAVERSAL_REF_BVH2 = 1 /* trace(), kernel.cu:112-161 op for op */,
        /* wide traversal, then every hit is checked against the reference tree's ancestor boxes with the reference's
         * slab arithmetic and re-traced the reference's way if the reference would not have reached it: results equal
@@ -201,6 +203,10 @@ typedef struct cupt_render_opts {
 	                             * bit for bit, fewer rays traced (and counted).  Default 0; CUPT_INTEGRATOR_PT and CUPT_TRAVERSAL_WIDE
 	                             * only (the reference's slab test distinguishes the +0 / -0 direction components that
 	                             * different samples get on the centre column and row). */
+	int32_t no_terminal_stop; /* 1: last segments are traced to their closest hit like every other ray (default 0: early stop, see
+	                           * CUPT_TRAVERSAL_WIDE above; never used by the strict / reference modes) */
+	int32_t record_retraces;  /* CUPT_TRAVERSAL_WIDE_STRICT: 1 = count, per pixel, the rays of its paths whose wide hit the reference
+	                           * would not have reached (cupt_read_retrace_counts); the counts accumulate until cupt_reset_accum */
 } cupt_render_opts;
 int cupt_default_render_opts(cupt_render_opts* o);
 int cupt_set_render_opts(cupt_context* c, const cupt_render_opts* o);
@@ -224,6 +230,10 @@ int cupt_add_accum_device(cupt_context* c, const float* src_device, int samples)
 int cupt_read_primary_hits(cupt_context* c, int32_t* tri_id, float* t);
 int cupt_trace_rays(cupt_context* c, const float* rays_host /* n*6: o, dir */, int64_t n, int32_t* tri_id, float* t);
 int cupt_camera_rays(cupt_context* c, float* rays_host /* P*6 */);
+/* parity hook (record_retraces): per pixel, row-major, how many rays of the paths rendered since cupt_reset_accum had a
+ * wide-BVH hit the reference's trace() would not have reached (BVH.h:65,79: its slab test is not conservative) and
+ * were therefore re-traced.  Pixels with 0 carry paths on which the plain wide mode and the reference agree ray by ray. */
+int cupt_read_retrace_counts(cupt_context* c, uint32_t* counts);
 
 typedef struct cupt_stats {
 	uint64_t rays;            /* extend invocations (one ray = one trace(), counted not nominal) */

@@ -76,7 +76,10 @@ def full(rep, prefix):
             "dram_bytes": rd * scale[u("dram__bytes_read.sum")] + wr * scale[u("dram__bytes_write.sum")],
             "threads_per_inst": float(g("smsp__thread_inst_executed_per_inst_executed.ratio")),
             "warp_inst": float(g("smsp__inst_executed.sum")), "regs": int(g("launch__registers_per_thread")),
-            "l1_hit_pct": float(g("l1tex__t_sector_hit_rate.pct")), "l2_hit_pct": float(g("lts__t_sector_hit_rate.pct"))})
+            "l1_hit_pct": float(g("l1tex__t_sector_hit_rate.pct")), "l2_hit_pct": float(g("lts__t_sector_hit_rate.pct")),
+            "issue_active_pct": float(g("smsp__issue_active.avg.pct_of_peak_sustained_active")),
+            "warps_active_pct": float(g("sm__warps_active.avg.pct_of_peak_sustained_active")),
+            "dram_throughput_pct": float(g("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"))})
     summary["dram_bytes_per_launch"] = sum(l["dram_bytes"] for l in summary["launches"]) / max(1, len(summary["launches"]))
     json.dump(summary, open(prefix + "_summary.json", "w"), indent=1)
     # opcode mix + stall samples of the longest captured launch
