@@ -71,6 +71,19 @@ struct PhiloxStream {
 	}
 };
 
+// ---- packed single precision (sm_100: fma.rn.f32x2 / add.rn.f32x2, SASS FFMA2 / FADD2) ----------------------------
+// One instruction works on the two f32 halves of a 64-bit register pair; each half rounds exactly like the scalar
+// fma / add, so a packed evaluation gives the bits of the scalar one in half the issue slots.  A pair whose halves are
+// the same scalar costs nothing: the SASS forms take a broadcast operand (`R.F32`).
+#ifndef CUPT_HOST_EMUL
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ float lo2(f32x2 v) { float lo, hi; asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); return lo; }
+__device__ __forceinline__ float hi2(f32x2 v) { float lo, hi; asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); return hi; }
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ f32x2 fadd2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+#endif
+
 // ---- 128-bit read-only fetches -----------------------------------------------------------------------------
 __device__ __forceinline__ uint4 ldg_nc_u4(const void* p)
 {

@@ -382,7 +382,7 @@ __global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene
 	if (MODE == 0) {
 		// front-to-back order of the hit inner children (wide_node_step_fast): perm[oct][mask] has bit (s ^ oct) set for every slot s in mask
 		__shared__ uint8_t s_perm[8 * 256];
-		for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) {
+		for (uint32_t i = threadIdx.x; i < 8u * 256u; i += 128u) {   // (128 = the block size this kernel is launched with; a run-time stride costs a division)
 			uint32_t v = 0u;
 			for (uint32_t sl = 0; sl < 8u; ++sl)
 				if ((i >> sl) & 1u) v |= 1u << (sl ^ (i >> 8));
@@ -390,7 +390,7 @@ __global__ void __launch_bounds__(128, CUPT_EXTEND_MIN_BLOCKS) k_extend(DevScene
 		}
 		// nib[mask]: the nibbles of the slots in mask (layout.h: one nibble of valid-record bits per slot)
 		__shared__ uint32_t s_nib[256];
-		for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x) {
+		for (uint32_t i = threadIdx.x; i < 256u; i += 128u) {
 			uint32_t v = 0u;
 			for (uint32_t sl = 0; sl < 8u; ++sl)
 				if ((i >> sl) & 1u) v |= 7u << (4u * sl);

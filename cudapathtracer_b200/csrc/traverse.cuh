@@ -134,6 +134,14 @@ __device__ __forceinline__ float u8f_biased(uint32_t w, int j, uint32_t bias_bit
 #endif
 }
 
+// 1: the child tests of wide_node_step_fast with sm_100's packed fma.rn.f32x2 / add.rn.f32x2 (FFMA2 / FADD2): same bits, 28 fewer
+// instructions per node step — and 0.85 ms per config 2 frame SLOWER (34.35 against 33.50 ms of extend, same box, profiles/
+// r2_extend_variants.md): FFMA2 has the FMA pipe for twice as long as FFMA (tools/ffma2_probe.cu: 37.1 against 35.9 TFMA/s), so it
+// only saves issue slots, and the child test is bound by the ALU pipe (6 PRMT + 2 FMNMX3 + LOP3 + SHF per child), not by issue.
+#ifndef CUPT_NODE_F32X2
+#define CUPT_NODE_F32X2 0
+#endif
+
 // Per-ray traversal state of the wide BVH (registers).
 struct WideRay {
 	f3 o, d;
@@ -275,6 +283,43 @@ __device__ __forceinline__ void wide_node_step_fast(const uint4* __restrict__ no
 	const float ofx = bx + kx, ofy = by + ky, ofz = bz + kz;
 	const uint32_t imask = n0.w >> 24;
 	uint32_t miss = 0u;
+#if !defined(CUPT_HOST_EMUL) && CUPT_NODE_F32X2
+	// Packed evaluation (FFMA2 / FADD2): the near and the far plane of an axis share the scale, so one fma.rn.f32x2 per
+	// child and axis yields (-tnear, tfar) = (qn, qf) * (-s, s) + (-on, of) — the near distance NEGATED, so that
+	// -tmin = min3 of the negated near distances and both bounds come out of FMNMX3.min — and one add.rn.f32x2 per PAIR
+	// of children each yields (tmax_a - tmin_a, tmax_b - tmin_b) and (best - tmin_a, best - tmin_b).  Negation commutes
+	// with round-to-nearest, so every value is the scalar path's bit for bit (or its exact negative): 3 FFMA2 + 1 FADD2 per
+	// child instead of 6 FFMA + 2 FADD.
+	const f32x2 s2x = pack2(-sx, sx), s2y = pack2(-sy, sy), s2z = pack2(-sz, sz);
+	const f32x2 o2x = pack2(-onx, ofx), o2y = pack2(-ony, ofy), o2z = pack2(-onz, ofz);
+	const f32x2 best2 = pack2(r.best, r.best);
+#pragma unroll
+	for (int h = 1; h >= 0; --h) {   // slots 7..0, so that slot j ends up in bit j
+		const uint32_t qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
+		const uint32_t qhx = h ? n3.w : n3.z, qhy = h ? n4.y : n4.x, qhz = h ? n4.w : n4.z;
+		const uint32_t nx = negx ? qhx : qlx, fx = negx ? qlx : qhx;
+		const uint32_t ny = negy ? qhy : qly, fy = negy ? qly : qhy;
+		const uint32_t nz = negz ? qhz : qlz, fz = negz ? qlz : qhz;
+#pragma unroll
+		for (int j = 3; j >= 1; j -= 2) {   // children j and j - 1
+			float ntmin[2], tmax[2];
+#pragma unroll
+			for (int c = 0; c < 2; ++c) {
+				const int jj = j - c;
+				const f32x2 tx = ffma2(pack2(u8f_biased(nx, jj, bias_bits), u8f_biased(fx, jj, bias_bits)), s2x, o2x);
+				const f32x2 ty = ffma2(pack2(u8f_biased(ny, jj, bias_bits), u8f_biased(fy, jj, bias_bits)), s2y, o2y);
+				const f32x2 tz = ffma2(pack2(u8f_biased(nz, jj, bias_bits), u8f_biased(fz, jj, bias_bits)), s2z, o2z);
+				ntmin[c] = fminf(fminf(lo2(tx), lo2(ty)), lo2(tz));
+				tmax[c] = fminf(fminf(hi2(tx), hi2(ty)), hi2(tz));
+			}
+			const f32x2 nt2 = pack2(ntmin[0], ntmin[1]);
+			const f32x2 w2 = fadd2(pack2(tmax[0], tmax[1]), nt2);    // tmax - tmin
+			const f32x2 b2 = fadd2(best2, nt2);                      // best - tmin
+			miss = __funnelshift_l(__float_as_uint(lo2(w2)) | __float_as_uint(lo2(b2)) | __float_as_uint(tmax[0]), miss, 1);
+			miss = __funnelshift_l(__float_as_uint(hi2(w2)) | __float_as_uint(hi2(b2)) | __float_as_uint(tmax[1]), miss, 1);
+		}
+	}
+#else
 #pragma unroll
 	for (int h = 1; h >= 0; --h) {   // slots 7..0, so that slot j ends up in bit j
 		const uint32_t qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
@@ -292,6 +337,7 @@ __device__ __forceinline__ void wide_node_step_fast(const uint4* __restrict__ no
 			miss = __funnelshift_l(neg, miss, 1);
 		}
 	}
+#endif
 	const uint32_t inner = ~miss & imask;
 	const uint32_t leaf = ~miss & ~imask & 0xffu;   // (an empty slot has no valid bits)
 	ngroup = make_uint2(n1.x, ((uint32_t)perm[inner] << 24) | imask);

@@ -719,3 +719,4 @@ def test_last_segment_early_stop_changes_nothing(ctx, get_case, name):
     assert same.mean() >= 0.999, (name, same.mean())
     assert ra == rb > 0   # every ray is still traced, only some of them less far
     assert a.sum() > 0 and abs(float(a.sum()) - float(b.sum())) <= 1e-3 * float(a.sum())
+
