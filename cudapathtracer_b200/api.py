@@ -31,6 +31,7 @@ INTEGRATOR_PT, INTEGRATOR_BDPT = 2, 1
 TRAVERSAL_WIDE, TRAVERSAL_REF_BVH2, TRAVERSAL_WIDE_STRICT = 0, 1, 2
 TRI_REFEXACT, TRI_WATERTIGHT = 0, 1
 OBJ_FACE_MATERIALS, OBJ_DEDUP_MATERIALS = 1, 2
+NOALLOC_MAX_RAYS = 65536   # CUPT_NOALLOC_MAX_RAYS
 
 
 class CuptError(RuntimeError):
@@ -420,6 +421,17 @@ class Context:
         ids, ts = np.empty(len(rays), dtype=np.int32), np.empty(len(rays), dtype=np.float32)
         _check(self.lib.cupt_trace_rays(self.h, _ptr(rays), C.c_int64(len(rays)), _ptr(ids), _ptr(ts)))
         return ids, ts
+
+    def trace_rays_noalloc(self, rays: np.ndarray):
+        """cupt_trace_rays_noalloc on host arrays: same hits as trace_rays, no allocation inside the library (<= NOALLOC_MAX_RAYS rays)"""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        ids, ts = np.empty(len(rays), dtype=np.int32), np.empty(len(rays), dtype=np.float32)
+        _check(self.lib.cupt_trace_rays_noalloc(self.h, _ptr(rays), C.c_int64(len(rays)), _ptr(ids), _ptr(ts), 1))
+        return ids, ts
+
+    def trace_rays_noalloc_ptr(self, rays_ptr: int, n: int, ids_ptr: int, ts_ptr: int, synchronise: bool = True):
+        """the same on raw (host or device) addresses"""
+        _check(self.lib.cupt_trace_rays_noalloc(self.h, C.c_void_p(rays_ptr), C.c_int64(n), C.c_void_p(ids_ptr), C.c_void_p(ts_ptr), int(synchronise)))
 
     def stats(self) -> dict:
         s = Stats()

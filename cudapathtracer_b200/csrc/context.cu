@@ -1039,3 +1039,107 @@ int cupt_reset_stats(cupt_context* c)
 }
 
 }  // extern "C"
+
+// ---- closest hits for caller rays WITHOUT any allocation (cupt_trace_rays_noalloc) ----------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it).  cupt_trace_rays allocates its ray / hit staging
+// and, on first use, the path records and queues; this variant keeps all of that scratch in ONE file-scope device array of a
+// fixed size, which every GPU that loads the library holds until the process exits:
+//   rays6 [N x 24 B] | rayA [N x 16 B] | rayB [N x 16 B] | queue [N x 4 B] | ids [N x 4 B] | ts [N x 4 B] | counters [128 u32] | stats [8 u64]
+// with N = CUPT_NOALLOC_MAX_RAYS = 65 536: 4 457 472 + 576 bytes.  In HOST code the array's name is only a stand-in for the
+// symbol, not a device address, so the address is fetched once per device with cudaGetSymbolAddress (device current, return
+// code checked) and that pointer is what the kernels get; device code (k_noalloc_begin) names the array directly.
+// Every call shares the array, which keeps the last call's contents: the counters are cleared at the start of each call and
+// nothing else is read before it is written.  Two calls that overlap on the GPU (two contexts / streams on one device) race.
+#define CUPT_NOALLOC_OFF_RAYS6 ((size_t)0)
+#define CUPT_NOALLOC_OFF_RAYA (CUPT_NOALLOC_OFF_RAYS6 + (size_t)CUPT_NOALLOC_MAX_RAYS * 24)
+#define CUPT_NOALLOC_OFF_RAYB (CUPT_NOALLOC_OFF_RAYA + (size_t)CUPT_NOALLOC_MAX_RAYS * 16)
+#define CUPT_NOALLOC_OFF_QUEUE (CUPT_NOALLOC_OFF_RAYB + (size_t)CUPT_NOALLOC_MAX_RAYS * 16)
+#define CUPT_NOALLOC_OFF_IDS (CUPT_NOALLOC_OFF_QUEUE + (size_t)CUPT_NOALLOC_MAX_RAYS * 4)
+#define CUPT_NOALLOC_OFF_TS (CUPT_NOALLOC_OFF_IDS + (size_t)CUPT_NOALLOC_MAX_RAYS * 4)
+#define CUPT_NOALLOC_OFF_COUNTERS (CUPT_NOALLOC_OFF_TS + (size_t)CUPT_NOALLOC_MAX_RAYS * 4)
+#define CUPT_NOALLOC_OFF_STATS (CUPT_NOALLOC_OFF_COUNTERS + 128 * sizeof(uint32_t))
+#define CUPT_NOALLOC_BYTES (CUPT_NOALLOC_OFF_STATS + 8 * sizeof(unsigned long long))
+static __device__ __align__(256) unsigned char g_noalloc_scratch[CUPT_NOALLOC_BYTES];
+
+// queue sizes / fetch cursors of this call: counters[0] = n, everything else 0 (the array keeps the previous call's values)
+static __global__ void __launch_bounds__(128) k_noalloc_begin(uint32_t n)
+{
+	uint32_t* counters = reinterpret_cast<uint32_t*>(g_noalloc_scratch + CUPT_NOALLOC_OFF_COUNTERS);
+	counters[threadIdx.x] = threadIdx.x == 0u ? n : 0u;
+	if (threadIdx.x < 8u) reinterpret_cast<unsigned long long*>(g_noalloc_scratch + CUPT_NOALLOC_OFF_STATS)[threadIdx.x] = 0ull;
+}
+
+namespace {
+struct NoAllocDevice {
+	unsigned char* base = nullptr;      // device address of g_noalloc_scratch on this device (cudaGetSymbolAddress)
+	int blocks[2] = {0, 0};             // persistent grid of k_extend<mode, false, false>
+	size_t smem[2] = {0, 0};            // the dynamic shared memory the grid was sized for
+};
+constexpr int kNoAllocMaxDevices = 64;
+NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+}  // namespace
+
+extern "C" {
+
+int cupt_trace_rays_noalloc(cupt_context* c, const float* rays, int64_t n, int32_t* tri_id, float* t, int synchronise)
+{
+	if (!c || n < 0 || (n > 0 && (!rays || !tri_id || !t))) return set_error(CUPT_ERR_INVALID, "bad arguments");
+	if (n > CUPT_NOALLOC_MAX_RAYS)
+		return set_error(CUPT_ERR_LIMIT, "cupt_trace_rays_noalloc: %lld rays exceed the fixed scratch of CUPT_NOALLOC_MAX_RAYS = %d rays per call "
+		                 "(split the batch, or use cupt_trace_rays, which allocates)", (long long)n, CUPT_NOALLOC_MAX_RAYS);
+	if (c->opts.traversal == CUPT_TRAVERSAL_WIDE_STRICT)
+		return set_error(CUPT_ERR_INVALID, "cupt_trace_rays_noalloc: the strict mode needs a re-trace list that is allocated on demand; use CUPT_TRAVERSAL_WIDE or CUPT_TRAVERSAL_REF_BVH2");
+	if (c->opts.tri_test != CUPT_TRI_REFEXACT)
+		return set_error(CUPT_ERR_INVALID, "cupt_trace_rays_noalloc: CUPT_TRI_WATERTIGHT builds its vertex records on demand; use CUPT_TRI_REFEXACT");
+	{ const int rc0 = check_ready(c, false, false); if (rc0) return rc0; }   // (allocates nothing with the reference-exact triangle test)
+	if (c->device >= kNoAllocMaxDevices) return set_error(CUPT_ERR_LIMIT, "device index %d beyond %d", c->device, kNoAllocMaxDevices);
+	CK(cudaSetDevice(c->device));
+	NoAllocDevice& nd = g_noalloc_dev[c->device];
+	if (!nd.base) {   // once per device, with that device current
+		unsigned char* ptr = nullptr;
+		CK(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+		if (!ptr) return set_error(CUPT_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the scratch array");
+		nd.base = ptr;
+	}
+	if (n == 0) return CUPT_OK;
+	const uint32_t m = (uint32_t)n;
+	PathBuffers pb{};
+	pb.rayA = reinterpret_cast<float4*>(nd.base + CUPT_NOALLOC_OFF_RAYA);
+	pb.rayB = reinterpret_cast<float4*>(nd.base + CUPT_NOALLOC_OFF_RAYB);
+	pb.queue[0] = pb.queue[1] = reinterpret_cast<uint32_t*>(nd.base + CUPT_NOALLOC_OFF_QUEUE);
+	pb.counters = reinterpret_cast<uint32_t*>(nd.base + CUPT_NOALLOC_OFF_COUNTERS);
+	pb.stats = reinterpret_cast<unsigned long long*>(nd.base + CUPT_NOALLOC_OFF_STATS);
+	float* d_rays = reinterpret_cast<float*>(nd.base + CUPT_NOALLOC_OFF_RAYS6);
+	int32_t* d_ids = reinterpret_cast<int32_t*>(nd.base + CUPT_NOALLOC_OFF_IDS);
+	float* d_t = reinterpret_cast<float*>(nd.base + CUPT_NOALLOC_OFF_TS);
+	const DevScene sc = make_scene(c);
+	const int mode = c->opts.traversal == CUPT_TRAVERSAL_REF_BVH2 ? 1 : 0;
+	const size_t smem = mode == 0 ? (size_t)sc.stack_cap * 128 * sizeof(uint2) + 128 * 16 : 0;
+	void (*kern)(DevScene, PathBuffers, int, int, ExtendTuning) = mode == 0 ? k_extend<0, false, false> : k_extend<1, false, false>;
+	if (nd.blocks[mode] == 0 || nd.smem[mode] != smem) {
+		if (smem > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		int per_sm = 0;
+		CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+		if (per_sm < 1) return set_error(CUPT_ERR_LIMIT, "the extend kernel does not fit an SM with a traversal stack of %d entries", sc.stack_cap);
+		nd.blocks[mode] = per_sm * c->num_sms; nd.smem[mode] = smem;
+	}
+	ExtendTuning tune;
+	tune.fetch_thresh = c->opts.fetch_threshold > 0 ? std::min(c->opts.fetch_threshold, 31) : 24;
+	tune.defer_pairs = c->opts.defer_pairs > 0 ? std::min(c->opts.defer_pairs, 64) : 16;
+	tune.qbias_bits = CUPT_QBIAS_BITS;
+	// the caller's pointers may be host or device memory (unified addressing decides); device pointers involve no host staging
+	CK(cudaMemcpyAsync(d_rays, rays, (size_t)m * 6 * sizeof(float), cudaMemcpyDefault, c->stream));
+	k_noalloc_begin<<<1, 128, 0, c->stream>>>(m);
+	k_load_rays<<<(m + 255) / 256, 256, 0, c->stream>>>(d_rays, m, 0u, pb);
+	kern<<<nd.blocks[mode], 128, smem, c->stream>>>(sc, pb, 0, 0, tune);
+	k_store_hits<<<(m + 255) / 256, 256, 0, c->stream>>>(m, 0u, pb, d_ids, d_t);
+	CK(cudaGetLastError());
+	c->launches += 4; c->extend_launches++;
+	CK(cudaMemcpyAsync(tri_id, d_ids, (size_t)m * sizeof(int32_t), cudaMemcpyDefault, c->stream));
+	CK(cudaMemcpyAsync(t, d_t, (size_t)m * sizeof(float), cudaMemcpyDefault, c->stream));
+	if (synchronise) CK(cudaStreamSynchronize(c->stream));
+	return CUPT_OK;
+}
+
+}  // extern "C"

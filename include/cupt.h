@@ -230,6 +230,20 @@ int cupt_add_accum_device(cupt_context* c, const float* src_device, int samples)
 int cupt_read_primary_hits(cupt_context* c, int32_t* tri_id, float* t);
 int cupt_trace_rays(cupt_context* c, const float* rays_host /* n*6: o, dir */, int64_t n, int32_t* tri_id, float* t);
 int cupt_camera_rays(cupt_context* c, float* rays_host /* P*6 */);
+/* cupt_trace_rays without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as cupt_trace_rays bit for bit.  All scratch (ray / hit staging, path records, queue, counters) lives in one
+ * file-scope device array of CUPT_NOALLOC_MAX_RAYS * 68 + 576 bytes (about 4.3 MiB) that every GPU which loads the library
+ * holds until the process exits; the call performs no cudaMalloc / cudaFree / allocating library call.
+ *   rays, tri_id, t   host OR device pointers (n*6 floats in, n ids and n distances out); with device pointers nothing is
+ *                     staged through the host
+ *   n                 0 .. CUPT_NOALLOC_MAX_RAYS; more is refused with CUPT_ERR_LIMIT (split the batch)
+ *   synchronise       != 0: wait for the context's stream before returning (needed before reading host outputs)
+ * CUPT_TRAVERSAL_WIDE or CUPT_TRAVERSAL_REF_BVH2 with CUPT_TRI_REFEXACT (the strict mode and the watertight test allocate on
+ * demand and are refused).  The array is shared by every call on a device and keeps the last call's contents (what must start
+ * at zero is cleared by the call): calls that OVERLAP on one GPU — two contexts or two streams — race; serialise them. */
+#define CUPT_NOALLOC_MAX_RAYS 65536
+int cupt_trace_rays_noalloc(cupt_context* c, const float* rays, int64_t n, int32_t* tri_id, float* t, int synchronise);
 /* parity hook (record_retraces): per pixel, row-major, how many rays of the paths rendered since cupt_reset_accum had a
  * wide-BVH hit the reference's trace() would not have reached (BVH.h:65,79: its slab test is not conservative) and
  * were therefore re-traced.  Pixels with 0 carry paths on which the plain wide mode and the reference agree ray by ray. */
