@@ -39,7 +39,7 @@ class CuptError(RuntimeError):
 
 
 class BvhOpts(C.Structure):
-    _fields_ = [("sah_bins", C.c_int), ("max_leaf_tris", C.c_int), ("threads", C.c_int), ("tie_rank", C.c_void_p), ("ploc_radius", C.c_int), ("greedy_collapse", C.c_int)]
+    _fields_ = [("sah_bins", C.c_int), ("max_leaf_tris", C.c_int), ("threads", C.c_int), ("tie_rank", C.c_void_p), ("ploc_radius", C.c_int), ("reinsert_passes", C.c_int), ("greedy_collapse", C.c_int)]
 
 
 class BvhInfo(C.Structure):
@@ -222,8 +222,8 @@ class SceneHandle:
             self.lib.cupt_bvh2_free(p)
         return nodes, depth.value
 
-    def build_bvh(self, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None, greedy_collapse=False) -> "BvhHandle":
-        return BvhHandle(self, sah_bins, max_leaf_tris, threads, tie_rank, greedy_collapse)
+    def build_bvh(self, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None, greedy_collapse=False, reinsert_passes=0) -> "BvhHandle":
+        return BvhHandle(self, sah_bins, max_leaf_tris, threads, tie_rank, greedy_collapse, reinsert_passes)
 
 
 def bvh2_leaf_order(nodes: np.ndarray, ntris: int) -> np.ndarray:
@@ -243,11 +243,11 @@ assert NODE8.itemsize == 80 and PRIM48.itemsize == 48
 class BvhHandle:
     """cupt_bvh: host image of the 8-wide quantised BVH (replaces buildBVH, BVH.h:443-474)."""
 
-    def __init__(self, scene: SceneHandle, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None, greedy_collapse=False):
+    def __init__(self, scene: SceneHandle, sah_bins=0, max_leaf_tris=0, threads=0, tie_rank: Optional[np.ndarray] = None, greedy_collapse=False, reinsert_passes=0):
         self.h = None
         self.lib = load_library()
         self._rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, dtype=np.uint32)
-        opts = BvhOpts(sah_bins, max_leaf_tris, threads, None if self._rank is None else self._rank.ctypes.data, 0, int(greedy_collapse))
+        opts = BvhOpts(sah_bins, max_leaf_tris, threads, None if self._rank is None else self._rank.ctypes.data, 0, int(reinsert_passes), int(greedy_collapse))
         h = C.c_void_p()
         _check(self.lib.cupt_bvh_build(scene.h, C.byref(opts), C.byref(h)))
         self.h = h
@@ -305,7 +305,7 @@ class Context:
     def build_bvh_device(self, max_leaf_tris=0, tie_rank: Optional[np.ndarray] = None, radius=0) -> dict:
         """cupt_build_bvh_device: wide BVH built on the GPU from the uploaded scene (replaces buildBVH + its upload)"""
         rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, dtype=np.uint32)
-        opts = BvhOpts(0, max_leaf_tris, 0, None if rank is None else rank.ctypes.data, radius)
+        opts = BvhOpts(0, max_leaf_tris, 0, None if rank is None else rank.ctypes.data, radius, 0, 0)
         i = BvhInfo()
         _check(self.lib.cupt_build_bvh_device(self.h, C.byref(opts), C.byref(i)))
         d = {n: getattr(i, n) for n, _ in BvhInfo._fields_}

@@ -8,6 +8,7 @@
 #include <cstdint>
 #include <cstring>
 #include <vector>
+#include <algorithm>
 #include <cuda_runtime.h>
 #undef __device__
 #undef __forceinline__
@@ -79,6 +80,64 @@ extern "C" int emul_trace_wide_fast(const void* nodes80, const void* prims48, in
 		nn += a; nt += b;
 	}
 	if (counts) { counts[0] = nn; counts[1] = nt; }
+	return 0;
+}
+
+// the loop of traverse_wide_fast once more, counting the node steps that find NOTHING (no inner child and no leaf record hit):
+// counts = {node steps, primitive tests, empty node steps, node steps in nodes that CONTAIN the ray origin, empty ones among those}
+extern "C" int emul_trace_wide_count_empty(const void* nodes80, const void* prims48, int depth, const float* rays6, long long n, unsigned long long* counts)
+{
+	std::vector<uint8_t> perm(8 * 256);
+	std::vector<uint32_t> nib(256);
+	for (uint32_t i = 0; i < 8u * 256u; ++i) { uint32_t v = 0u; for (uint32_t sl = 0; sl < 8u; ++sl) if ((i >> sl) & 1u) v |= 1u << (sl ^ (i >> 8)); perm[i] = (uint8_t)v; }
+	for (uint32_t i = 0; i < 256u; ++i) { uint32_t v = 0u; for (uint32_t sl = 0; sl < 8u; ++sl) if ((i >> sl) & 1u) v |= 7u << (4u * sl); nib[i] = v; }
+	unsigned long long nn = 0, nt = 0, ne = 0, no = 0, neo = 0;
+#pragma omp parallel for schedule(dynamic, 256) reduction(+ : nn, nt, ne, no, neo)
+	for (long long i = 0; i < n; ++i) {
+		std::vector<uint2> stack((size_t)depth + 1);
+		WideRay r;
+		wide_ray_init(r, mk3(rays6[6 * i], rays6[6 * i + 1], rays6[6 * i + 2]), mk3(rays6[6 * i + 3], rays6[6 * i + 4], rays6[6 * i + 5]));
+		uint2 ngroup = make_uint2(0u, 0x80000000u);
+		int sp = 0;
+		for (;;) {
+			uint2 rest, tgroup;
+			// which node will this step fetch (same arithmetic as the step): is the ray's ORIGIN inside the union of its child boxes?
+			bool inside;
+			{
+				const uint32_t hits = ngroup.y, bit = 31u - __clz(hits), slot = (bit - 24u) ^ r.oct_inv;
+				const uint32_t rel = __popc(hits & 0xffu & ~(0xffffffffu << slot));
+				const Node8& nd = ((const Node8*)nodes80)[ngroup.x + rel];
+				const float o3[3] = {r.o.x, r.o.y, r.o.z};
+				inside = true;
+				for (int a = 0; a < 3; ++a) {
+					int lo = 255, hi = 0;
+					for (int sl = 0; sl < 8; ++sl) if (((nd.imask >> sl) & 1u) || ((nd.pvalid >> (4 * sl)) & 7u)) { lo = std::min(lo, (int)nd.qlo[a][sl]); hi = std::max(hi, (int)nd.qhi[a][sl]); }
+					const float sc = __uint_as_float((uint32_t)nd.e[a] << 23);
+					if (o3[a] < nd.p[a] + lo * sc - 1e-3f || o3[a] > nd.p[a] + hi * sc + 1e-3f) inside = false;
+				}
+			}
+			wide_node_step_fast((const uint4*)nodes80, r, ngroup, rest, tgroup, CUPT_QBIAS_BITS, perm.data() + (r.oct_inv << 8), nib.data());
+			if (group_has_node(rest)) stack[(size_t)sp++] = rest;
+			++nn;
+			if (inside) ++no;
+			if (!group_has_node(ngroup) && tgroup.y == 0u) { ++ne; if (inside) ++neo; }
+			if (tgroup.y != 0u) {
+				const uint2 tv = node_records((const uint4*)nodes80, tgroup.x);
+				while (tgroup.y != 0u) {
+					const uint32_t k = __ffs(tgroup.y) - 1u;
+					tgroup.y &= tgroup.y - 1u;
+					uint2 one = make_uint2(sparse_record(tv, k), 1u);
+					wide_prim_step((const float4*)prims48, r, one);
+					++nt;
+				}
+			}
+			if (!group_has_node(ngroup)) {
+				if (sp == 0) break;
+				ngroup = stack[(size_t)--sp];
+			}
+		}
+	}
+	counts[0] = nn; counts[1] = nt; counts[2] = ne; counts[3] = no; counts[4] = neo;
 	return 0;
 }
 

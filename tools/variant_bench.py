@@ -14,7 +14,7 @@ def main():
     sc = scenes.atrium(262144)
     s = api.SceneHandle(); s.add_scene(sc)
     n2, d2 = s.build_bvh2()
-    b = s.build_bvh(tie_rank=api.bvh2_leaf_order(n2, s.counts()[1]))
+    b = s.build_bvh(tie_rank=api.bvh2_leaf_order(n2, s.counts()[1]), reinsert_passes=int(os.environ.get("REINSERT", "0")), sah_bins=int(os.environ.get("BINS", "0")))
     ctx = api.Context(0)
     ctx.set_scene(s); ctx.set_bvh(b); ctx.set_camera(api.make_camera(1024, 1024, **sc.camera))
     ctx.set_options(max_depth=5, seed=1234, traversal=api.TRAVERSAL_WIDE, time_stages=1, collect_stats=0)
