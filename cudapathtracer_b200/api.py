@@ -442,6 +442,131 @@ class Context:
         _check(self.lib.cupt_reset_stats(self.h))
 
 
+class _BorrowedContext(Context):
+    """a group member's context: owned (and destroyed) by the group"""
+
+    def __init__(self, handle, cam):
+        self.h, self.lib, self.opts, self._cam = handle, load_library(), RenderOpts(), cam
+        _check(self.lib.cupt_default_render_opts(C.byref(self.opts)))
+
+    def close(self):
+        self.h = None
+
+    __del__ = close
+
+
+def group_unique_id() -> bytes:
+    buf = C.create_string_buffer(128)
+    _check(load_library().cupt_group_unique_id(buf))
+    return buf.raw
+
+
+class Group:
+    """cupt_group: several GPUs behind one handle.  Group(devices=[0, 1, ...]) drives every member from this process (one
+    host thread per GPU); Group(device=d, rank=r, nranks=n, unique_id=id) is this process's member of an n-process group."""
+
+    def __init__(self, devices=None, device=None, rank=None, nranks=None, unique_id=None):
+        self.h = None
+        self.lib = load_library()
+        self.lib.cupt_group_context.restype = C.c_void_p
+        self.lib.cupt_group_context.argtypes = [C.c_void_p, C.c_int]
+        self.lib.cupt_group_destroy.restype = None
+        self.lib.cupt_group_destroy.argtypes = [C.c_void_p]
+        h = C.c_void_p()
+        if devices is not None:
+            arr = (C.c_int * len(devices))(*devices)
+            _check(self.lib.cupt_group_create_local(arr, len(devices), C.byref(h)))
+        else:
+            _check(self.lib.cupt_group_create_rank(int(device), int(rank), int(nranks), C.c_char_p(unique_id), C.byref(h)))
+        self.h = h
+        self.opts = RenderOpts()
+        _check(self.lib.cupt_default_render_opts(C.byref(self.opts)))
+        self._cam = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.cupt_group_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def info(self):
+        out = (C.c_int * 3)()
+        _check(self.lib.cupt_group_info(self.h, out))
+        return {"nranks": out[0], "nlocal": out[1], "first_rank": out[2]}
+
+    def context(self, local_index: int) -> Context:
+        p = self.lib.cupt_group_context(self.h, local_index)
+        if not p:
+            _check(-1)
+        return _BorrowedContext(C.c_void_p(p), self._cam)
+
+    def set_scene(self, scene: Optional[SceneHandle]):
+        _check(self.lib.cupt_group_set_scene(self.h, None if scene is None else scene.h))
+
+    def set_bvh(self, bvh: Optional[BvhHandle]):
+        _check(self.lib.cupt_group_set_bvh(self.h, None if bvh is None else bvh.h))
+
+    def build_bvh_device(self, max_leaf_tris=0, tie_rank: Optional[np.ndarray] = None, radius=0) -> dict:
+        rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, dtype=np.uint32)
+        opts = BvhOpts(0, max_leaf_tris, 0, None if rank is None else rank.ctypes.data, radius, 0, 0)
+        i = BvhInfo()
+        _check(self.lib.cupt_group_build_bvh_device(self.h, C.byref(opts), C.byref(i)))
+        return {n: getattr(i, n) for n, _ in BvhInfo._fields_}
+
+    def set_bvh2(self, nodes: Optional[np.ndarray], depth: int = 0):
+        if nodes is None:
+            _check(self.lib.cupt_group_set_bvh2(self.h, None, 0, 0))
+            return
+        nodes = np.ascontiguousarray(nodes, dtype=BVH2_NODE)
+        _check(self.lib.cupt_group_set_bvh2(self.h, _ptr(nodes), len(nodes), depth))
+
+    def set_camera(self, cam: np.ndarray):
+        self._cam = np.ascontiguousarray(cam, dtype=CAMERA)
+        _check(self.lib.cupt_group_set_camera(self.h, _ptr(self._cam)))
+
+    def set_options(self, **kw):
+        for k, v in kw.items():
+            if not hasattr(self.opts, k):
+                raise AttributeError(k)
+            setattr(self.opts, k, v)
+        _check(self.lib.cupt_group_set_render_opts(self.h, C.byref(self.opts)))
+
+    def reset_accum(self):
+        _check(self.lib.cupt_group_reset_accum(self.h))
+
+    def render(self, first_sample: int, num_samples: int):
+        _check(self.lib.cupt_group_render(self.h, first_sample, num_samples))
+
+    def sync(self):
+        _check(self.lib.cupt_group_sync(self.h))
+
+    def read_accum(self, normalise: bool = True, out: Optional[np.ndarray] = None):
+        """the image from rank 0; None on a process that does not hold rank 0"""
+        h, w = int(self._cam["pxlHeight"][0]), int(self._cam["pxlWidth"][0])
+        if out is None:
+            out = np.empty((h * w, 3), dtype=np.float32)
+        rc = self.lib.cupt_group_read_accum(self.h, _ptr(out), int(normalise))
+        if rc == 1:
+            return None
+        _check(rc)
+        return out
+
+    def read_image_rgb8(self, mirror_x: bool = False):
+        h, w = int(self._cam["pxlHeight"][0]), int(self._cam["pxlWidth"][0])
+        out = np.empty((h, w, 3), dtype=np.uint8)
+        rc = self.lib.cupt_group_read_image_rgb8(self.h, _ptr(out), int(mirror_x))
+        if rc == 1:
+            return None
+        _check(rc)
+        return out
+
+    def stats(self) -> dict:
+        s = Stats()
+        _check(self.lib.cupt_group_get_stats(self.h, C.byref(s)))
+        return s.as_dict()
+
+
 def write_ppm(path: str, rgb_mean: np.ndarray, width: int, height: int):
     """kernel.cu:763-778"""
     rgb_mean = np.ascontiguousarray(rgb_mean, dtype=np.float32)

@@ -51,6 +51,7 @@ struct cupt_context {
 	double ms[4] = {0, 0, 0, 0};
 	std::vector<StageEvent> pending, pool;
 	std::map<void**, size_t> capacity;   // bytes behind each uploaded device pointer (upload())
+	std::map<void**, size_t> used;       // bytes of it that the last upload filled (what a group broadcasts, group.cuh)
 	// persistent grid of the extend stage per kernel instantiation (mode, stats, vis): blocks, and the dynamic shared memory it was sized for
 	int extend_blocks[2][2][2] = {}; size_t extend_smem[2][2][2] = {};
 	uint32_t* d_retrace_counts = nullptr; size_t retrace_pixels = 0;   // cupt_render_opts.record_retraces
@@ -126,6 +127,7 @@ template <class T>
 int ensure_device(cupt_context* c, T** dst, size_t bytes)
 {
 	size_t& cap = c->capacity[(void**)dst];
+	c->used[(void**)dst] = bytes;
 	if (bytes > cap || !*dst) {
 		if (*dst) { CK(cudaFree(*dst)); *dst = nullptr; cap = 0; }
 		if (bytes == 0) return CUPT_OK;
@@ -1143,3 +1145,5 @@ int cupt_trace_rays_noalloc(cupt_context* c, const float* rays, int64_t n, int32
 }
 
 }  // extern "C"
+
+#include "group.cuh"

@@ -265,6 +265,43 @@ typedef struct cupt_stats {
 int cupt_get_stats(cupt_context* c, cupt_stats* out);
 int cupt_reset_stats(cupt_context* c);
 
+/* ---- several GPUs — replaces the single-device loop (kernel.cu:569 `cudaGetDeviceProperties(&p, 0)`, kernel.cu:709-736) -----
+ * A group is one context per GPU, one host thread per context and an NCCL communicator owned by the group (SURVEY 8b
+ * "Threading").  The scene and the BVH are staged through host memory once, on rank 0, and reach the other members by
+ * ncclBroadcast over NVLink; cupt_group_render gives member r the r-th of N contiguous sample ranges of every pixel (disjoint
+ * Philox sample indices, replicated BVH) and sums the f32 accumulators onto rank 0 with one ncclReduce — the path's only
+ * exchange step; the image is read from rank 0.  NCCL (libnccl.so.2) is dlopen()ed by the first group call: a process that
+ * makes no group does not need it.
+ *   cupt_group_create_local   all members are threads of this process (devices[i] = CUDA device of rank i)
+ *   cupt_group_create_rank    this process drives ONE member of an nranks-wide group (one process per GPU: torchrun, MPI);
+ *                             id128 = the 128 bytes cupt_group_unique_id wrote on one process, distributed by the caller
+ * Group calls are collective: every process of the group makes the same calls in the same order.  A call that fails on one
+ * process only (e.g. out of memory) can leave the others waiting in NCCL, as with any collective. */
+typedef struct cupt_group cupt_group;
+int cupt_group_unique_id(void* id128);
+int cupt_group_create_local(const int* devices, int n, cupt_group** out);
+int cupt_group_create_rank(int device, int rank, int nranks, const void* id128, cupt_group** out);
+void cupt_group_destroy(cupt_group* g);
+int cupt_group_info(const cupt_group* g, int* out3 /* members in the group, members driven by this process, rank of the first of those */);
+cupt_context* cupt_group_context(cupt_group* g, int local_index);   /* a member's context, for per-context calls (stats, hooks) between group calls */
+/* cupt_set_scene / cupt_set_bvh / cupt_build_bvh_device / cupt_set_bvh2 on rank 0, then broadcast; processes that do not hold
+ * rank 0 may pass NULL for the scene / BVH / nodes */
+int cupt_group_set_scene(cupt_group* g, const cupt_scene* s);
+int cupt_group_set_bvh(cupt_group* g, const cupt_bvh* b);
+int cupt_group_build_bvh_device(cupt_group* g, const cupt_bvh_opts* opts, cupt_bvh_info* info);
+int cupt_group_set_bvh2(cupt_group* g, const cupt_bvh2_node* nodes, int size, int depth);
+int cupt_group_set_camera(cupt_group* g, const cupt_camera* cam);            /* the same camera on every member */
+int cupt_group_set_render_opts(cupt_group* g, const cupt_render_opts* o);
+int cupt_group_reset_accum(cupt_group* g);
+/* samples [first_sample, first_sample + num_samples) of every pixel, split over the members; asynchronous.  Afterwards rank 0's
+ * accumulator holds the sum of everything rendered since cupt_group_reset_accum and the other members' are zero. */
+int cupt_group_render(cupt_group* g, int first_sample, int num_samples);
+int cupt_group_sync(cupt_group* g);
+/* the image, from rank 0 (cupt_read_accum / cupt_read_image_rgb8).  Returns 1 and writes nothing on a process that does not hold rank 0. */
+int cupt_group_read_accum(cupt_group* g, float* rgb_host, int normalise);
+int cupt_group_read_image_rgb8(cupt_group* g, uint8_t* rgb, int mirror_x);
+int cupt_group_get_stats(cupt_group* g, cupt_stats* out);                    /* counters summed (stage times: max) over this process's members */
+
 /* ---- output — kernel.cu:763-778 ------------------------------------------------------------------ */
 /* P3 PPM: x mirrored, Reinhard c/(c+1) (color.h:59-62), gamma 1/2.2 (color.h:68-71), (int)(c*255) truncation */
 int cupt_write_ppm(const char* path, const float* rgb_mean, int width, int height);

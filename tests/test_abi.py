@@ -93,3 +93,19 @@ def test_product_never_touches_the_oracle():
                     if re.search(r"liboracle|oraclebind|refbind|libcupt_ref|oracle/oracle\.c", t):
                         bad.append(os.path.join(dp, f))
     assert not bad, bad
+
+
+def test_compat_shim_compiles_against_the_reference_headers(lib):
+    """include/cupt_compat.h + examples/reference_main.cpp (loadOBJ, buildBVH, the camera POD, MAX_BVH_DEPTH, the reference's
+    color functions in the PPM writer) compile with a plain host compiler against the reference's OWN vec3.h / color.h /
+    camera.h.  Built by __graft_entry__.build() where /root/reference exists; run on the GPU by test_gpu_parity."""
+    import os
+    if not os.path.isdir("/root/reference"):
+        pytest.skip("no reference tree on this machine")
+    import __graft_entry__
+    __graft_entry__.build()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    assert os.path.exists(os.path.join(root, "examples", "reference_main"))
+    text = open(os.path.join(root, "include", "cupt_compat.h")).read()
+    for name in ("loadOBJ", "buildBVH", "BVH_array", "materialDesc", "totalLightArea"):
+        assert name in text

@@ -333,6 +333,27 @@ def test_native_render_loop_example(ctx, lib, tmp_path):
     ctx.set_options(traversal=api.TRAVERSAL_WIDE)
 
 
+def test_reference_style_main_over_the_compat_shim(ctx, lib, tmp_path):
+    """examples/reference_main.cpp — the reference's main() shape (loadOBJ with its hard-coded "models/" MTL path, buildBVH,
+    camera, depth guard, NUM_SAMPLES - 1 samples, the PPM written with the reference's own normalized / gammaCorrect) over
+    include/cupt_compat.h — writes the same PPM, byte for byte, as examples/render_loop on the same scene."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe, exe2 = os.path.join(root, "examples", "reference_main"), os.path.join(root, "examples", "render_loop")
+    if not os.path.exists(exe):
+        pytest.skip("examples/reference_main is built where the reference's headers are (the container), and travels with the snapshot")
+    sc = scenes.cornell_box()
+    obj, mtl = scenes.to_obj(sc)
+    (tmp_path / "models").mkdir()
+    (tmp_path / "models" / "CornellBox-Original.obj").write_text(obj)
+    (tmp_path / "models" / "scene.mtl").write_text(mtl)
+    r = subprocess.run([exe, "models/CornellBox-Original.obj", "64", "48", "9", "shim.ppm"], cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert r.returncode == 0 and "32 tris" in r.stdout and "bvh size 31" in r.stdout, r.stdout
+    r2 = subprocess.run([exe2, "models/CornellBox-Original.obj", "models/", "64", "48", "8", "3", "loop.ppm", "wide"], cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert r2.returncode == 0, r2.stdout
+    assert (tmp_path / "shim.ppm").read_bytes() == (tmp_path / "loop.ppm").read_bytes()
+
+
 @pytest.mark.parametrize("name", CASES)
 def test_bdpt_live_integrator_vs_oracle_and_golden(ctx, get_case, name):
     """CUPT_INTEGRATOR_BDPT = radianceAlongSingleStep (kernel.cu:217-415), what drawPixel calls at HEAD, as three

@@ -52,3 +52,18 @@ def test_reduce_of_accumulators_gloo_world2(tmp_path):
     got = np.load(out)
     want = np.arange(18, dtype=np.float32) * sum(range(1, 11)) / 10.0
     assert np.allclose(got, want)
+
+
+def test_group_needs_a_gpu(lib):
+    """cupt_group is the native multi-GPU path (NCCL owned by the library): without a CUDA device it fails loudly, like
+    cupt_create — there is no CPU stand-in"""
+    import ctypes as C
+    from cudapathtracer_b200 import api
+    try:
+        n = C.c_int(0)
+        if C.CDLL("libcudart.so.12").cudaGetDeviceCount(C.byref(n)) == 0 and n.value > 0:
+            pytest.skip("a GPU is present")
+    except OSError:
+        pass
+    with pytest.raises(api.CuptError):
+        api.Group(devices=[0])
