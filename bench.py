@@ -257,7 +257,7 @@ def multi_gpu_check(ctx, api, sharding, dist, torch, rank, world, ranges, accum_
     return out
 
 
-def strong_record(ctx, api, sharding, dist, torch, s, bvh, sc, rank, world, stream, steps):
+def strong_record(ctx, api, sharding, dist, torch, s, bvh, sc, rank, world, stream, steps, group=None):
     """BASELINE config 3's frame (3840x2160) with a FIXED total of STRONG_SPP samples split over the ranks by sample
     ranges: device ms (CUDA events, max over ranks) and e2e ms (host buffers: scene + BVH H2D on every rank, render,
     NCCL reduce, image D2H on rank 0)."""
@@ -275,6 +275,14 @@ def strong_record(ctx, api, sharding, dist, torch, s, bvh, sc, rank, world, stre
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
 
     def e2e_step():
+        if group is not None:   # the public multi-GPU API: scene + BVH staged on rank 0 and broadcast, one ncclReduce, image read on rank 0
+            group.set_scene(s if rank == 0 else None); group.set_camera(cam); group.set_bvh(bvh if rank == 0 else None)
+            group.reset_accum(); group.render(0, STRONG_SPP)
+            if rank == 0:
+                group.read_accum(False, out=host_t.numpy())
+            else:
+                group.sync()
+            return
         ctx.set_scene(s); ctx.set_camera(cam); ctx.set_bvh(bvh)
         ctx.reset_accum(); ctx.render(first, n)
         if world > 1:
@@ -459,7 +467,35 @@ def main():
         h2d += len(n2) * 32 * 2 + nt * 4                                   # reference-layout tree, its parent-linked copy, leaf parents
     d2h = W * H * 12
 
+    # N > 1: the public multi-GPU API, cupt_group (one member per process here, torchrun's shape): the scene and the BVH are staged
+    # through host memory on rank 0 only and reach the other ranks by ncclBroadcast; one ncclReduce; the image is read on rank 0
+    group = None
+    if world > 1 and args.partition == "samples":
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(api.group_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, src=0)
+        group = api.Group(device=local, rank=rank, nranks=world, unique_id=bytes(uid.cpu().numpy().tobytes()))
+        group.set_options(max_depth=DEPTH, seed=SEED, traversal=mode, integrator=api.INTEGRATOR_BDPT if args.integrator == "bdpt" else api.INTEGRATOR_PT,
+                          tri_test=api.TRI_WATERTIGHT if args.tri_test == "watertight" else api.TRI_REFEXACT, share_primary_hits=int(args.share_primary))
+    e2e_total_spp = SPP if args.config == 3 else SPP * world
+
     def e2e_step():
+        if group is not None:
+            root = rank == 0
+            group.set_scene(s if root else None); group.set_camera(cam)
+            if args.bvh == "device":
+                group.build_bvh_device(tie_rank=dev_rank)
+            else:
+                group.set_bvh(bvh if root else None)
+            if mode != api.TRAVERSAL_WIDE:
+                group.set_bvh2(n2 if root else None, d2)
+            group.reset_accum(); group.render(0, e2e_total_spp)
+            if root:
+                group.read_accum(False, out=host_img)
+            else:
+                group.sync()
+            return
         ctx.set_scene(s); ctx.set_camera(cam)
         if args.bvh == "device":
             ctx.build_bvh_device(tie_rank=dev_rank)      # the build itself is inside the e2e step
@@ -495,7 +531,7 @@ def main():
         mgc = multi_gpu_check(ctx, api, sharding, dist, torch, rank, world, ranges, accum_t, W, H)
     strong = None
     if args.config == 2 and plain and not args.no_strong and args.bvh == "host":
-        strong = strong_record(ctx, api, sharding, dist, torch, s, bvh, sc, rank, world, stream, max(1, min(args.steps, 2)))
+        strong = strong_record(ctx, api, sharding, dist, torch, s, bvh, sc, rank, world, stream, max(1, min(args.steps, 2)), group)
         ctx.set_camera(cam)
 
     if rank == 0:
@@ -521,7 +557,9 @@ def main():
             "msamples_per_s": samples_step * args.steps / (ms_total * 1e-3) / 1e6,
             "rays_per_step_per_gpu": rays_step, "rays_per_sample": rays_step / (W * H * spp_rank),
             "clocks": clocks,
-            "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": n_e2e},
+            "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": n_e2e,
+                    "api": "cupt_group (rank 0 stages scene + BVH once, ncclBroadcast to the other ranks, ncclReduce, image D2H on rank 0)" if group is not None
+                           else ("cupt_context per rank + torch.distributed reduce" if world > 1 else "cupt_context")},
             "gpu_launches": int(st["kernel_launches"]),
             "stage_ms_per_step": {k: st["ms_" + k] / args.steps for k in ("raygen", "extend", "shade", "accum")},
             "roofline": {"bound": "issue", "bound_note": "instruction issue / L1-L2 latency: the 16 MB BVH is cache-resident, DRAM carries the path records only "
@@ -566,6 +604,8 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             line["legacy_gpu"] = legacy_gpu(s, cam)
         print(json.dumps(line), flush=True)
+    if group is not None:
+        group.close()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
