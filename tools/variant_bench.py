@@ -25,7 +25,7 @@ def main():
         t0 = time.perf_counter(); ctx.render(0, spp); ctx.sync(); dt = time.perf_counter() - t0
         if dt < best: best, st = dt, ctx.stats()
     h = hashlib.sha1(ctx.read_accum(False).tobytes()).hexdigest()[:12]
-    print(f"{label:28s} frame {best*1e3:7.2f} ms  extend {st['ms_extend']:6.2f}  shade {st['ms_shade']:5.2f}  raygen {st['ms_raygen']:4.2f}  "
+    print(f"{label:28s} frame {best*1e3:7.2f} ms  extend {st['ms_extend']:6.2f}  shade {st['ms_shade']:5.2f}  raygen {st['ms_raygen']:4.2f}  accum {st['ms_accum']:5.2f}  "
           f"{st['rays']/best/1e6:7.1f} Mrays/s  image {h}", flush=True)
     ctx.close()
 
