@@ -6,7 +6,6 @@
 #include "layout.h"
 #include "kernels.cuh"
 #include "bdpt.cuh"
-#include "shade_regroup.cuh"
 #include "bvh_device.h"
 #include "output.cuh"
 #include <algorithm>
@@ -15,10 +14,6 @@
 #include <thread>
 
 using namespace cupt;
-
-#ifndef CUPT_SHADE_REGROUP
-#define CUPT_SHADE_REGROUP 1   // 0: k_shade (one thread per entry throughout) instead of k_shade_regroup
-#endif
 
 #define CK(call)                                                                                           \
 	do {                                                                                                   \
@@ -768,11 +763,7 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 				c->launches++;
 			} else if ((rc = launch_extend(c, sc, depth, depth & 1, depth > 0 && pp.term_stop, &pp))) return rc;
 			stage_begin(c, 2, ev);
-#if CUPT_SHADE_REGROUP
-			k_shade_regroup<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb, depth, depth & 1);
-#else
 			k_shade<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb, depth, depth & 1);
-#endif
 			stage_end(c, ev);
 			c->launches++;
 		}
