@@ -6,8 +6,8 @@
     compute-sanitizer --tool initcheck --error-exitcode 9 python tools/sanitize_run.py
 
 Sizes are tiny (64x64, 2 spp, a 20 k-triangle atrium) because the tools slow the kernels down 10-100x.  No oracle, no
-checks of the values: the tools' reports are the result.  (On this round's GPU pool compute-sanitizer is refused by the
-box; the plain run still walks every kernel family once and was clean: gpurun_out/san_plain.log.)"""
+checks of the values: the tools' reports are the result.  (On this GPU pool compute-sanitizer is closed — rounds 1 and 2 — so
+the plain run is what there is: it walks every kernel family and entry point once and was clean.)"""
 import os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -48,7 +48,9 @@ def run(scene, name, spheres=False):
     ctx.set_options(share_primary_hits=0)
     if not spheres:
         ctx.set_bvh2(n2, d2)
-        frame(ctx, f"{name} pt strict", traversal=api.TRAVERSAL_WIDE_STRICT)
+        frame(ctx, f"{name} pt strict", traversal=api.TRAVERSAL_WIDE_STRICT, record_retraces=1)
+        ctx.read_retrace_counts()
+        ctx.set_options(record_retraces=0)
         frame(ctx, f"{name} pt bvh2", traversal=api.TRAVERSAL_REF_BVH2)
         frame(ctx, f"{name} pt watertight", traversal=api.TRAVERSAL_WIDE, tri_test=api.TRI_WATERTIGHT)
         ctx.set_options(tri_test=api.TRI_REFEXACT)
@@ -62,6 +64,10 @@ def run(scene, name, spheres=False):
     ctx.read_image_rgb8(mirror_x=True)
     rays = ctx.camera_rays()
     ctx.trace_rays(rays[:1000])
+    ctx.trace_rays_noalloc(rays[:1000]); ctx.trace_rays_noalloc(rays[:77])
+    g = api.Group(devices=[0])   # the group path with one member: broadcast header, workers, in-place reduce skipped
+    g.set_scene(s); g.set_bvh(bvh); g.set_camera(cam); g.set_options(max_depth=5, seed=1234)
+    g.reset_accum(); g.render(0, SPP); g.read_accum(True); g.read_image_rgb8(); g.close()
     info = ctx.build_bvh_device(tie_rank=rank)
     print(f"{name} device bvh: {info}", flush=True)
     frame(ctx, f"{name} pt wide, device bvh", traversal=api.TRAVERSAL_WIDE)
