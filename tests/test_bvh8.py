@@ -81,6 +81,27 @@ def test_wide_traversal_logic_matches_brute_force_and_reference(get_case, emul, 
     assert nn > 0 and nt > 0
 
 
+@pytest.mark.parametrize("name", ["atrium20k", "soup5k"])
+def test_insertion_based_optimisation_keeps_the_tree_valid_and_makes_it_cheaper(get_case, emul, name):
+    """cupt_bvh_opts.reinsert_passes (default 2 sweeps): subtrees are moved to where the binary tree's total surface area drops
+    most (bvh8_build.cpp: Reinserter).  Whatever the sweeps do, the wide BVH must keep every structural invariant, return the
+    same hits (argmin over all triangles), and the SAH cost and the node visits per ray must not get worse."""
+    c = get_case(name)
+    rays = random_rays(c, 6000, 5)
+    want = c.osc.brute_force(rays, c.rank)
+    stats = {}
+    for passes in (-1, 1, 0, 6):          # none, one sweep, the default (two), many
+        b = c.handle.build_bvh(tie_rank=c.rank, reinsert_passes=passes)
+        info = b.info()
+        nodes, prims = b.arrays()
+        check_wide_bvh(c, nodes, prims, info, 3)
+        ids, ts, (nn, nt) = emul_trace(emul, nodes, prims, info["depth"], rays, fast=True)
+        assert np.array_equal(ids, want[0]) and ts.tobytes() == want[1].tobytes(), passes
+        stats[passes] = (info["sah_cost"], nn)
+    assert stats[0][0] < stats[-1][0] and stats[6][0] <= stats[1][0] * 1.001, stats       # cheaper by the builder's own measure
+    assert stats[0][1] < stats[-1][1], stats                                                  # and fewer node visits on these rays
+
+
 def test_bvh2_traversal_header_is_the_reference_algorithm(get_case, emul):
     c = get_case("atrium20k")
     rays = c.osc.camera_rays(c.cam)
