@@ -351,6 +351,82 @@ __global__ void __launch_bounds__(kTile) k_ploc_merge(N2* __restrict__ nodes, ui
 	ploc_merge_block(nodes, cnt, cid_in, cid_out, nn, n, tile_offs[blockIdx.x], node_base, dp, max_leaf, (int)blockIdx.x, s_warp, &tot);
 }
 
+// ---- clustering rounds driven from the device (round 2) ------------------------------------------------------------------
+// Round 1 read the survivor count back after EVERY round (16 - 43 host synchronisations per build).  Now the round's state
+// lives on the device: every kernel of a round takes the cluster count, the next node index and the ping-pong parity from
+// `PlocState`, a one-thread kernel advances it after the merge, and the host queues several rounds back to back with grids
+// sized for the count it last saw (blocks beyond the current count return at once; all kernels return once at most kTile
+// clusters are left) and reads the state back once per batch.
+struct PlocState { int32_t n; uint32_t node_base; uint32_t rounds; uint32_t stalled; };
+static_assert(sizeof(PlocState) == 16, "PlocState travels through the arena's 16-byte pinned word");
+
+template <int kRadius>
+__global__ void __launch_bounds__(kTile) k_ploc_nearest_s(const N2* __restrict__ nodes, const uint32_t* __restrict__ cid0, const uint32_t* __restrict__ cid1,
+                                                          const PlocState* __restrict__ st, uint32_t* __restrict__ nn)
+{
+	__shared__ float s_box[6][kTile + 2 * kRadius];
+	const int n = st->n;
+	if (n <= kTile || (int)blockIdx.x * kTile >= n) return;
+	ploc_nearest_block<kRadius, false>(nodes, (st->rounds & 1u) ? cid1 : cid0, n, nn, (int)blockIdx.x, s_box);
+}
+
+__global__ void __launch_bounds__(kTile) k_ploc_count_s(const uint32_t* __restrict__ nn, const PlocState* __restrict__ st, uint64_t* __restrict__ tile_sums)
+{
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	const int n = st->n;
+	if (n <= kTile || (int)blockIdx.x * kTile >= n) return;
+	int partner;
+	const uint64_t f = ploc_flags(nn, (int)blockIdx.x * kTile + threadIdx.x, n, &partner);
+	uint64_t tot;
+	block_scan_excl(f, s_warp, &tot);
+	if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(kTile) k_scan_tiles_s(uint64_t* __restrict__ tile_sums, const PlocState* __restrict__ st, uint64_t* __restrict__ total_out)
+{
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	const int n = st->n;
+	if (n <= kTile) return;
+	const int ntiles = (n + kTile - 1) / kTile;
+	uint64_t carry = 0;
+	for (int base = 0; base < ntiles; base += kTile * kScanRun) {
+		const int first = base + (int)threadIdx.x * kScanRun;
+		uint64_t v[kScanRun];
+		uint64_t sum = 0;
+#pragma unroll
+		for (int k = 0; k < kScanRun; ++k) { v[k] = first + k < ntiles ? tile_sums[first + k] : 0ull; sum += v[k]; }
+		uint64_t tot;
+		uint64_t run = carry + block_scan_excl(sum, s_warp, &tot);
+#pragma unroll
+		for (int k = 0; k < kScanRun; ++k) {
+			if (first + k < ntiles) tile_sums[first + k] = run;
+			run += v[k];
+		}
+		carry += tot;
+	}
+	if (threadIdx.x == 0) *total_out = carry;
+}
+
+__global__ void __launch_bounds__(kTile) k_ploc_merge_s(N2* __restrict__ nodes, uint32_t* __restrict__ cnt, uint32_t* __restrict__ cid0, uint32_t* __restrict__ cid1,
+                                                        const uint32_t* __restrict__ nn, const PlocState* __restrict__ st, const uint64_t* __restrict__ tile_offs,
+                                                        Dp* __restrict__ dp, const uint32_t max_leaf)
+{
+	__shared__ uint64_t s_warp[kTile / 32 + 1];
+	const int n = st->n;
+	if (n <= kTile || (int)blockIdx.x * kTile >= n) return;
+	const bool odd = (st->rounds & 1u) != 0u;
+	uint64_t tot;
+	ploc_merge_block(nodes, cnt, odd ? cid1 : cid0, odd ? cid0 : cid1, nn, n, tile_offs[blockIdx.x], st->node_base, dp, max_leaf, (int)blockIdx.x, s_warp, &tot);
+}
+
+__global__ void k_ploc_advance(PlocState* st, const uint64_t* __restrict__ total)
+{
+	if (st->n <= kTile) return;
+	const uint32_t valid = (uint32_t)*total, leaders = (uint32_t)(*total >> 32);
+	if (leaders == 0u || (int)(valid + leaders) != st->n) { st->stalled = 1u; st->n = 0; return; }   // (cannot happen: the smallest pair is always mutual)
+	st->n = (int32_t)valid; st->node_base += leaders; st->rounds += 1u;
+}
+
 // The last rounds in ONE launch: once at most kTile clusters are left, a single block runs nearest / merge round after round
 // with block barriers in between (no launches, no host read-back): about log_1.5(256) = 14 of the ~30 rounds of a 262 k-triangle
 // build.  state[0] = node_base afterwards, state[1] = rounds run here, state[2] = which cid buffer holds the root.
@@ -414,9 +490,12 @@ __device__ __forceinline__ void gather_kids(const N2* __restrict__ nodes, const 
 	}
 }
 
-// per item of the level: (inner children | leaf primitives << 32), reduced to one sum per tile
+// per item of the level: (inner children | leaf primitives << 32), reduced to one sum per tile.  The item's children (the
+// cost-optimal cut, a serial walk of up to 15 dependent node reads) are kept for k_collapse_emit, and so is the item's
+// exclusive prefix inside its tile: the emission then needs neither the walk nor a block-wide scan.
 __global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt, const Dp* __restrict__ dp, const int32_t* __restrict__ items,
-                                                          const int n_items, const uint32_t max_leaf, uint64_t* __restrict__ item_counts, uint64_t* __restrict__ tile_sums)
+                                                          const int n_items, const uint32_t max_leaf, uint64_t* __restrict__ item_prefix, int32_t* __restrict__ item_kids,
+                                                          uint64_t* __restrict__ tile_sums)
 {
 	__shared__ uint64_t s_warp[kTile / 32 + 1];
 	const int i = (int)blockIdx.x * kTile + threadIdx.x;
@@ -425,15 +504,23 @@ __global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__
 		Kids k;
 		gather_kids(nodes, cnt, dp, items[i], max_leaf, k);
 		uint32_t ni = 0, np = 0;
-		for (int q = 0; q < k.n; ++q) {
-			const uint32_t c = cnt[k.id[q]];
-			if (c > max_leaf) ni++; else np += c;
+		int32_t ids[8];
+#pragma unroll
+		for (int q = 0; q < 8; ++q) {
+			ids[q] = q < k.n ? k.id[q] : -1;
+			if (q < k.n) {
+				const uint32_t c = cnt[k.id[q]];
+				if (c > max_leaf) ni++; else np += c;
+			}
 		}
 		f = (uint64_t)ni | ((uint64_t)np << 32);
-		item_counts[i] = f;
+		int4* dst = reinterpret_cast<int4*>(item_kids + 8 * (size_t)i);
+		dst[0] = make_int4(ids[0], ids[1], ids[2], ids[3]);
+		dst[1] = make_int4(ids[4], ids[5], ids[6], ids[7]);
 	}
 	uint64_t tot;
-	block_scan_excl(f, s_warp, &tot);
+	const uint64_t ex = block_scan_excl(f, s_warp, &tot);
+	if (i < n_items) item_prefix[i] = ex;
 	if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
 }
 
@@ -463,7 +550,7 @@ __device__ __forceinline__ void write_prim(const int32_t prim, const int64_t nt,
 
 struct EmitArgs {
 	const N2* nodes; const uint32_t* cnt; const Dp* dp; const int32_t* items; int n_items; uint32_t max_leaf;
-	const uint64_t* item_counts; const uint64_t* tile_offs;
+	const uint64_t* item_prefix; const int32_t* item_kids; const uint64_t* tile_offs;
 	uint32_t level_base, next_base, prim_base;
 	int32_t* next_items; Node8* out_nodes; float4* out_prims;
 	int32_t* rec_prim;   // primitive of every record, in record order (k_emit_prims)
@@ -482,118 +569,142 @@ __global__ void __launch_bounds__(kTile) k_emit_prims(const int32_t* __restrict_
 	if (r < N) write_prim(rec_prim[r], nt, verts, tris, spheres, rank, out_prims + 3 * (size_t)r);
 }
 
+// One wide node per EIGHT lanes, lane q of the group = child q of the cut (round 1: one thread per wide node with the 8 x 8
+// slot assignment, the boxes and the node image in local memory — 23 of the 57 ms of a 100 M-triangle build).  The serial
+// rules of the host builder (bvh8_build.cpp) are kept exactly: greedy slot assignment = eight rounds of "largest cost over
+// (unassigned child, free slot), first in (child, slot) order wins"; children's inner-node and record offsets in SLOT order.
 __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 {
-	__shared__ uint64_t s_warp[kTile / 32 + 1];
-	const int i = (int)blockIdx.x * kTile + threadIdx.x;
-	const uint64_t f = i < A.n_items ? A.item_counts[i] : 0ull;
-	uint64_t tot;
-	const uint64_t ex = A.tile_offs[blockIdx.x] + block_scan_excl(f, s_warp, &tot);
+	__shared__ __align__(16) uint8_t s_q[kTile / 8][48];   // per group: qlo[3][8], qhi[3][8] of the node being assembled
+	__shared__ double s_sah[kTile / 32];
+	const uint32_t lane = threadIdx.x & 31u, q = lane & 7u, grp = threadIdx.x >> 3;
+	const uint32_t gmask = 0xffu << (lane & 24u);     // the eight lanes of this group
+	const int i = (int)blockIdx.x * (kTile / 8) + (int)grp;
 	double sah = 0;
-	if (i < A.n_items) {
-	const int32_t self = A.items[i];
-	Kids k;
-	gather_kids(A.nodes, A.cnt, A.dp, self, A.max_leaf, k);
-	float blo[3], bhi[3];
-	{
-		const float4* p = reinterpret_cast<const float4*>(&A.nodes[self]);
-		const float4 a = __ldg(p), b = __ldg(p + 1);
-		blo[0] = a.x; blo[1] = a.y; blo[2] = a.z; bhi[0] = b.x; bhi[1] = b.y; bhi[2] = b.z;
-	}
-	// octant slots: greedy assignment maximising dot(child centre - node centre, slot direction), as bvh8_build.cpp
-	float clo[8][3], chi[8][3], cost[8][8];
-	int slotOf[8], childIn[8];
-	for (int q = 0; q < 8; ++q) { slotOf[q] = -1; childIn[q] = -1; }
-	for (int q = 0; q < k.n; ++q) {
-		const float4* p = reinterpret_cast<const float4*>(&A.nodes[k.id[q]]);
-		const float4 a = __ldg(p), b = __ldg(p + 1);
-		clo[q][0] = a.x; clo[q][1] = a.y; clo[q][2] = a.z; chi[q][0] = b.x; chi[q][1] = b.y; chi[q][2] = b.z;
-		float d[3];
-		for (int a3 = 0; a3 < 3; ++a3) d[a3] = (0.5f * clo[q][a3] + 0.5f * chi[q][a3]) - (0.5f * blo[a3] + 0.5f * bhi[a3]);
-		for (int sl = 0; sl < 8; ++sl)
-			cost[q][sl] = ((sl & 4) ? d[0] : -d[0]) + ((sl & 2) ? d[1] : -d[1]) + ((sl & 1) ? d[2] : -d[2]);
-	}
-	for (int it = 0; it < k.n; ++it) {
-		int bk = -1, bs = -1; float bc = -3.0e38f;
-		for (int q = 0; q < k.n; ++q) {
-			if (slotOf[q] >= 0) continue;
-			for (int sl = 0; sl < 8; ++sl)
-				if (childIn[sl] < 0 && (cost[q][sl] > bc || bk < 0)) { bc = cost[q][sl]; bk = q; bs = sl; }
+	if (i < A.n_items) {   // (uniform over the group)
+		const int32_t self = A.items[i];
+		const int32_t kid = A.item_kids[8 * (size_t)i + q];
+		const uint64_t ex = A.tile_offs[i / kTile] + A.item_prefix[i];
+		float blo[3], bhi[3], clo[3] = {0.f, 0.f, 0.f}, chi[3] = {0.f, 0.f, 0.f};
+		{
+			const float4* p = reinterpret_cast<const float4*>(&A.nodes[self]);
+			const float4 a = __ldg(p), b = __ldg(p + 1);
+			blo[0] = a.x; blo[1] = a.y; blo[2] = a.z; bhi[0] = b.x; bhi[1] = b.y; bhi[2] = b.z;
 		}
-		slotOf[bk] = bs; childIn[bs] = bk;
-	}
-	// quantisation grid: power-of-two cell per axis, at least 2^-24 of the coordinate magnitude
-	Node8 nd;
-	memset(&nd, 0, sizeof(nd));
-	double scale[3], inv_scale[3];
-	for (int a = 0; a < 3; ++a) {
-		nd.p[a] = blo[a];
-		const double ext = (double)bhi[a] - (double)blo[a];
-		int e = -126;
-		if (ext > 0) {
-			// smallest e with 255 * 2^e >= ext, from the exponent field (a double log2 per axis and node was a third of this
-			// kernel): 2^k <= ext < 2^(k+1) gives 255 * 2^(k-8) < ext, so start there; at most two steps
-			e = ((__double2hiint(ext) >> 20) & 0x7ff) - 1023 - 8;
-			while (ldexp(255.0, e) < ext) ++e;
-		}
-		const float m = fmaxf(fabsf(blo[a]), fabsf(bhi[a]));
-		e = max(e, dev_float_exponent(m) - 24);
-		e = max(-126, min(127, e));
-		nd.e[a] = (uint8_t)(e + 127);
-		scale[a] = ldexp(1.0, e);
-		inv_scale[a] = ldexp(1.0, -e);   // exact: the divisions below become multiplications with the same result
-	}
-	const uint32_t child_off = (uint32_t)ex, prim_off = (uint32_t)(ex >> 32);
-	nd.child_base = A.next_base + child_off;
-	nd.tri_base = A.prim_base + prim_off;
-	uint32_t triOfs = 0, ninner = 0;
-	for (int sl = 0; sl < 8; ++sl) {
-		const int q = childIn[sl];
-		if (q < 0) continue;
-		const int32_t c = k.id[q];
-		for (int a = 0; a < 3; ++a) {
-			const double p = nd.p[a];
-			double ql = floor(((double)clo[q][a] - p) * inv_scale[a]);
-			double qh = ceil(((double)chi[q][a] - p) * inv_scale[a]);
-			while (ql > 0 && p + ql * scale[a] > (double)clo[q][a]) ql -= 1;
-			while (p + qh * scale[a] < (double)chi[q][a]) qh += 1;
-			ql = fmax(0.0, fmin(255.0, ql));
-			qh = fmin(255.0, fmax(qh, ql));   // hi <= node hi <= p + 255 * scale by construction of e
-			nd.qlo[a][sl] = (uint8_t)ql; nd.qhi[a][sl] = (uint8_t)qh;
-		}
-		const uint32_t cc = A.cnt[c];
-		const double area2 = 2.0 * (double)half_area(clo[q][0], clo[q][1], clo[q][2], chi[q][0], chi[q][1], chi[q][2]);
-		if (cc > A.max_leaf) {
-			nd.imask |= (uint8_t)(1u << sl);
-			A.next_items[child_off + ninner++] = c;
-			sah += area2 * A.inv_root_area;
-		} else {
-			const uint32_t unary = cc == 1 ? 1u : (cc == 2 ? 3u : 7u);
-			nd.pvalid |= unary << (4 * sl);
-			int32_t stack[4]; int sp = 0;
-			stack[sp++] = c;
-			uint32_t w = 0;
-			while (sp > 0) {                       // <= 3 primitives: left-first walk of the tiny subtree
-				const int32_t x = stack[--sp];
-				const int32_t l = A.nodes[x].left;
-				if (l < 0) {
-					A.rec_prim[nd.tri_base + triOfs + w] = -1 - l;   // the record itself is written by k_emit_prims
-					++w;
-				} else {
-					stack[sp++] = A.nodes[x].right; stack[sp++] = l;
-				}
-			}
-			triOfs += cc;
-			sah += area2 * A.inv_root_area * cc;
-		}
-	}
-	const uint4* src = reinterpret_cast<const uint4*>(&nd);
-	uint4* dst = reinterpret_cast<uint4*>(&A.out_nodes[A.level_base + i]);
+		float cost[8];
+		if (kid >= 0) {
+			const float4* p = reinterpret_cast<const float4*>(&A.nodes[kid]);
+			const float4 a = __ldg(p), b = __ldg(p + 1);
+			clo[0] = a.x; clo[1] = a.y; clo[2] = a.z; chi[0] = b.x; chi[1] = b.y; chi[2] = b.z;
+			float d[3];
 #pragma unroll
-	for (int w = 0; w < 5; ++w) dst[w] = src[w];
+			for (int a3 = 0; a3 < 3; ++a3) d[a3] = (0.5f * clo[a3] + 0.5f * chi[a3]) - (0.5f * blo[a3] + 0.5f * bhi[a3]);
+#pragma unroll
+			for (int sl = 0; sl < 8; ++sl) cost[sl] = ((sl & 4) ? d[0] : -d[0]) + ((sl & 2) ? d[1] : -d[1]) + ((sl & 1) ? d[2] : -d[2]);
+		}
+		// greedy octant slots
+		const uint32_t nk = (uint32_t)__popc(__ballot_sync(gmask, kid >= 0) & gmask);
+		uint32_t free_slots = 0xffu;
+		int slot = -1;
+		for (uint32_t it = 0; it < nk; ++it) {
+			float bc = -3.0e38f; int bs = -1;
+			if (kid >= 0 && slot < 0) {
+#pragma unroll
+				for (int sl = 0; sl < 8; ++sl)
+					if (((free_slots >> sl) & 1u) && (cost[sl] > bc || bs < 0)) { bc = cost[sl]; bs = sl; }
+			}
+			// the group's winner: largest cost, lowest child index on a tie (the serial loop's strict `>`); a lane without a candidate never wins
+			float wc = bc; int wq = bs >= 0 ? (int)q : 99, ws = bs;
+#pragma unroll
+			for (int o = 4; o > 0; o >>= 1) {
+				const float oc = __shfl_xor_sync(gmask, wc, o); const int oq = __shfl_xor_sync(gmask, wq, o), os = __shfl_xor_sync(gmask, ws, o);
+				const bool take = oq < 99 && (wq == 99 || oc > wc || (oc == wc && oq < wq));
+				if (take) { wc = oc; wq = oq; ws = os; }
+			}
+			if ((int)q == wq) slot = ws;
+			free_slots &= ~(1u << ws);
+		}
+		// quantisation grid: power-of-two cell per axis, at least 2^-24 of the coordinate magnitude (every lane: the same values)
+		double scale[3], inv_scale[3];
+		uint32_t ebits = 0u;
+#pragma unroll
+		for (int a = 0; a < 3; ++a) {
+			const double ext = (double)bhi[a] - (double)blo[a];
+			int e = -126;
+			if (ext > 0) {
+				e = ((__double2hiint(ext) >> 20) & 0x7ff) - 1023 - 8;   // 2^k <= ext < 2^(k+1): 255 * 2^(k-8) < ext, at most two steps up
+				while (ldexp(255.0, e) < ext) ++e;
+			}
+			const float m = fmaxf(fabsf(blo[a]), fabsf(bhi[a]));
+			e = max(e, dev_float_exponent(m) - 24);
+			e = max(-126, min(127, e));
+			ebits |= (uint32_t)(e + 127) << (8 * a);
+			scale[a] = ldexp(1.0, e);
+			inv_scale[a] = ldexp(1.0, -e);
+		}
+		// this child's record count / kind, and what lies before it in SLOT order
+		const uint32_t cc = kid >= 0 ? A.cnt[kid] : 0u;
+		const bool inner = kid >= 0 && cc > A.max_leaf, leaf = kid >= 0 && !inner;
+		uint32_t inner_before = 0u, prims_before = 0u;
+#pragma unroll
+		for (int j = 0; j < 8; ++j) {
+			const int os = __shfl_sync(gmask, slot, (int)(lane & 24u) + j);
+			const uint32_t occ = __shfl_sync(gmask, cc, (int)(lane & 24u) + j);
+			const int oin = __shfl_sync(gmask, (int)inner, (int)(lane & 24u) + j);
+			if (os >= 0 && slot >= 0 && os < slot) { if (oin) ++inner_before; else prims_before += occ; }
+		}
+		const uint32_t child_off = (uint32_t)ex, prim_off = (uint32_t)(ex >> 32);
+		const uint32_t child_base = A.next_base + child_off, tri_base = A.prim_base + prim_off;
+		for (uint32_t k = q; k < 48u; k += 8u) s_q[grp][k] = 0u;
+		__syncwarp(gmask);
+		uint32_t my_imask = 0u, my_pvalid = 0u;
+		if (kid >= 0) {
+#pragma unroll
+			for (int a = 0; a < 3; ++a) {
+				const double p = (double)blo[a];
+				double ql = floor(((double)clo[a] - p) * inv_scale[a]);
+				double qh = ceil(((double)chi[a] - p) * inv_scale[a]);
+				while (ql > 0 && p + ql * scale[a] > (double)clo[a]) ql -= 1;
+				while (p + qh * scale[a] < (double)chi[a]) qh += 1;
+				ql = fmax(0.0, fmin(255.0, ql));
+				qh = fmin(255.0, fmax(qh, ql));   // hi <= node hi <= p + 255 * scale by construction of e
+				s_q[grp][8 * a + slot] = (uint8_t)ql; s_q[grp][24 + 8 * a + slot] = (uint8_t)qh;
+			}
+			const double area2 = 2.0 * (double)half_area(clo[0], clo[1], clo[2], chi[0], chi[1], chi[2]);
+			if (inner) {
+				my_imask = 1u << slot;
+				A.next_items[child_off + inner_before] = kid;
+				sah += area2 * A.inv_root_area;
+			} else {
+				my_pvalid = (cc == 1 ? 1u : (cc == 2 ? 3u : 7u)) << (4 * slot);
+				int32_t stack[4]; int sp = 0;
+				stack[sp++] = kid;
+				uint32_t w = 0;
+				while (sp > 0) {                       // <= 3 primitives: left-first walk of the tiny subtree
+					const int32_t x = stack[--sp];
+					const int32_t l = A.nodes[x].left;
+					if (l < 0) {
+						A.rec_prim[tri_base + prims_before + w] = -1 - l;   // the record itself is written by k_emit_prims
+						++w;
+					} else {
+						stack[sp++] = A.nodes[x].right; stack[sp++] = l;
+					}
+				}
+				sah += area2 * A.inv_root_area * cc;
+			}
+		}
+		(void)leaf;
+		const uint32_t imask = __reduce_or_sync(gmask, my_imask), pvalid = __reduce_or_sync(gmask, my_pvalid);
+		__syncwarp(gmask);
+		if (q < 5u) {   // the 80-byte node: five 16-byte words, one per lane
+			uint4 w;
+			if (q == 0u) w = make_uint4(__float_as_uint(blo[0]), __float_as_uint(blo[1]), __float_as_uint(blo[2]), ebits | (imask << 24));
+			else if (q == 1u) w = make_uint4(child_base, 0u, tri_base, pvalid);
+			else w = *reinterpret_cast<const uint4*>(&s_q[grp][16u * (q - 2u)]);
+			reinterpret_cast<uint4*>(&A.out_nodes[A.level_base + i])[q] = w;
+		}
 	}
 	// one atomic per block: one per thread on the single address serialised the kernel (2.9 M wide nodes at 30 M triangles)
-	__shared__ double s_sah[kTile / 32];
 #pragma unroll
 	for (int o = 16; o > 0; o >>= 1) sah += __shfl_down_sync(0xffffffffu, sah, o);
 	if ((threadIdx.x & 31) == 0) s_sah[threadIdx.x >> 5] = sah;
@@ -671,7 +782,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	// leaves are written, the collapse reuses the cluster arrays for its level queues
 	const size_t need = up256(n * sizeof(N2)) + up256(64) + 2 * up256(n * 8) + 2 * up256(n * 4) + up256(temp_bytes + 256)
 	                    + up256(2 * n * sizeof(N2)) + up256(2 * n * sizeof(Dp)) + up256(2 * n * 4) + 3 * up256(n * 4) + up256(((size_t)tilesN + 1) * 8) + up256(64)
-	                    + up256((n / 2 + 2) * 8) + up256(64) + 4096;
+	                    + up256((n / 2 + 2) * 8) + up256((n / 2 + 2) * 32) + up256(64) + 4096;
 	int rc;
 	if ((rc = arena.reserve(need))) return rc;
 	cudaEvent_t* ev = arena.ev;
@@ -701,30 +812,44 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	uint64_t* tile_sums = take<uint64_t>(arena, (size_t)tilesN + 1);
 	uint64_t* d_total = take<uint64_t>(arena, 1);
 	uint64_t* item_counts = take<uint64_t>(arena, n / 2 + 2);
+	int32_t* item_kids = take<int32_t>(arena, (n / 2 + 2) * 8);
 	double* d_sah = take<double>(arena, 1);
 	if (arena.off > arena.cap) return set_error(CUPT_ERR_CUDA, "internal: BVH build workspace undersized (%zu > %zu)", arena.off, arena.cap);
 	k_sorted_leaves<<<tilesN, kTile, 0, st>>>(leaf, vals[sorted], N, nodes, cnt, cid[0]);
 	int cn = (int)N, cur = 0, rounds = 0;
 	uint32_t node_base = (uint32_t)N;
-	while (cn > kTile) {
-		const int tiles = (cn + kTile - 1) / kTile;
-		switch (radius) {
-		case 32: k_ploc_nearest<32><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
-		case 16: k_ploc_nearest<16><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
-		case 8: k_ploc_nearest<8><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
-		case 2: k_ploc_nearest<2><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
-		case 1: k_ploc_nearest<1><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
-		default: k_ploc_nearest<4><<<tiles, kTile, 0, st>>>(nodes, cid[cur], cn, nn); break;
+	if (cn > kTile) {
+		PlocState* d_state = reinterpret_cast<PlocState*>(item_counts);   // (the collapse's per-item counts are not in use yet)
+		PlocState* h_state = reinterpret_cast<PlocState*>(h_total);
+		h_state->n = cn; h_state->node_base = node_base; h_state->rounds = 0u; h_state->stalled = 0u;
+		CKB(cudaMemcpyAsync(d_state, h_state, sizeof(PlocState), cudaMemcpyHostToDevice, st));
+		int bound = cn;
+		while (bound > kTile) {
+			const int tiles = (bound + kTile - 1) / kTile;
+			// rounds per read-back: clusters shrink by a third to a half per round, so a batch's later rounds launch up to ~3 x the
+			// blocks they need; cheap when the grids are small (where the synchronisation is what costs), not at 10^5 tiles
+			const int batch = tiles >= 32768 ? 1 : (tiles >= 4096 ? 2 : (tiles >= 512 ? 4 : 8));
+			for (int b = 0; b < batch; ++b) {
+				switch (radius) {
+				case 32: k_ploc_nearest_s<32><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
+				case 16: k_ploc_nearest_s<16><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
+				case 8: k_ploc_nearest_s<8><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
+				case 2: k_ploc_nearest_s<2><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
+				case 1: k_ploc_nearest_s<1><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
+				default: k_ploc_nearest_s<4><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
+				}
+				k_ploc_count_s<<<tiles, kTile, 0, st>>>(nn, d_state, tile_sums);
+				k_scan_tiles_s<<<1, kTile, 0, st>>>(tile_sums, d_state, d_total);
+				k_ploc_merge_s<<<tiles, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, d_state, tile_sums, dp, (uint32_t)max_leaf);
+				k_ploc_advance<<<1, 1, 0, st>>>(d_state, d_total);
+			}
+			CKB(cudaMemcpyAsync(h_state, d_state, sizeof(PlocState), cudaMemcpyDeviceToHost, st));
+			CKB(cudaStreamSynchronize(st));
+			if (h_state->stalled || h_state->n >= bound || h_state->n < 1)
+				return set_error(CUPT_ERR_CUDA, "internal: PLOC made no progress (clusters %d -> %d after %u rounds)", bound, h_state->n, h_state->rounds);
+			bound = h_state->n;
 		}
-		k_ploc_count<<<tiles, kTile, 0, st>>>(nn, cn, tile_sums);
-		k_scan_tiles<<<1, kTile, 0, st>>>(tile_sums, tiles, d_total);
-		k_ploc_merge<<<tiles, kTile, 0, st>>>(nodes, cnt, cid[cur], cid[cur ^ 1], nn, cn, tile_sums, node_base, dp, (uint32_t)max_leaf);
-		CKB(cudaMemcpyAsync(h_total, d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
-		CKB(cudaStreamSynchronize(st));
-		const uint32_t valid = (uint32_t)*h_total, leaders = (uint32_t)(*h_total >> 32);
-		if (leaders == 0 || (int)valid + (int)leaders != cn)
-			return set_error(CUPT_ERR_CUDA, "internal: PLOC round made no progress (n %d, valid %u, merged %u)", cn, valid, leaders);
-		cn = (int)valid; node_base += leaders; cur ^= 1; ++rounds;
+		cn = h_state->n; node_base = h_state->node_base; rounds = (int)h_state->rounds; cur = rounds & 1;
 	}
 	if (cn > 1) {   // the remaining rounds in one launch (k_ploc_tail)
 		uint32_t* state = reinterpret_cast<uint32_t*>(tile_sums);
@@ -780,17 +905,17 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 			out->nodes = bigger; out->nodes_capacity_bytes = ncap;
 		}
 		const int tiles = (n_items + kTile - 1) / kTile;
-		k_collapse_count<<<tiles, kTile, 0, st>>>(nodes, cnt, dp, items[lvl], n_items, (uint32_t)max_leaf, item_counts, tile_sums);
+		k_collapse_count<<<tiles, kTile, 0, st>>>(nodes, cnt, dp, items[lvl], n_items, (uint32_t)max_leaf, item_counts, item_kids, tile_sums);
 		k_scan_tiles<<<1, kTile, 0, st>>>(tile_sums, tiles, d_total);
 		EmitArgs A;
 		A.nodes = nodes; A.cnt = cnt; A.dp = dp; A.items = items[lvl]; A.n_items = n_items; A.max_leaf = (uint32_t)max_leaf;
-		A.item_counts = item_counts; A.tile_offs = tile_sums;
+		A.item_prefix = item_counts; A.item_kids = item_kids; A.tile_offs = tile_sums;
 		A.level_base = level_base; A.next_base = level_base + (uint32_t)n_items; A.prim_base = prim_base;
 		A.next_items = items[lvl ^ 1]; A.out_nodes = static_cast<Node8*>(out->nodes); A.out_prims = static_cast<float4*>(out->prims);
 		A.rec_prim = reinterpret_cast<int32_t*>(nn);   // (the PLOC neighbour array is free by now)
 		A.verts = verts; A.tris = tris; A.spheres = spheres; A.rank = rank; A.nt = nt;
 		A.inv_root_area = 1.0 / root_area; A.sah = d_sah;
-		k_collapse_emit<<<tiles, kTile, 0, st>>>(A);
+		k_collapse_emit<<<(n_items + kTile / 8 - 1) / (kTile / 8), kTile, 0, st>>>(A);
 		CKB(cudaMemcpyAsync(h_total, d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
 		CKB(cudaStreamSynchronize(st));
 		level_base += (uint32_t)n_items;
