@@ -1,0 +1,15 @@
+"""Developer tool (GPU box): build the wide BVH of an N-million-triangle soup on the device twice (first = warm-up) and print the
+stage times; meant for an ncu launch list of the builder's kernels:  SIZE=30 python tools/build_only.py"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from cudapathtracer_b200 import api, scenes
+
+n = int(float(os.environ.get("SIZE", "30")) * 1e6)
+sc = scenes.triangle_soup(n) if os.environ.get("SCENE", "soup") == "soup" else scenes.atrium(n)
+s = api.SceneHandle(); s.add_scene(sc)
+ctx = api.Context(0)
+ctx.set_scene(s)
+for _ in range(int(os.environ.get("REPS", "2"))):
+    info = ctx.build_bvh_device()
+print({k: (round(v, 3) if isinstance(v, float) else v) for k, v in info.items()})
