@@ -285,8 +285,12 @@ int cupt_bvh_build(const cupt_scene* s, const cupt_bvh_opts* opts, cupt_bvh** ou
 
 	int32_t root2 = 0;
 	// default: two sweeps (config 2: SAH cost 20.9 -> 20.3, node visits per ray 11.4 -> 10.7, extend 33.5 -> 31.0 ms per frame; more
-	// sweeps change nothing measurable) while the single-threaded search stays within seconds; none for the multi-million soups
-	int reinsert_passes = (opts && opts->reinsert_passes != 0) ? std::min(opts->reinsert_passes, 16) : (N <= ((int64_t)1 << 22) ? 2 : 0);
+	// sweeps change nothing measurable) up to 2^20 primitives, where the single-threaded search stays within a few seconds (6 us
+	// per primitive and sweep); none above.  The multi-million soups of config 4 would not profit anyway: uniformly random
+	// triangles leave the sweeps nothing to find (1.5 M: SAH cost 129.20 -> 129.04 for 8 s).  A batched parallel search (moves
+	// found concurrently on a frozen tree, applied in order when their nodes were untouched) was tried and rejected: even at 64
+	// candidates per batch the stale gains cost half of the improvement (SAH 20.49 instead of 20.27, visits 10.95 instead of 10.67).
+	int reinsert_passes = (opts && opts->reinsert_passes != 0) ? std::min(opts->reinsert_passes, 16) : (N <= ((int64_t)1 << 20) ? 2 : 0);
 	reinsert_passes = std::max(reinsert_passes, 0);
 	if (reinsert_passes > 0 && B.next.load() > 3) {
 		Reinserter R(B.nodes, B.next.load());

@@ -131,7 +131,7 @@ typedef struct cupt_bvh_opts {
 	const uint32_t* tie_rank;  /* optional rank per triangle (cupt_bvh2_leaf_order); NULL = triangle index */
 	int ploc_radius;       /* cupt_build_bvh_device only: neighbour search radius of the clustering: 1, 2, 4 (default, also for any other value), 8, 16 or 32 */
 	int reinsert_passes;   /* cupt_bvh_build only: sweeps of insertion-based optimisation over the binary tree before the collapse (every
-	                          subtree is re-inserted where the tree's total surface area drops most).  0 = default (2 sweeps up to 2^22
+	                          subtree is re-inserted where the tree's total surface area drops most).  0 = default (2 sweeps up to 2^20
 	                          primitives, none above: the search is single-threaded), < 0 = none, k > 0 = k sweeps (at most 16) */
 	int greedy_collapse;   /* cupt_bvh_build only: 1 = open the largest child until there are eight (the first collapse rule, kept for
 	                          comparison: tools/build_compare.py); default 0 = cost-optimal cut */
