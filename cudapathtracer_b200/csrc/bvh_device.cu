@@ -51,23 +51,38 @@ __host__ __device__ __forceinline__ float ord2f(const uint32_t o) { const uint32
 // Grid-stride over the primitives with the centroid bounds kept in registers: one atomic pair per BLOCK and axis at the end
 // (one pair per warp — 5.6 M atomics on six addresses for 30 M primitives — made this kernel 4.7 ms where its 3 GB of
 // traffic need 0.5 ms).
+// Also written here, while the triangle and its vertices are in registers anyway: the primitive's 48-byte traversal record, in
+// primitive order.  k_emit_prims then moves ONE 48-byte piece per record into tree order; round 1 gathered the triangle and its
+// three vertices a second time there (2.3 cache lines per record on the soups, more on a mesh with shared vertices: 30 GB of DRAM
+// traffic and 6.8 ms for 100 M triangles).
 __global__ void __launch_bounds__(kTile) k_leaf_boxes(const float* __restrict__ verts, const cupt_triangle* __restrict__ tris, const int64_t nt,
-                                                      const float4* __restrict__ spheres, const int64_t N, N2* __restrict__ leaf, uint32_t* __restrict__ cbounds)
+                                                      const float4* __restrict__ spheres, const uint32_t* __restrict__ rank, const int64_t N,
+                                                      N2* __restrict__ leaf, float4* __restrict__ records, uint32_t* __restrict__ cbounds)
 {
 	uint32_t mn[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, mx[3] = {0u, 0u, 0u};
 	for (int64_t i = (int64_t)blockIdx.x * kTile + threadIdx.x; i < N; i += (int64_t)gridDim.x * kTile) {
 		float lo[3], hi[3];
+		float4 r0, r1, r2;
 		if (i < nt) {
 			const cupt_triangle t = tris[i];
 			const int32_t vi[3] = {t.v0, t.v1, t.v2};
+			float v[3][3];
 			for (int a = 0; a < 3; ++a) { lo[a] = 3.0e38f; hi[a] = -3.0e38f; }
 			for (int k = 0; k < 3; ++k)
-				for (int a = 0; a < 3; ++a) { const float v = verts[3 * (size_t)vi[k] + a]; lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v); }
+				for (int a = 0; a < 3; ++a) { v[k][a] = verts[3 * (size_t)vi[k] + a]; lo[a] = fminf(lo[a], v[k][a]); hi[a] = fmaxf(hi[a], v[k][a]); }
+			// the record: v0, e1 = v1 - v0, e2 = v2 - v0 (modelLoader.h:57-58), primitive, rank, kind 0
+			r0 = make_float4(v[0][0], v[0][1], v[0][2], __fsub_rn(v[1][0], v[0][0]));
+			r1 = make_float4(__fsub_rn(v[1][1], v[0][1]), __fsub_rn(v[1][2], v[0][2]), __fsub_rn(v[2][0], v[0][0]), __fsub_rn(v[2][1], v[0][1]));
+			r2 = make_float4(__fsub_rn(v[2][2], v[0][2]), __uint_as_float((uint32_t)i), __uint_as_float(rank ? rank[i] : (uint32_t)i), __uint_as_float(0u));
 		} else {
 			const float4 s = spheres[3 * (i - nt)];   // SphereShade: centre, radius
 			const float cc[3] = {s.x, s.y, s.z};
 			for (int a = 0; a < 3; ++a) { lo[a] = __fsub_rn(cc[a], s.w); hi[a] = __fadd_rn(cc[a], s.w); }
+			r0 = s;
+			r1 = make_float4(0.f, 0.f, 0.f, 0.f);
+			r2 = make_float4(0.f, __uint_as_float((uint32_t)(i - nt)), __uint_as_float((uint32_t)i), __uint_as_float(1u));
 		}
+		records[3 * i] = r0; records[3 * i + 1] = r1; records[3 * i + 2] = r2;
 		N2 n;
 		for (int a = 0; a < 3; ++a) {
 			const float c = __fadd_rn(__fmul_rn(0.5f, lo[a]), __fmul_rn(0.5f, hi[a]));
@@ -231,13 +246,6 @@ __device__ __forceinline__ void ploc_nearest_block(const N2* nodes, const uint32
 	nn[i] = (uint32_t)bj;
 }
 
-template <int kRadius>
-__global__ void __launch_bounds__(kTile) k_ploc_nearest(const N2* __restrict__ nodes, const uint32_t* __restrict__ cid, const int n, uint32_t* __restrict__ nn)
-{
-	__shared__ float s_box[6][kTile + 2 * kRadius];
-	ploc_nearest_block<kRadius, false>(nodes, cid, n, nn, (int)blockIdx.x, s_box);
-}
-
 // valid = the slot survives the round (everything but the higher half of a mutual pair); leader = lower half
 __device__ __forceinline__ uint64_t ploc_flags(const uint32_t* nn, const int i, const int n, int* partner)
 {
@@ -247,16 +255,6 @@ __device__ __forceinline__ uint64_t ploc_flags(const uint32_t* nn, const int i, 
 	*partner = mutual ? j : -1;
 	const uint64_t valid = !(mutual && i > j), leader = mutual && i < j;
 	return valid | (leader << 32);
-}
-
-__global__ void __launch_bounds__(kTile) k_ploc_count(const uint32_t* __restrict__ nn, const int n, uint64_t* __restrict__ tile_sums)
-{
-	__shared__ uint64_t s_warp[kTile / 32 + 1];
-	int partner;
-	const uint64_t f = ploc_flags(nn, (int)blockIdx.x * kTile + threadIdx.x, n, &partner);
-	uint64_t tot;
-	block_scan_excl(f, s_warp, &tot);
-	if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
 }
 
 // Cost-optimal collapse (Ylitie, Karras, Laine 2017, section 3.1; the host builder does the same, bvh8_build.cpp):
@@ -284,6 +282,44 @@ __device__ __forceinline__ void dp_of(const Dp* dp, const N2* nodes, const uint3
 	}
 }
 
+// the merged node `id` of clusters l and r (boxes la/lb and ra/rb = {lo, .} / {hi, .}): box, children, primitive count, collapse costs
+__device__ __forceinline__ void ploc_create_node(N2* nodes, uint32_t* cnt, Dp* dp, const uint32_t max_leaf, const uint32_t id, const uint32_t l, const uint32_t r,
+                                                 const float4 la, const float4 lb, const float4 ra, const float4 rb)
+{
+	const float4 oa = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), __int_as_float((int32_t)l));
+	const float4 ob = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), __int_as_float((int32_t)r));
+	float4* po = reinterpret_cast<float4*>(&nodes[id]);
+	po[0] = oa; po[1] = ob;
+	const uint32_t total = cnt[l] + cnt[r];
+	cnt[id] = total;
+	if (total > max_leaf) {
+		float cl[8], cr[8];
+		dp_of(dp, nodes, cnt, l, max_leaf, cl);
+		dp_of(dp, nodes, cnt, r, max_leaf, cr);
+		Dp d;
+		uint32_t splits = 0u;
+		float D8 = 0.f;
+#pragma unroll
+		for (int j = 2; j <= 8; ++j) {
+			float best = 3.0e38f; uint32_t bk = 1u;
+#pragma unroll
+			for (int k = 1; k < j; ++k) {
+				const float v = cl[k < 7 ? k : 7] + cr[(j - k) < 7 ? (j - k) : 7];
+				if (v < best) { best = v; bk = (uint32_t)k; }
+			}
+			splits |= bk << (3 * (j - 2));
+			if (j <= 7) d.c[j - 1] = best; else D8 = best;
+		}
+		d.c[0] = half_area(oa.x, oa.y, oa.z, ob.x, ob.y, ob.z) * kCostNode + D8;
+#pragma unroll
+		for (int i = 1; i < 7; ++i) d.c[i] = fminf(d.c[i], d.c[i - 1]);
+		d.splits = splits;
+		float4* pd = reinterpret_cast<float4*>(&dp[id]);
+		pd[0] = make_float4(d.c[0], d.c[1], d.c[2], d.c[3]);
+		pd[1] = make_float4(d.c[4], d.c[5], d.c[6], __uint_as_float(d.splits));
+	}
+}
+
 // one tile of a PLOC round: order-preserving compaction of the surviving clusters, creation of the merged nodes and their
 // collapse costs.  *tile_total = (survivors, leaders << 32) of this tile.
 __device__ __forceinline__ void ploc_merge_block(N2* nodes, uint32_t* cnt, const uint32_t* cid_in, uint32_t* cid_out, const uint32_t* nn, const int n,
@@ -303,128 +339,199 @@ __device__ __forceinline__ void ploc_merge_block(N2* nodes, uint32_t* cnt, const
 		const uint32_t l = cid_in[i], r = cid_in[partner];
 		const float4* pl = reinterpret_cast<const float4*>(&nodes[l]);
 		const float4* pr = reinterpret_cast<const float4*>(&nodes[r]);
-		const float4 la = pl[0], lb = pl[1], ra = pr[0], rb = pr[1];
-		float4 oa = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), __int_as_float((int32_t)l));
-		float4 ob = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), __int_as_float((int32_t)r));
-		float4* po = reinterpret_cast<float4*>(&nodes[id]);
-		po[0] = oa; po[1] = ob;
-		const uint32_t total = cnt[l] + cnt[r];
-		cnt[id] = total;
+		ploc_create_node(nodes, cnt, dp, max_leaf, id, l, r, pl[0], pl[1], pr[0], pr[1]);
 		cid_out[out] = id;
-		if (total > max_leaf) {
-			float cl[8], cr[8];
-			dp_of(dp, nodes, cnt, l, max_leaf, cl);
-			dp_of(dp, nodes, cnt, r, max_leaf, cr);
-			Dp d;
-			uint32_t splits = 0u;
-			float D8 = 0.f;
-#pragma unroll
-			for (int j = 2; j <= 8; ++j) {
-				float best = 3.0e38f; uint32_t bk = 1u;
-#pragma unroll
-				for (int k = 1; k < j; ++k) {
-					const float v = cl[k < 7 ? k : 7] + cr[(j - k) < 7 ? (j - k) : 7];
-					if (v < best) { best = v; bk = (uint32_t)k; }
-				}
-				splits |= bk << (3 * (j - 2));
-				if (j <= 7) d.c[j - 1] = best; else D8 = best;
-			}
-			d.c[0] = half_area(oa.x, oa.y, oa.z, ob.x, ob.y, ob.z) * kCostNode + D8;
-#pragma unroll
-			for (int i = 1; i < 7; ++i) d.c[i] = fminf(d.c[i], d.c[i - 1]);
-			d.splits = splits;
-			float4* pd = reinterpret_cast<float4*>(&dp[id]);
-			pd[0] = make_float4(d.c[0], d.c[1], d.c[2], d.c[3]);
-			pd[1] = make_float4(d.c[4], d.c[5], d.c[6], __uint_as_float(d.splits));
-		}
 	} else {
 		cid_out[out] = cid_in[i];
 	}
 }
 
-__global__ void __launch_bounds__(kTile) k_ploc_merge(N2* __restrict__ nodes, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ cid_in,
-                                                      uint32_t* __restrict__ cid_out, const uint32_t* __restrict__ nn, const int n,
-                                                      const uint64_t* __restrict__ tile_offs, const uint32_t node_base, Dp* __restrict__ dp, const uint32_t max_leaf)
-{
-	__shared__ uint64_t s_warp[kTile / 32 + 1];
-	uint64_t tot;
-	ploc_merge_block(nodes, cnt, cid_in, cid_out, nn, n, tile_offs[blockIdx.x], node_base, dp, max_leaf, (int)blockIdx.x, s_warp, &tot);
-}
-
-// ---- clustering rounds driven from the device (round 2) ------------------------------------------------------------------
-// Round 1 read the survivor count back after EVERY round (16 - 43 host synchronisations per build).  Now the round's state
-// lives on the device: every kernel of a round takes the cluster count, the next node index and the ping-pong parity from
-// `PlocState`, a one-thread kernel advances it after the merge, and the host queues several rounds back to back with grids
-// sized for the count it last saw (blocks beyond the current count return at once; all kernels return once at most kTile
-// clusters are left) and reads the state back once per batch.
+// ---- one clustering round = ONE launch (round 2) -------------------------------------------------------------------------------
+// Round 1 ran four kernels per round (nearest, count, scan of the tile sums by one block, merge) and read the survivor count back
+// after every round.  Now a block does the whole round for its tile:
+//   * it loads the boxes of its kTile clusters and of 2R neighbours on either side into shared memory ONCE (the separate kernels
+//     read every box three times: nearest, and both halves of a pair in the merge), finds the nearest neighbour of its clusters
+//     and of R on either side (a partner lies within R, and mutual needs the partner's choice too) — the neighbour array never
+//     leaves the block;
+//   * the tile's position in the compacted output comes from a decoupled look-back over the per-tile (survivors, leaders) sums
+//     (Merrill & Garland, "Single-pass Parallel Prefix Scan with Decoupled Look-back", 2016) instead of a count kernel and a
+//     one-block scan: tiles are handed out by a ticket counter so that every lower tile is already running, a tile publishes
+//     its sum, then adds up its predecessors' sums until it meets one that carries an inclusive prefix.  Sums are exact
+//     integers, so node numbering is as deterministic as before;
+//   * the state of the round (cluster count, next node index, rounds so far = ping-pong parity) lives on the device in
+//     state[launch & 1]; the block of the LAST tile writes state[(launch + 1) & 1], so the host can queue several rounds back to
+//     back with grids sized for the count it last saw and read the state once per batch.  A launch that finds at most kTile
+//     clusters left only copies the state forward (k_ploc_tail finishes the build).
 struct PlocState { int32_t n; uint32_t node_base; uint32_t rounds; uint32_t stalled; };
 static_assert(sizeof(PlocState) == 16, "PlocState travels through the arena's 16-byte pinned word");
+constexpr int kMaxRoundLaunches = 4096;   // ticket counters, one per launch (51 rounds at 100 M primitives)
 
-template <int kRadius>
-__global__ void __launch_bounds__(kTile) k_ploc_nearest_s(const N2* __restrict__ nodes, const uint32_t* __restrict__ cid0, const uint32_t* __restrict__ cid1,
-                                                          const PlocState* __restrict__ st, uint32_t* __restrict__ nn)
+// look-back word: flag (2 bits: 1 = this tile's sum, 2 = inclusive prefix) | launch tag (6 bits) | leaders (28) | survivors (28)
+__device__ __forceinline__ uint64_t lb_word(const uint64_t flag, const uint32_t launch, const uint64_t sums /* survivors | leaders << 32 */)
 {
-	__shared__ float s_box[6][kTile + 2 * kRadius];
-	const int n = st->n;
-	if (n <= kTile || (int)blockIdx.x * kTile >= n) return;
-	ploc_nearest_block<kRadius, false>(nodes, (st->rounds & 1u) ? cid1 : cid0, n, nn, (int)blockIdx.x, s_box);
+	return (flag << 62) | ((uint64_t)(launch & 63u) << 56) | ((sums >> 32) << 28) | (sums & 0xfffffffull);
 }
+__device__ __forceinline__ uint64_t lb_sums(const uint64_t w) { return (w & 0xfffffffull) | (((w >> 28) & 0xfffffffull) << 32); }
 
-__global__ void __launch_bounds__(kTile) k_ploc_count_s(const uint32_t* __restrict__ nn, const PlocState* __restrict__ st, uint64_t* __restrict__ tile_sums)
+// kRoundItems clusters per thread: large tiles keep the look-back short at 10^7+ clusters (with 256-cluster tiles the blocks arrive
+// faster than a look-back of 32 tiles per L2 round trip can follow: 30.7 ms of clustering at 100 M primitives against 19.8 with
+// 1024-cluster tiles), small tiles keep all SMs busy at 10^5 (0.47 against 0.54 ms at 262 k)
+#ifndef CUPT_PLOC_ITEMS
+#define CUPT_PLOC_ITEMS 4
+#endif
+template <int kRadius, int kRoundItems>
+__global__ void __launch_bounds__(kTile, 6) k_ploc_round(N2* nodes, uint32_t* cnt, uint32_t* cid0, uint32_t* cid1, PlocState* state, const uint32_t launch,
+                                                      uint32_t* tickets, uint64_t* tile_state, Dp* dp, const uint32_t max_leaf)
 {
+	constexpr int kRoundTile = kTile * kRoundItems;
+	constexpr int W = kRoundTile + 4 * kRadius;
+	__shared__ float s_box[6][W];
+	__shared__ uint32_t s_cid[W];
+	__shared__ int8_t s_nn[kRoundTile + 2 * kRadius];            // neighbour's position minus the cluster's own (within +-R)
+	__shared__ __align__(4) uint8_t s_flag[kRoundTile];     // bit 0: survives the round, bit 4: leader (lower half of a mutual pair)
+	__shared__ uint64_t s_pref[kRoundTile / 4];                    // exclusive (survivors | leaders << 32) before every group of four positions
 	__shared__ uint64_t s_warp[kTile / 32 + 1];
-	const int n = st->n;
-	if (n <= kTile || (int)blockIdx.x * kTile >= n) return;
-	int partner;
-	const uint64_t f = ploc_flags(nn, (int)blockIdx.x * kTile + threadIdx.x, n, &partner);
-	uint64_t tot;
-	block_scan_excl(f, s_warp, &tot);
-	if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
-}
-
-__global__ void __launch_bounds__(kTile) k_scan_tiles_s(uint64_t* __restrict__ tile_sums, const PlocState* __restrict__ st, uint64_t* __restrict__ total_out)
-{
-	__shared__ uint64_t s_warp[kTile / 32 + 1];
-	const int n = st->n;
-	if (n <= kTile) return;
-	const int ntiles = (n + kTile - 1) / kTile;
-	uint64_t carry = 0;
-	for (int base = 0; base < ntiles; base += kTile * kScanRun) {
-		const int first = base + (int)threadIdx.x * kScanRun;
-		uint64_t v[kScanRun];
-		uint64_t sum = 0;
-#pragma unroll
-		for (int k = 0; k < kScanRun; ++k) { v[k] = first + k < ntiles ? tile_sums[first + k] : 0ull; sum += v[k]; }
-		uint64_t tot;
-		uint64_t run = carry + block_scan_excl(sum, s_warp, &tot);
-#pragma unroll
-		for (int k = 0; k < kScanRun; ++k) {
-			if (first + k < ntiles) tile_sums[first + k] = run;
-			run += v[k];
-		}
-		carry += tot;
+	__shared__ uint32_t s_tile;
+	__shared__ uint64_t s_off;
+	const PlocState cur = state[launch & 1u];
+	const int n = cur.n;
+	if (n <= kTile) {
+		if (blockIdx.x == 0 && threadIdx.x == 0) state[(launch + 1u) & 1u] = cur;
+		return;
 	}
-	if (threadIdx.x == 0) *total_out = carry;
-}
-
-__global__ void __launch_bounds__(kTile) k_ploc_merge_s(N2* __restrict__ nodes, uint32_t* __restrict__ cnt, uint32_t* __restrict__ cid0, uint32_t* __restrict__ cid1,
-                                                        const uint32_t* __restrict__ nn, const PlocState* __restrict__ st, const uint64_t* __restrict__ tile_offs,
-                                                        Dp* __restrict__ dp, const uint32_t max_leaf)
-{
-	__shared__ uint64_t s_warp[kTile / 32 + 1];
-	const int n = st->n;
-	if (n <= kTile || (int)blockIdx.x * kTile >= n) return;
-	const bool odd = (st->rounds & 1u) != 0u;
+	if (threadIdx.x == 0) s_tile = atomicAdd(&tickets[launch], 1u);
+	__syncthreads();
+	const int tile = (int)s_tile;
+	const int ntiles = (n + kRoundTile - 1) / kRoundTile;
+	if (tile >= ntiles) return;
+	const uint32_t* cin = (cur.rounds & 1u) ? cid1 : cid0;
+	uint32_t* cout = (cur.rounds & 1u) ? cid0 : cid1;
+	// boxes of positions [tile * kRoundTile - 2R, (tile + 1) * kRoundTile + 2R)
+	const int base = tile * kRoundTile - 2 * kRadius;
+	for (int k = threadIdx.x; k < W; k += kTile) {
+		const int g = base + k;
+		if (g >= 0 && g < n) {
+			const uint32_t c = cin[g];
+			const float4* p = reinterpret_cast<const float4*>(&nodes[c]);
+			const float4 a = p[0], b = p[1];
+			s_cid[k] = c;
+			s_box[0][k] = a.x; s_box[1][k] = a.y; s_box[2][k] = a.z;
+			s_box[3][k] = b.x; s_box[4][k] = b.y; s_box[5][k] = b.z;
+		}
+	}
+	__syncthreads();
+	// nearest neighbour of positions [tile * kRoundTile - R, (tile + 1) * kRoundTile + R): same rule as ploc_nearest_block
+	const int nn0 = tile * kRoundTile - kRadius;   // position of s_nn[0]
+	for (int k2 = threadIdx.x; k2 < kRoundTile + 2 * kRadius; k2 += kTile) {
+		const int i = nn0 + k2;
+		int bj = i;
+		bool found = false;
+		if (i >= 0 && i < n) {
+			const int li = k2 + kRadius;
+			const float lx = s_box[0][li], ly = s_box[1][li], lz = s_box[2][li], hx = s_box[3][li], hy = s_box[4][li], hz = s_box[5][li];
+			float best = 3.0e38f;
+#pragma unroll
+			for (int d = 1; d <= kRadius; ++d) {
+				const bool right_first = (((i - d) & 1) == 1) && ((i & 1) == 0);
+#pragma unroll
+				for (int side = 0; side < 2; ++side) {
+					const int off = ((side == 0) == right_first) ? d : -d;
+					const int j = i + off;
+					if (j < 0 || j >= n) continue;
+					const int lj = li + off;
+					const float a = half_area(fminf(lx, s_box[0][lj]), fminf(ly, s_box[1][lj]), fminf(lz, s_box[2][lj]),
+					                          fmaxf(hx, s_box[3][lj]), fmaxf(hy, s_box[4][lj]), fmaxf(hz, s_box[5][lj]));
+					if (a < best || !found) { best = a; bj = j; found = true; }
+				}
+			}
+		}
+		s_nn[k2] = (int8_t)(bj - i);
+	}
+	__syncthreads();
+	// survivors and leaders: thread t owns positions t, t + kTile, ... of the tile
+	int partner[kRoundItems];
+#pragma unroll
+	for (int k = 0; k < kRoundItems; ++k) {
+		const int p = k * kTile + (int)threadIdx.x;
+		const int i = tile * kRoundTile + p;
+		partner[k] = -1;
+		uint32_t fl = 0u;
+		if (i < n) {
+			const int j = i + (int)s_nn[i - nn0];
+			const bool mutual = j + (int)s_nn[j - nn0] == i;
+			if (mutual) partner[k] = j;
+			fl = (uint32_t)(!(mutual && i > j)) | ((uint32_t)(mutual && i < j) << 4);
+		}
+		s_flag[p] = (uint8_t)fl;
+	}
+	__syncthreads();
+	const uint32_t fw = threadIdx.x < kRoundTile / 4 ? reinterpret_cast<const uint32_t*>(s_flag)[threadIdx.x] : 0u;   // positions 4 t .. 4 t + 3
 	uint64_t tot;
-	ploc_merge_block(nodes, cnt, odd ? cid1 : cid0, odd ? cid0 : cid1, nn, n, tile_offs[blockIdx.x], st->node_base, dp, max_leaf, (int)blockIdx.x, s_warp, &tot);
-}
-
-__global__ void k_ploc_advance(PlocState* st, const uint64_t* __restrict__ total)
-{
-	if (st->n <= kTile) return;
-	const uint32_t valid = (uint32_t)*total, leaders = (uint32_t)(*total >> 32);
-	if (leaders == 0u || (int)(valid + leaders) != st->n) { st->stalled = 1u; st->n = 0; return; }   // (cannot happen: the smallest pair is always mutual)
-	st->n = (int32_t)valid; st->node_base += leaders; st->rounds += 1u;
+	const uint64_t ex = block_scan_excl((uint64_t)__popc(fw & 0x01010101u) | ((uint64_t)__popc(fw & 0x10101010u) << 32), s_warp, &tot);
+	if (threadIdx.x < kRoundTile / 4) s_pref[threadIdx.x] = ex;
+	// decoupled look-back (warp 0): exclusive prefix of the tile sums
+	if (threadIdx.x < 32) {
+		volatile uint64_t* ts = tile_state;
+		uint64_t excl = 0ull;
+		if (tile == 0) {
+			if (threadIdx.x == 0) ts[0] = lb_word(2ull, launch, tot);
+		} else {
+			if (threadIdx.x == 0) ts[tile] = lb_word(1ull, launch, tot);
+			int look = tile - 1;
+			for (;;) {
+				const int t = look - (int)threadIdx.x;
+				uint64_t w = 0ull;
+				bool prefix = false;
+				if (t >= 0) {
+					do { w = ts[t]; } while (((w >> 56) & 63ull) != (uint64_t)(launch & 63u) || (w >> 62) == 0ull);
+					prefix = (w >> 62) == 2ull;
+				}
+				const uint32_t pm = __ballot_sync(0xffffffffu, prefix);
+				const int first = pm ? __ffs(pm) - 1 : 32;                 // nearest predecessor that carries an inclusive prefix
+				uint64_t v = (t >= 0 && (int)threadIdx.x <= first) ? lb_sums(w) : 0ull;
+#pragma unroll
+				for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+				excl += v;
+				if (pm != 0u || look < 32) break;
+				look -= 32;
+			}
+			if (threadIdx.x == 0) ts[tile] = lb_word(2ull, launch, excl + tot);
+		}
+		if (threadIdx.x == 0) {
+			s_off = excl;
+			if (tile == ntiles - 1) {   // the round's totals: the state of the next launch
+				const uint64_t all = excl + tot;
+				const uint32_t valid = (uint32_t)all, leaders = (uint32_t)(all >> 32);
+				PlocState nx = cur;
+				if (leaders == 0u || (int)(valid + leaders) != n) { nx.stalled = 1u; nx.n = 0; }   // (cannot happen: the smallest pair is always mutual)
+				else { nx.n = (int32_t)valid; nx.node_base = cur.node_base + leaders; nx.rounds = cur.rounds + 1u; }
+				state[(launch + 1u) & 1u] = nx;
+			}
+		}
+	}
+	__syncthreads();
+	const uint64_t off = s_off;
+#pragma unroll
+	for (int k = 0; k < kRoundItems; ++k) {
+		const int p = k * kTile + (int)threadIdx.x;
+		const uint32_t fl = s_flag[p];
+		if (!(fl & 1u)) continue;
+		const uint32_t w4 = reinterpret_cast<const uint32_t*>(s_flag)[p >> 2];
+		const uint32_t below = (1u << (8 * (p & 3))) - 1u;
+		const uint64_t pos = off + s_pref[p >> 2] + ((uint64_t)__popc(w4 & 0x01010101u & below) | ((uint64_t)__popc(w4 & 0x10101010u & below) << 32));
+		const uint32_t out = (uint32_t)pos;
+		const int li = p + 2 * kRadius;
+		if (fl & 16u) {
+			const uint32_t id = cur.node_base + (uint32_t)(pos >> 32);
+			const int lp = li + (partner[k] - (tile * kRoundTile + p));
+			ploc_create_node(nodes, cnt, dp, max_leaf, id, s_cid[li], s_cid[lp],
+			                 make_float4(s_box[0][li], s_box[1][li], s_box[2][li], 0.f), make_float4(s_box[3][li], s_box[4][li], s_box[5][li], 0.f),
+			                 make_float4(s_box[0][lp], s_box[1][lp], s_box[2][lp], 0.f), make_float4(s_box[3][lp], s_box[4][lp], s_box[5][lp], 0.f));
+			cout[out] = id;
+		} else {
+			cout[out] = s_cid[li];
+		}
+	}
 }
 
 // The last rounds in ONE launch: once at most kTile clusters are left, a single block runs nearest / merge round after round
@@ -526,47 +633,25 @@ __global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__
 
 __device__ __forceinline__ int dev_float_exponent(const float v) { return (int)((__float_as_uint(v) >> 23) & 0xffu) - 127; }
 
-__device__ __forceinline__ void write_prim(const int32_t prim, const int64_t nt, const float* __restrict__ verts, const cupt_triangle* __restrict__ tris,
-                                           const float4* __restrict__ spheres, const uint32_t* __restrict__ rank, float4* __restrict__ out)
-{
-	float4 r0, r1, r2;
-	if (prim < nt) {
-		const cupt_triangle t = tris[prim];
-		const float* a = verts + 3 * (size_t)t.v0; const float* b = verts + 3 * (size_t)t.v1; const float* c = verts + 3 * (size_t)t.v2;
-		const float v0x = a[0], v0y = a[1], v0z = a[2];
-		const float e1x = __fsub_rn(b[0], v0x), e1y = __fsub_rn(b[1], v0y), e1z = __fsub_rn(b[2], v0z);   // modelLoader.h:57-58
-		const float e2x = __fsub_rn(c[0], v0x), e2y = __fsub_rn(c[1], v0y), e2z = __fsub_rn(c[2], v0z);
-		r0 = make_float4(v0x, v0y, v0z, e1x);
-		r1 = make_float4(e1y, e1z, e2x, e2y);
-		r2 = make_float4(e2z, __uint_as_float((uint32_t)prim), __uint_as_float(rank ? rank[prim] : (uint32_t)prim), __uint_as_float(0u));
-	} else {
-		const float4 s = spheres[3 * (size_t)(prim - nt)];
-		r0 = make_float4(s.x, s.y, s.z, s.w);
-		r1 = make_float4(0.f, 0.f, 0.f, 0.f);
-		r2 = make_float4(0.f, __uint_as_float((uint32_t)(prim - nt)), __uint_as_float((uint32_t)prim), __uint_as_float(1u));
-	}
-	out[0] = r0; out[1] = r1; out[2] = r2;
-}
-
 struct EmitArgs {
 	const N2* nodes; const uint32_t* cnt; const Dp* dp; const int32_t* items; int n_items; uint32_t max_leaf;
 	const uint64_t* item_prefix; const int32_t* item_kids; const uint64_t* tile_offs;
 	uint32_t level_base, next_base, prim_base;
 	int32_t* next_items; Node8* out_nodes; float4* out_prims;
 	int32_t* rec_prim;   // primitive of every record, in record order (k_emit_prims)
-	const float* verts; const cupt_triangle* tris; const float4* spheres; const uint32_t* rank; int64_t nt;
 	double inv_root_area; double* sah;
 };
 
-// The 48-byte records, one thread per record: gathers of the triangle and its vertices, consecutive stores.  (Written from
-// k_collapse_emit — one thread per WIDE NODE, up to 24 records in a row behind dependent gathers — this was most of that
-// kernel's 9 ms per 30 M primitives.)
-__global__ void __launch_bounds__(kTile) k_emit_prims(const int32_t* __restrict__ rec_prim, const int64_t N, const int64_t nt, const float* __restrict__ verts,
-                                                      const cupt_triangle* __restrict__ tris, const float4* __restrict__ spheres, const uint32_t* __restrict__ rank,
+// The 48-byte records in tree order, one thread per record: one 48-byte piece from the primitive-order array k_leaf_boxes wrote.
+__global__ void __launch_bounds__(kTile) k_emit_prims(const int32_t* __restrict__ rec_prim, const int64_t N, const float4* __restrict__ records,
                                                       float4* __restrict__ out_prims)
 {
 	const int64_t r = (int64_t)blockIdx.x * kTile + threadIdx.x;
-	if (r < N) write_prim(rec_prim[r], nt, verts, tris, spheres, rank, out_prims + 3 * (size_t)r);
+	if (r >= N) return;
+	const float4* src = records + 3 * (size_t)rec_prim[r];
+	const float4 r0 = __ldg(src), r1 = __ldg(src + 1), r2 = __ldg(src + 2);
+	float4* dst = out_prims + 3 * (size_t)r;
+	dst[0] = r0; dst[1] = r1; dst[2] = r2;
 }
 
 // One wide node per EIGHT lanes, lane q of the group = child q of the cut (round 1: one thread per wide node with the 8 x 8
@@ -780,9 +865,9 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	const int sort_passes = std::min(8, (log2n + 9 + 7) / 8);
 	// everything the build touches except its two outputs, in one arena; the sort buffers are dead once the sorted
 	// leaves are written, the collapse reuses the cluster arrays for its level queues
-	const size_t need = up256(n * sizeof(N2)) + up256(64) + 2 * up256(n * 8) + 2 * up256(n * 4) + up256(temp_bytes + 256)
+	const size_t need = up256(n * sizeof(N2)) + up256(n * 48) + up256(64) + 2 * up256(n * 8) + 2 * up256(n * 4) + up256(temp_bytes + 256)
 	                    + up256(2 * n * sizeof(N2)) + up256(2 * n * sizeof(Dp)) + up256(2 * n * 4) + 3 * up256(n * 4) + up256(((size_t)tilesN + 1) * 8) + up256(64)
-	                    + up256((n / 2 + 2) * 8) + up256((n / 2 + 2) * 32) + up256(64) + 4096;
+	                    + up256((n / 2 + 2) * 8) + up256((n / 2 + 2) * 32) + up256(64) + up256(kMaxRoundLaunches * 4) + 4096;
 	int rc;
 	if ((rc = arena.reserve(need))) return rc;
 	cudaEvent_t* ev = arena.ev;
@@ -790,6 +875,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 
 	// 1-2: boxes, Morton codes, sort
 	N2* leaf = take<N2>(arena, n);
+	float4* records = take<float4>(arena, 3 * n);
 	uint32_t* cbounds = take<uint32_t>(arena, 6);
 	uint64_t* keys[2]; uint32_t* vals[2];
 	for (int b = 0; b < 2; ++b) keys[b] = take<uint64_t>(arena, n);
@@ -798,7 +884,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	static const uint32_t cb_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
 	CKB(cudaEventRecord(ev[0], st));
 	CKB(cudaMemcpyAsync(cbounds, cb_init, sizeof(cb_init), cudaMemcpyHostToDevice, st));
-	k_leaf_boxes<<<std::min(tilesN, 148 * 16), kTile, 0, st>>>(verts, tris, nt, spheres, N, leaf, cbounds);
+	k_leaf_boxes<<<std::min(tilesN, 148 * 16), kTile, 0, st>>>(verts, tris, nt, spheres, rank, N, leaf, records, cbounds);
 	k_morton<<<tilesN, kTile, 0, st>>>(leaf, N, cbounds, keys[0], vals[0]);
 	const int sorted = rsort::sort_pairs(st, keys, vals, (uint32_t)N, sort_passes, reinterpret_cast<uint32_t*>(temp));
 	CKB(cudaEventRecord(ev[1], st));
@@ -814,36 +900,43 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	uint64_t* item_counts = take<uint64_t>(arena, n / 2 + 2);
 	int32_t* item_kids = take<int32_t>(arena, (n / 2 + 2) * 8);
 	double* d_sah = take<double>(arena, 1);
+	uint32_t* tickets = take<uint32_t>(arena, kMaxRoundLaunches);
 	if (arena.off > arena.cap) return set_error(CUPT_ERR_CUDA, "internal: BVH build workspace undersized (%zu > %zu)", arena.off, arena.cap);
 	k_sorted_leaves<<<tilesN, kTile, 0, st>>>(leaf, vals[sorted], N, nodes, cnt, cid[0]);
 	int cn = (int)N, cur = 0, rounds = 0;
 	uint32_t node_base = (uint32_t)N;
 	if (cn > kTile) {
-		PlocState* d_state = reinterpret_cast<PlocState*>(item_counts);   // (the collapse's per-item counts are not in use yet)
+		PlocState* d_state = reinterpret_cast<PlocState*>(item_counts);   // state[2] (the collapse's per-item counts are not in use yet)
 		PlocState* h_state = reinterpret_cast<PlocState*>(h_total);
 		h_state->n = cn; h_state->node_base = node_base; h_state->rounds = 0u; h_state->stalled = 0u;
 		CKB(cudaMemcpyAsync(d_state, h_state, sizeof(PlocState), cudaMemcpyHostToDevice, st));
+		CKB(cudaMemsetAsync(tickets, 0, kMaxRoundLaunches * sizeof(uint32_t), st));
+		CKB(cudaMemsetAsync(tile_sums, 0, ((size_t)tilesN + 1) * sizeof(uint64_t), st));
 		int bound = cn;
+		uint32_t launch = 0;
 		while (bound > kTile) {
 			const int tiles = (bound + kTile - 1) / kTile;
-			// rounds per read-back: clusters shrink by a third to a half per round, so a batch's later rounds launch up to ~3 x the
+			// rounds per read-back: clusters shrink by a quarter to a half per round, so a batch's later rounds launch up to ~3 x the
 			// blocks they need; cheap when the grids are small (where the synchronisation is what costs), not at 10^5 tiles
 			const int batch = tiles >= 32768 ? 1 : (tiles >= 4096 ? 2 : (tiles >= 512 ? 4 : 8));
-			for (int b = 0; b < batch; ++b) {
+			if (launch + (uint32_t)batch > (uint32_t)kMaxRoundLaunches) return set_error(CUPT_ERR_LIMIT, "PLOC needs more than %d rounds", kMaxRoundLaunches);
+			const int items = bound >= (1 << 20) ? CUPT_PLOC_ITEMS : 1;
+			const int grid = (bound + kTile * items - 1) / (kTile * items);
+			for (int b = 0; b < batch; ++b, ++launch) {
+#define CUPT_ROUND(R)                                                                                                                                        \
+	if (items == CUPT_PLOC_ITEMS) k_ploc_round<R, CUPT_PLOC_ITEMS><<<grid, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], d_state, launch, tickets, tile_sums, dp, (uint32_t)max_leaf); \
+	else k_ploc_round<R, 1><<<grid, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], d_state, launch, tickets, tile_sums, dp, (uint32_t)max_leaf);
 				switch (radius) {
-				case 32: k_ploc_nearest_s<32><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
-				case 16: k_ploc_nearest_s<16><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
-				case 8: k_ploc_nearest_s<8><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
-				case 2: k_ploc_nearest_s<2><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
-				case 1: k_ploc_nearest_s<1><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
-				default: k_ploc_nearest_s<4><<<tiles, kTile, 0, st>>>(nodes, cid[0], cid[1], d_state, nn); break;
+				case 32: CUPT_ROUND(32) break;
+				case 16: CUPT_ROUND(16) break;
+				case 8: CUPT_ROUND(8) break;
+				case 2: CUPT_ROUND(2) break;
+				case 1: CUPT_ROUND(1) break;
+				default: CUPT_ROUND(4) break;
 				}
-				k_ploc_count_s<<<tiles, kTile, 0, st>>>(nn, d_state, tile_sums);
-				k_scan_tiles_s<<<1, kTile, 0, st>>>(tile_sums, d_state, d_total);
-				k_ploc_merge_s<<<tiles, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, d_state, tile_sums, dp, (uint32_t)max_leaf);
-				k_ploc_advance<<<1, 1, 0, st>>>(d_state, d_total);
+#undef CUPT_ROUND
 			}
-			CKB(cudaMemcpyAsync(h_state, d_state, sizeof(PlocState), cudaMemcpyDeviceToHost, st));
+			CKB(cudaMemcpyAsync(h_state, d_state + (launch & 1u), sizeof(PlocState), cudaMemcpyDeviceToHost, st));
 			CKB(cudaStreamSynchronize(st));
 			if (h_state->stalled || h_state->n >= bound || h_state->n < 1)
 				return set_error(CUPT_ERR_CUDA, "internal: PLOC made no progress (clusters %d -> %d after %u rounds)", bound, h_state->n, h_state->rounds);
@@ -913,7 +1006,6 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 		A.level_base = level_base; A.next_base = level_base + (uint32_t)n_items; A.prim_base = prim_base;
 		A.next_items = items[lvl ^ 1]; A.out_nodes = static_cast<Node8*>(out->nodes); A.out_prims = static_cast<float4*>(out->prims);
 		A.rec_prim = reinterpret_cast<int32_t*>(nn);   // (the PLOC neighbour array is free by now)
-		A.verts = verts; A.tris = tris; A.spheres = spheres; A.rank = rank; A.nt = nt;
 		A.inv_root_area = 1.0 / root_area; A.sah = d_sah;
 		k_collapse_emit<<<(n_items + kTile / 8 - 1) / (kTile / 8), kTile, 0, st>>>(A);
 		CKB(cudaMemcpyAsync(h_total, d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
@@ -925,7 +1017,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 		// the same bound cupt_set_bvh applies: the extend kernel's shared-memory stack holds `depth` entries per thread
 		if (depth > 64) return set_error(CUPT_ERR_LIMIT, "wide BVH deeper than 64 levels (the traversal stack's limit, as for cupt_set_bvh)");
 	}
-	k_emit_prims<<<tilesN, kTile, 0, st>>>(reinterpret_cast<const int32_t*>(nn), N, nt, verts, tris, spheres, rank, static_cast<float4*>(out->prims));
+	k_emit_prims<<<tilesN, kTile, 0, st>>>(reinterpret_cast<const int32_t*>(nn), N, records, static_cast<float4*>(out->prims));
 	CKB(cudaEventRecord(ev[3], st));
 	double sah = 0;
 	CKB(cudaMemcpyAsync(&sah, d_sah, sizeof(double), cudaMemcpyDeviceToHost, st));

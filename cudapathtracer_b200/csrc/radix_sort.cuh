@@ -207,8 +207,9 @@ inline int sort_pairs(cudaStream_t st, uint64_t* keys[2], uint32_t* vals[2], con
 	const uint32_t stiles = (hist_n + kScanTile - 1) / kScanTile;
 	uint32_t* hist = scratch;
 	uint32_t* tile_sums = scratch + hist_n;
-	static bool attr_set = false;   // 50 KB of dynamic shared memory: above the 48 KB default
-	if (!attr_set) { cudaFuncSetAttribute(k_radix_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem); attr_set = true; }
+	// 50 KB of dynamic shared memory: above the 48 KB default.  Per call, not once per process: the attribute belongs to the current
+	// DEVICE, and a process may build on several (cupt_group)
+	cudaFuncSetAttribute(k_radix_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem);
 	int cur = 0;
 	for (int p = 0; p < passes; ++p) {
 		const int shift = 63 - 8 * (passes - p);

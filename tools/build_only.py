@@ -10,6 +10,11 @@ sc = scenes.triangle_soup(n) if os.environ.get("SCENE", "soup") == "soup" else s
 s = api.SceneHandle(); s.add_scene(sc)
 ctx = api.Context(0)
 ctx.set_scene(s)
+if os.environ.get("L2FETCH"):   # experiment: cudaLimitMaxL2FetchGranularity (0x05), a hint of 32 / 64 / 128 bytes
+    import ctypes as C
+    rt = C.CDLL("libcudart.so.12")
+    print("cudaDeviceSetLimit ->", rt.cudaDeviceSetLimit(5, C.c_size_t(int(os.environ["L2FETCH"]))))
+    v = C.c_size_t(0); rt.cudaDeviceGetLimit(C.byref(v), 5); print("L2 fetch granularity now", v.value)
 for _ in range(int(os.environ.get("REPS", "2"))):
     info = ctx.build_bvh_device()
 print({k: (round(v, 3) if isinstance(v, float) else v) for k, v in info.items()})
