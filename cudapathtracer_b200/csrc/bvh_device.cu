@@ -631,6 +631,7 @@ __global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__
 	if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
 }
 
+__device__ __forceinline__ double pow2_double(const int e) { return __hiloint2double((1023 + e) << 20, 0); }   // 2^e, -1022 <= e <= 1023
 __device__ __forceinline__ int dev_float_exponent(const float v) { return (int)((__float_as_uint(v) >> 23) & 0xffu) - 127; }
 
 struct EmitArgs {
@@ -676,7 +677,7 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 			const float4 a = __ldg(p), b = __ldg(p + 1);
 			blo[0] = a.x; blo[1] = a.y; blo[2] = a.z; bhi[0] = b.x; bhi[1] = b.y; bhi[2] = b.z;
 		}
-		float cost[8];
+		float cost[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 		if (kid >= 0) {
 			const float4* p = reinterpret_cast<const float4*>(&A.nodes[kid]);
 			const float4 a = __ldg(p), b = __ldg(p + 1);
@@ -685,29 +686,31 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 #pragma unroll
 			for (int a3 = 0; a3 < 3; ++a3) d[a3] = (0.5f * clo[a3] + 0.5f * chi[a3]) - (0.5f * blo[a3] + 0.5f * bhi[a3]);
 #pragma unroll
-			for (int sl = 0; sl < 8; ++sl) cost[sl] = ((sl & 4) ? d[0] : -d[0]) + ((sl & 2) ? d[1] : -d[1]) + ((sl & 1) ? d[2] : -d[2]);
-		}
+			for (int sl = 0; sl < 8; ++sl) cost[sl] = (((sl & 4) ? d[0] : -d[0]) + ((sl & 2) ? d[1] : -d[1]) + ((sl & 1) ? d[2] : -d[2])) + 0.0f;   // (+ 0: no -0, so that
+		}                                                                                                                                   //  the integer order below is the float order)
 		// greedy octant slots
 		const uint32_t nk = (uint32_t)__popc(__ballot_sync(gmask, kid >= 0) & gmask);
-		uint32_t free_slots = 0xffu;
+		// Per round: every unassigned child's best free slot (largest cost, lowest slot on a tie; a taken slot's cost is -inf in every
+		// lane), then the group's winner — largest cost, lowest child on a tie: one integer max-reduction over the order-preserving
+		// image of the cost and a ballot — takes its slot.  (The first version of this kernel spent 47 % of its instructions here on a
+		// slot-by-slot scan with a free mask and a three-value butterfly: profiles/r2w_builder_metrics.md.)
 		int slot = -1;
 		for (uint32_t it = 0; it < nk; ++it) {
-			float bc = -3.0e38f; int bs = -1;
-			if (kid >= 0 && slot < 0) {
+			const bool cand = kid >= 0 && slot < 0;
+			const float m = fmaxf(fmaxf(fmaxf(cost[0], cost[1]), fmaxf(cost[2], cost[3])), fmaxf(fmaxf(cost[4], cost[5]), fmaxf(cost[6], cost[7])));
+			int bs = 7;
 #pragma unroll
-				for (int sl = 0; sl < 8; ++sl)
-					if (((free_slots >> sl) & 1u) && (cost[sl] > bc || bs < 0)) { bc = cost[sl]; bs = sl; }
-			}
-			// the group's winner: largest cost, lowest child index on a tie (the serial loop's strict `>`); a lane without a candidate never wins
-			float wc = bc; int wq = bs >= 0 ? (int)q : 99, ws = bs;
+			for (int sl = 6; sl >= 0; --sl)
+				if (cost[sl] == m) bs = sl;
+			const uint32_t key = cand ? f2ord(m) : 0u;   // (f2ord of a finite float is never 0)
+			const uint32_t top = __reduce_max_sync(gmask, key);
+			const uint32_t winners = __ballot_sync(gmask, cand && key == top) & gmask;
+			const int wl = __ffs(winners) - 1;             // lowest lane = lowest child index
+			const int ws = __shfl_sync(gmask, bs, wl);
+			if ((int)lane == wl) slot = ws;
 #pragma unroll
-			for (int o = 4; o > 0; o >>= 1) {
-				const float oc = __shfl_xor_sync(gmask, wc, o); const int oq = __shfl_xor_sync(gmask, wq, o), os = __shfl_xor_sync(gmask, ws, o);
-				const bool take = oq < 99 && (wq == 99 || oc > wc || (oc == wc && oq < wq));
-				if (take) { wc = oc; wq = oq; ws = os; }
-			}
-			if ((int)q == wq) slot = ws;
-			free_slots &= ~(1u << ws);
+			for (int sl = 0; sl < 8; ++sl)
+				if (sl == ws) cost[sl] = -INFINITY;
 		}
 		// quantisation grid: power-of-two cell per axis, at least 2^-24 of the coordinate magnitude (every lane: the same values)
 		double scale[3], inv_scale[3];
@@ -718,14 +721,14 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 			int e = -126;
 			if (ext > 0) {
 				e = ((__double2hiint(ext) >> 20) & 0x7ff) - 1023 - 8;   // 2^k <= ext < 2^(k+1): 255 * 2^(k-8) < ext, at most two steps up
-				while (ldexp(255.0, e) < ext) ++e;
+				while (255.0 * pow2_double(e) < ext) ++e;
 			}
 			const float m = fmaxf(fabsf(blo[a]), fabsf(bhi[a]));
 			e = max(e, dev_float_exponent(m) - 24);
 			e = max(-126, min(127, e));
 			ebits |= (uint32_t)(e + 127) << (8 * a);
-			scale[a] = ldexp(1.0, e);
-			inv_scale[a] = ldexp(1.0, -e);
+			scale[a] = pow2_double(e);
+			inv_scale[a] = pow2_double(-e);
 		}
 		// this child's record count / kind, and what lies before it in SLOT order
 		const uint32_t cc = kid >= 0 ? A.cnt[kid] : 0u;
@@ -762,18 +765,20 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 				sah += area2 * A.inv_root_area;
 			} else {
 				my_pvalid = (cc == 1 ? 1u : (cc == 2 ? 3u : 7u)) << (4 * slot);
-				int32_t stack[4]; int sp = 0;
-				stack[sp++] = kid;
-				uint32_t w = 0;
-				while (sp > 0) {                       // <= 3 primitives: left-first walk of the tiny subtree
-					const int32_t x = stack[--sp];
-					const int32_t l = A.nodes[x].left;
-					if (l < 0) {
-						A.rec_prim[tri_base + prims_before + w] = -1 - l;   // the record itself is written by k_emit_prims
-						++w;
-					} else {
-						stack[sp++] = A.nodes[x].right; stack[sp++] = l;
-					}
+				// <= 3 primitives: the tiny subtree is at most two levels deep; left first (the records themselves are written by k_emit_prims)
+				int32_t* dst = A.rec_prim + tri_base + prims_before;
+				const int32_t l0 = A.nodes[kid].left;
+				if (l0 < 0) {
+					dst[0] = -1 - l0;
+				} else {
+					const int32_t r0 = A.nodes[kid].right;
+					uint32_t w = 0;
+					const int32_t ll = A.nodes[l0].left;
+					if (ll < 0) dst[w++] = -1 - ll;
+					else { dst[w++] = -1 - A.nodes[ll].left; dst[w++] = -1 - A.nodes[A.nodes[l0].right].left; }
+					const int32_t rl = A.nodes[r0].left;
+					if (rl < 0) dst[w++] = -1 - rl;
+					else { dst[w++] = -1 - A.nodes[rl].left; dst[w++] = -1 - A.nodes[A.nodes[r0].right].left; }
 				}
 				sah += area2 * A.inv_root_area * cc;
 			}

@@ -4,9 +4,9 @@
 //   k_radix_hist     one block per tile of 4096 pairs: digit histogram in shared memory -> hist[digit][tile]
 //   scan             exclusive prefix sum over hist in digit-major order (k_scan32_reduce, k_scan32_tiles,
 //                    k_scan32_apply), which turns it into the global start of every (digit, tile) run
-//   k_radix_scatter  one block per tile, each warp owns 512 consecutive pairs: __match_any_sync ranks equal digits
-//                    inside a round of 32, a warp-private counter array carries the rank across the 16 rounds, a
-//                    prefix over the 8 warps per digit gives the place inside the tile's run.  Order inside a run is
+//   k_radix_scatter  one block per tile, each warp owns 256 consecutive pairs: __match_any_sync ranks equal digits
+//                    inside a round of 32, a warp-private counter array carries the rank across the 8 rounds, a
+//                    prefix over the 16 warps per digit gives the place inside the tile's run.  Order inside a run is
 //                    (warp, round, lane) = memory order, so the sort is stable.  The tile is put in sorted order in
 //                    shared memory first and written out from there, so that a warp's stores are consecutive
 //                    addresses inside the digits' runs.
@@ -119,27 +119,32 @@ __global__ void __launch_bounds__(kThreads) k_scan32_apply(uint32_t* __restrict_
 // Dynamic shared memory of k_radix_scatter: the tile's pairs in sorted order (keys, values), then per digit the offset that
 // turns a position inside the sorted tile into a global position.
 constexpr size_t kScatterSmem = (size_t)kTileN * (sizeof(uint64_t) + sizeof(uint32_t)) + 256 * sizeof(uint32_t);
+// 512 threads x 8 pairs (round 1: 256 x 16 — 100 registers and 58 KB of shared memory per block left two blocks = 16 warps per SM,
+// issue slots 11 % busy, DRAM at 19 % of its peak: profiles/r2w_builder_metrics.md)
+constexpr int kScThreads = 512;
+constexpr int kScItems = kTileN / kScThreads;
+constexpr int kScWarps = kScThreads / 32;
 
-__global__ void __launch_bounds__(kThreads) k_radix_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                                                            uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, const uint32_t n,
-                                                            const int shift, const uint32_t* __restrict__ offs, const uint32_t ntiles)
+__global__ void __launch_bounds__(kScThreads, 2) k_radix_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                                 uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, const uint32_t n,
+                                                                 const int shift, const uint32_t* __restrict__ offs, const uint32_t ntiles)
 {
 	extern __shared__ uint64_t s_dyn[];
 	uint64_t* s_key = s_dyn;                                                   // [kTileN] the tile in sorted order
 	uint32_t* s_val = reinterpret_cast<uint32_t*>(s_dyn + kTileN);             // [kTileN]
 	uint32_t* s_gofs = s_val + kTileN;                                         // [256] global start of the digit's run - its start inside the sorted tile
-	__shared__ uint32_t s_cnt[kWarps][256];   // per warp: pairs seen so far per digit; later: the warp's start inside the sorted tile
-	__shared__ uint32_t s_w[kWarps + 1];
+	__shared__ uint32_t s_cnt[kScWarps][256];   // per warp: pairs seen so far per digit; later: the warp's start inside the sorted tile
+	__shared__ uint32_t s_w[kScWarps + 1];
 	const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
 	const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
-	for (int i = 0; i < kWarps; ++i) s_cnt[i][threadIdx.x] = 0u;
+	for (int i = 0; i < kScWarps * 256 / kScThreads; ++i) (&s_cnt[0][0])[i * kScThreads + threadIdx.x] = 0u;
 	__syncthreads();
-	const uint32_t wbase = blockIdx.x * (uint32_t)kTileN + w * (uint32_t)(kItems * 32);
-	uint64_t key[kItems];
-	uint32_t rank[kItems];
+	const uint32_t wbase = blockIdx.x * (uint32_t)kTileN + w * (uint32_t)(kScItems * 32);
+	uint64_t key[kScItems];
+	uint32_t rank[kScItems];
 #pragma unroll
-	for (int i = 0; i < kItems; ++i) {
+	for (int i = 0; i < kScItems; ++i) {
 		const uint32_t idx = wbase + (uint32_t)i * 32u + lane;
 		const bool valid = idx < n;
 		key[i] = valid ? keys_in[idx] : ~0ull;
@@ -153,21 +158,35 @@ __global__ void __launch_bounds__(kThreads) k_radix_scatter(const uint64_t* __re
 		__syncwarp();
 	}
 	__syncthreads();
-	{   // thread t = digit t: the digit's start inside the sorted tile (exclusive scan of the tile's digit counts), the warps'
-		// starts behind it, and the offset to the global run of this (digit, tile)
-		uint32_t c[kWarps], tot = 0u;
+	{   // thread t < 256 = digit t: the digit's start inside the sorted tile (exclusive scan of the tile's digit counts), the warps'
+		// starts behind it, and the offset to the global run of this (digit, tile); threads 256.. only take part in the scan
+		const bool digit = threadIdx.x < 256u;
+		uint32_t tot = 0u;
+		if (digit) {
 #pragma unroll
-		for (int i = 0; i < kWarps; ++i) { c[i] = s_cnt[i][threadIdx.x]; tot += c[i]; }
-		uint32_t all;
-		uint32_t run = block_excl32(tot, s_w, &all);
-		s_gofs[threadIdx.x] = offs[(size_t)threadIdx.x * ntiles + blockIdx.x] - run;
+			for (int i = 0; i < kScWarps; ++i) tot += s_cnt[i][threadIdx.x];
+		}
+		// exclusive scan over the block (kScWarps warps)
+		const uint32_t incl = warp_incl32(tot);
+		if (lane == 31u) s_w[w] = incl;
+		__syncthreads();
+		if (w == 0u) {
+			const uint32_t x = lane < (uint32_t)kScWarps ? s_w[lane] : 0u;
+			const uint32_t xi = warp_incl32(x);
+			if (lane < (uint32_t)kScWarps) s_w[lane] = xi - x;
+		}
+		__syncthreads();
+		if (digit) {
+			uint32_t run = s_w[w] + incl - tot;
+			s_gofs[threadIdx.x] = offs[(size_t)threadIdx.x * ntiles + blockIdx.x] - run;
 #pragma unroll
-		for (int i = 0; i < kWarps; ++i) { s_cnt[i][threadIdx.x] = run; run += c[i]; }
+			for (int i = 0; i < kScWarps; ++i) { const uint32_t c = s_cnt[i][threadIdx.x]; s_cnt[i][threadIdx.x] = run; run += c; }
+		}
 	}
 	__syncthreads();
 	// the tile in sorted order in shared memory: order inside a digit is (warp, round, lane) = memory order, so the sort is stable
 #pragma unroll
-	for (int i = 0; i < kItems; ++i) {
+	for (int i = 0; i < kScItems; ++i) {
 		const uint32_t idx = wbase + (uint32_t)i * 32u + lane;
 		if (idx < n) {
 			const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
@@ -182,7 +201,7 @@ __global__ void __launch_bounds__(kThreads) k_radix_scatter(const uint64_t* __re
 	// pairs, 350 GB/s)
 	const uint32_t tile_n = min((uint32_t)kTileN, n - blockIdx.x * (uint32_t)kTileN);
 #pragma unroll 4
-	for (uint32_t j = threadIdx.x; j < tile_n; j += kThreads) {
+	for (uint32_t j = threadIdx.x; j < tile_n; j += kScThreads) {
 		const uint64_t k = s_key[j];
 		const uint32_t pos = s_gofs[(uint32_t)(k >> shift) & 255u] + j;
 		keys_out[pos] = k;
@@ -217,7 +236,7 @@ inline int sort_pairs(cudaStream_t st, uint64_t* keys[2], uint32_t* vals[2], con
 		k_scan32_reduce<<<stiles, kThreads, 0, st>>>(hist, hist_n, tile_sums);
 		k_scan32_tiles<<<1, kThreads, 0, st>>>(tile_sums, stiles);
 		k_scan32_apply<<<stiles, kThreads, 0, st>>>(hist, hist_n, tile_sums);
-		k_radix_scatter<<<ntiles, kThreads, kScatterSmem, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift < 0 ? 0 : shift, hist, ntiles);
+		k_radix_scatter<<<ntiles, kScThreads, kScatterSmem, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift < 0 ? 0 : shift, hist, ntiles);
 		cur ^= 1;
 	}
 	return cur;

@@ -18,3 +18,7 @@ if os.environ.get("L2FETCH"):   # experiment: cudaLimitMaxL2FetchGranularity (0x
 for _ in range(int(os.environ.get("REPS", "2"))):
     info = ctx.build_bvh_device()
 print({k: (round(v, 3) if isinstance(v, float) else v) for k, v in info.items()})
+if os.environ.get("HASH") and n <= 40_000_000:   # the tree's bytes (nodes + records), to check that a builder change leaves the trees as they were
+    import hashlib
+    nodes, prims, *_ = ctx.read_bvh()
+    print("tree sha1", hashlib.sha1(nodes.tobytes()).hexdigest()[:16], hashlib.sha1(prims.tobytes()).hexdigest()[:16])
