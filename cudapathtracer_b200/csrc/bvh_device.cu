@@ -140,13 +140,38 @@ __global__ void __launch_bounds__(kTile) k_morton(const N2* __restrict__ leaf, c
 	keys[i] = code; vals[i] = (uint32_t)i;
 }
 
+// ---- the binary tree ---------------------------------------------------------------------------------------------------------
+// Leaves are nodes 0..N-1 in Morton order (32 bytes: box, left = -1 - primitive); inner node id >= N is inner[id - N], ONE 64-byte
+// record: box, children, the collapse costs of its subtree (Dp below) and, in bits 24..26 of `splits`, its primitive count
+// saturated at 7 (all anybody asks is "at most max_leaf <= 3?" and, if so, how many).  Round 1 kept boxes + children, costs and
+// counts in three arrays: every node visited by the clustering's merge or by the collapse's cut walk was three random 128-byte
+// line fetches instead of one (profiles/r2w_builder_metrics.md: k_collapse_count at 66 % of the DRAM peak for 740 bytes per item).
+struct alignas(16) Inner { float lo[3]; int32_t left; float hi[3]; int32_t right; float c[7]; uint32_t splits; };
+static_assert(sizeof(Inner) == 64, "one inner node = half a cache line");
+struct Tree {
+	N2* leaf; Inner* inner; uint32_t N;
+	__device__ __forceinline__ const float4* rec(const uint32_t id) const
+	{
+		return id < N ? reinterpret_cast<const float4*>(leaf + id) : reinterpret_cast<const float4*>(inner + (id - N));
+	}
+	__device__ __forceinline__ int32_t left(const uint32_t id) const { return id < N ? leaf[id].left : inner[id - N].left; }
+	__device__ __forceinline__ int32_t right(const uint32_t id) const { return id < N ? leaf[id].right : inner[id - N].right; }
+	__device__ __forceinline__ uint32_t count(const uint32_t id) const { return id < N ? 1u : (inner[id - N].splits >> 24) & 7u; }
+};
+
+// the sorted leaves, and the first round's cluster list: cluster i = leaf i, its box in cbox (every round reads the clusters' boxes
+// from such a list in cluster order — a stream — instead of through the node indices)
 __global__ void __launch_bounds__(kTile) k_sorted_leaves(const N2* __restrict__ leaf, const uint32_t* __restrict__ order, const int64_t N,
-                                                         N2* __restrict__ nodes, uint32_t* __restrict__ cnt, uint32_t* __restrict__ cid)
+                                                         N2* __restrict__ sorted, N2* __restrict__ cbox, uint32_t* __restrict__ cid)
 {
 	const int64_t i = (int64_t)blockIdx.x * kTile + threadIdx.x;
 	if (i >= N) return;
-	nodes[i] = leaf[order[i]];
-	cnt[i] = 1u; cid[i] = (uint32_t)i;
+	const float4* src = reinterpret_cast<const float4*>(&leaf[order[i]]);
+	const float4 a = __ldg(src), b = __ldg(src + 1);
+	float4* d0 = reinterpret_cast<float4*>(&sorted[i]);
+	float4* d1 = reinterpret_cast<float4*>(&cbox[i]);
+	d0[0] = a; d0[1] = b; d1[0] = a; d1[1] = b;
+	cid[i] = (uint32_t)i;
 }
 
 // ---- exclusive scan of per-tile 64-bit sums (two 32-bit counters packed in one word), one block -------------------
@@ -207,22 +232,21 @@ __global__ void __launch_bounds__(kTile) k_scan_tiles(uint64_t* __restrict__ til
 // Nearest neighbour of cluster i among positions i-R..i+R by the half-area of the union box.  Ties are broken by a
 // strict total order on UNORDERED pairs — (area, |i-j|, min(i,j) odd, min(i,j)) — so the globally smallest pair is
 // always mutual (progress every round) and a run of identical boxes pairs up as (0,1)(2,3)... instead of chaining.
-// TAIL = called from k_ploc_tail, which reads what it wrote itself a round earlier: plain loads instead of ld.global.nc
-template <int kRadius, bool TAIL>
-__device__ __forceinline__ void ploc_nearest_block(const N2* nodes, const uint32_t* cid, const int n, uint32_t* nn, const int block, float (*s_box)[kTile + 2 * kRadius])
+// (k_ploc_tail's version: one block, plain loads of what it wrote itself a round earlier)
+template <int kRadius>
+__device__ __forceinline__ void ploc_nearest_block(const N2* cbox, const int n, uint32_t* nn, float (*s_box)[kTile + 2 * kRadius])
 {
-	const int base = block * kTile - kRadius;
 	for (int k = threadIdx.x; k < kTile + 2 * kRadius; k += kTile) {
-		const int g = base + k;
+		const int g = k - kRadius;
 		if (g >= 0 && g < n) {
-			const float4* p = reinterpret_cast<const float4*>(&nodes[cid[g]]);
-			const float4 a = TAIL ? p[0] : __ldg(p), b = TAIL ? p[1] : __ldg(p + 1);
+			const float4* p = reinterpret_cast<const float4*>(&cbox[g]);
+			const float4 a = p[0], b = p[1];
 			s_box[0][k] = a.x; s_box[1][k] = a.y; s_box[2][k] = a.z;
 			s_box[3][k] = b.x; s_box[4][k] = b.y; s_box[5][k] = b.z;
 		}
 	}
 	__syncthreads();
-	const int i = block * kTile + threadIdx.x;
+	const int i = threadIdx.x;
 	if (i >= n) return;
 	const int li = threadIdx.x + kRadius;
 	const float lx = s_box[0][li], ly = s_box[1][li], lz = s_box[2][li], hx = s_box[3][li], hy = s_box[4][li], hz = s_box[5][li];
@@ -260,44 +284,43 @@ __device__ __forceinline__ uint64_t ploc_flags(const uint32_t* nn, const int i, 
 // Cost-optimal collapse (Ylitie, Karras, Laine 2017, section 3.1; the host builder does the same, bvh8_build.cpp):
 // c[i-1] = cheapest way to hang the subtree under a wide node using at most i of its slots (i = 1..7), splits = for
 // j = 2..8 the number of slots that go to the left child, 3 bits each.  A subtree of at most max_leaf primitives is a
-// leaf slot: A * P * c_prim for every i.  Filled in by k_ploc_merge the moment a node is created (its children are
-// complete subtrees by then), read by gather_kids top-down.
-struct alignas(16) Dp { float c[7]; uint32_t splits; };
+// leaf slot: A * P * c_prim for every i.  Filled in the moment a node is created (its children are complete subtrees by
+// then), read by gather_kids top-down.
 constexpr float kCostNode = 1.0f, kCostPrim = 0.3f;
 
-__device__ __forceinline__ void dp_of(const Dp* dp, const N2* nodes, const uint32_t* cnt,
-                                      const uint32_t id, const uint32_t max_leaf, float c[8])
+// costs c[1..7] and primitive count (saturated at 7) of the subtree `id` whose box is (a, b)
+__device__ __forceinline__ uint32_t subtree_costs(const Tree& t, const uint32_t id, const float4 a, const float4 b, const uint32_t max_leaf, float c[8])
 {
-	const uint32_t n = cnt[id];
+	uint32_t n = 1u;
+	float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0;
+	if (id >= t.N) {
+		const float4* p = reinterpret_cast<const float4*>(t.inner + (id - t.N));
+		c0 = p[2]; c1 = p[3];
+		n = (__float_as_uint(c1.w) >> 24) & 7u;
+	}
 	if (n <= max_leaf) {
-		const float4* p = reinterpret_cast<const float4*>(&nodes[id]);
-		const float4 a = p[0], b = p[1];
 		const float v = half_area(a.x, a.y, a.z, b.x, b.y, b.z) * (float)n * kCostPrim;
 #pragma unroll
 		for (int i = 1; i <= 7; ++i) c[i] = v;
 	} else {
-		const float4* p = reinterpret_cast<const float4*>(&dp[id]);
-		const float4 a = p[0], b = p[1];
-		c[1] = a.x; c[2] = a.y; c[3] = a.z; c[4] = a.w; c[5] = b.x; c[6] = b.y; c[7] = b.z;
+		c[1] = c0.x; c[2] = c0.y; c[3] = c0.z; c[4] = c0.w; c[5] = c1.x; c[6] = c1.y; c[7] = c1.z;
 	}
+	return n;
 }
 
-// the merged node `id` of clusters l and r (boxes la/lb and ra/rb = {lo, .} / {hi, .}): box, children, primitive count, collapse costs
-__device__ __forceinline__ void ploc_create_node(N2* nodes, uint32_t* cnt, Dp* dp, const uint32_t max_leaf, const uint32_t id, const uint32_t l, const uint32_t r,
-                                                 const float4 la, const float4 lb, const float4 ra, const float4 rb)
+// the merged node `id` of clusters l and r (boxes la/lb and ra/rb = {lo, .} / {hi, .}): its 64-byte record; returns its box
+__device__ __forceinline__ void ploc_create_node(const Tree& t, const uint32_t max_leaf, const uint32_t id, const uint32_t l, const uint32_t r,
+                                                 const float4 la, const float4 lb, const float4 ra, const float4 rb, float4* box_lo, float4* box_hi)
 {
 	const float4 oa = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), __int_as_float((int32_t)l));
 	const float4 ob = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), __int_as_float((int32_t)r));
-	float4* po = reinterpret_cast<float4*>(&nodes[id]);
-	po[0] = oa; po[1] = ob;
-	const uint32_t total = cnt[l] + cnt[r];
-	cnt[id] = total;
+	*box_lo = oa; *box_hi = ob;
+	float cl[8], cr[8];
+	const uint32_t nl = subtree_costs(t, l, la, lb, max_leaf, cl), nr = subtree_costs(t, r, ra, rb, max_leaf, cr);
+	const uint32_t total = min(nl + nr, 7u);
+	float c[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+	uint32_t splits = 0u;
 	if (total > max_leaf) {
-		float cl[8], cr[8];
-		dp_of(dp, nodes, cnt, l, max_leaf, cl);
-		dp_of(dp, nodes, cnt, r, max_leaf, cr);
-		Dp d;
-		uint32_t splits = 0u;
 		float D8 = 0.f;
 #pragma unroll
 		for (int j = 2; j <= 8; ++j) {
@@ -308,42 +331,43 @@ __device__ __forceinline__ void ploc_create_node(N2* nodes, uint32_t* cnt, Dp* d
 				if (v < best) { best = v; bk = (uint32_t)k; }
 			}
 			splits |= bk << (3 * (j - 2));
-			if (j <= 7) d.c[j - 1] = best; else D8 = best;
+			if (j <= 7) c[j - 1] = best; else D8 = best;
 		}
-		d.c[0] = half_area(oa.x, oa.y, oa.z, ob.x, ob.y, ob.z) * kCostNode + D8;
+		c[0] = half_area(oa.x, oa.y, oa.z, ob.x, ob.y, ob.z) * kCostNode + D8;
 #pragma unroll
-		for (int i = 1; i < 7; ++i) d.c[i] = fminf(d.c[i], d.c[i - 1]);
-		d.splits = splits;
-		float4* pd = reinterpret_cast<float4*>(&dp[id]);
-		pd[0] = make_float4(d.c[0], d.c[1], d.c[2], d.c[3]);
-		pd[1] = make_float4(d.c[4], d.c[5], d.c[6], __uint_as_float(d.splits));
+		for (int i = 1; i < 7; ++i) c[i] = fminf(c[i], c[i - 1]);
 	}
+	float4* po = reinterpret_cast<float4*>(t.inner + (id - t.N));
+	po[0] = oa; po[1] = ob;
+	po[2] = make_float4(c[0], c[1], c[2], c[3]);
+	po[3] = make_float4(c[4], c[5], c[6], __uint_as_float(splits | (total << 24)));
 }
 
-// one tile of a PLOC round: order-preserving compaction of the surviving clusters, creation of the merged nodes and their
-// collapse costs.  *tile_total = (survivors, leaders << 32) of this tile.
-__device__ __forceinline__ void ploc_merge_block(N2* nodes, uint32_t* cnt, const uint32_t* cid_in, uint32_t* cid_out, const uint32_t* nn, const int n,
-                                                 const uint64_t tile_off, const uint32_t node_base, Dp* dp, const uint32_t max_leaf, const int block,
-                                                 uint64_t* s_warp, uint64_t* tile_total)
+// one tile of a PLOC round (k_ploc_tail): order-preserving compaction of the surviving clusters, creation of the merged nodes and
+// their collapse costs.  *tile_total = (survivors, leaders << 32) of this tile.
+__device__ __forceinline__ void ploc_merge_block(const Tree& t, const uint32_t* cid_in, const N2* cbox_in, uint32_t* cid_out, N2* cbox_out, const uint32_t* nn,
+                                                 const int n, const uint32_t node_base, const uint32_t max_leaf, uint64_t* s_warp, uint64_t* tile_total)
 {
-	const int i = block * kTile + threadIdx.x;
+	const int i = threadIdx.x;
 	int partner;
 	const uint64_t f = ploc_flags(nn, i, n, &partner);
 	uint64_t tot;
-	const uint64_t pos = tile_off + block_scan_excl(f, s_warp, &tot);
+	const uint64_t pos = block_scan_excl(f, s_warp, &tot);
 	*tile_total = tot;
 	if (!(f & 1ull)) return;
 	const uint32_t out = (uint32_t)pos;
+	const float4* pl = reinterpret_cast<const float4*>(&cbox_in[i]);
+	float4 a = pl[0], b = pl[1];
+	uint32_t id = cid_in[i];
 	if (f >> 32) {
-		const uint32_t id = node_base + (uint32_t)(pos >> 32);
-		const uint32_t l = cid_in[i], r = cid_in[partner];
-		const float4* pl = reinterpret_cast<const float4*>(&nodes[l]);
-		const float4* pr = reinterpret_cast<const float4*>(&nodes[r]);
-		ploc_create_node(nodes, cnt, dp, max_leaf, id, l, r, pl[0], pl[1], pr[0], pr[1]);
-		cid_out[out] = id;
-	} else {
-		cid_out[out] = cid_in[i];
+		const float4* pr = reinterpret_cast<const float4*>(&cbox_in[partner]);
+		const uint32_t l = id, r = cid_in[partner];
+		id = node_base + (uint32_t)(pos >> 32);
+		ploc_create_node(t, max_leaf, id, l, r, a, b, pr[0], pr[1], &a, &b);
 	}
+	cid_out[out] = id;
+	float4* po = reinterpret_cast<float4*>(&cbox_out[out]);
+	po[0] = a; po[1] = b;
 }
 
 // ---- one clustering round = ONE launch (round 2) -------------------------------------------------------------------------------
@@ -380,8 +404,8 @@ __device__ __forceinline__ uint64_t lb_sums(const uint64_t w) { return (w & 0xff
 #define CUPT_PLOC_ITEMS 4
 #endif
 template <int kRadius, int kRoundItems>
-__global__ void __launch_bounds__(kTile, 6) k_ploc_round(N2* nodes, uint32_t* cnt, uint32_t* cid0, uint32_t* cid1, PlocState* state, const uint32_t launch,
-                                                      uint32_t* tickets, uint64_t* tile_state, Dp* dp, const uint32_t max_leaf)
+__global__ void __launch_bounds__(kTile, 6) k_ploc_round(const Tree t, uint32_t* cid0, uint32_t* cid1, N2* cbox0, N2* cbox1, PlocState* state, const uint32_t launch,
+                                                      uint32_t* tickets, uint64_t* tile_state, const uint32_t max_leaf)
 {
 	constexpr int kRoundTile = kTile * kRoundItems;
 	constexpr int W = kRoundTile + 4 * kRadius;
@@ -406,15 +430,16 @@ __global__ void __launch_bounds__(kTile, 6) k_ploc_round(N2* nodes, uint32_t* cn
 	if (tile >= ntiles) return;
 	const uint32_t* cin = (cur.rounds & 1u) ? cid1 : cid0;
 	uint32_t* cout = (cur.rounds & 1u) ? cid0 : cid1;
+	const N2* cbin = (cur.rounds & 1u) ? cbox1 : cbox0;
+	N2* cbout = (cur.rounds & 1u) ? cbox0 : cbox1;
 	// boxes of positions [tile * kRoundTile - 2R, (tile + 1) * kRoundTile + 2R)
 	const int base = tile * kRoundTile - 2 * kRadius;
 	for (int k = threadIdx.x; k < W; k += kTile) {
 		const int g = base + k;
 		if (g >= 0 && g < n) {
-			const uint32_t c = cin[g];
-			const float4* p = reinterpret_cast<const float4*>(&nodes[c]);
+			const float4* p = reinterpret_cast<const float4*>(&cbin[g]);
 			const float4 a = p[0], b = p[1];
-			s_cid[k] = c;
+			s_cid[k] = cin[g];
 			s_box[0][k] = a.x; s_box[1][k] = a.y; s_box[2][k] = a.z;
 			s_box[3][k] = b.x; s_box[4][k] = b.y; s_box[5][k] = b.z;
 		}
@@ -521,16 +546,18 @@ __global__ void __launch_bounds__(kTile, 6) k_ploc_round(N2* nodes, uint32_t* cn
 		const uint64_t pos = off + s_pref[p >> 2] + ((uint64_t)__popc(w4 & 0x01010101u & below) | ((uint64_t)__popc(w4 & 0x10101010u & below) << 32));
 		const uint32_t out = (uint32_t)pos;
 		const int li = p + 2 * kRadius;
+		float4 a = make_float4(s_box[0][li], s_box[1][li], s_box[2][li], 0.f), b = make_float4(s_box[3][li], s_box[4][li], s_box[5][li], 0.f);
+		uint32_t id = s_cid[li];
 		if (fl & 16u) {
-			const uint32_t id = cur.node_base + (uint32_t)(pos >> 32);
 			const int lp = li + (partner[k] - (tile * kRoundTile + p));
-			ploc_create_node(nodes, cnt, dp, max_leaf, id, s_cid[li], s_cid[lp],
-			                 make_float4(s_box[0][li], s_box[1][li], s_box[2][li], 0.f), make_float4(s_box[3][li], s_box[4][li], s_box[5][li], 0.f),
-			                 make_float4(s_box[0][lp], s_box[1][lp], s_box[2][lp], 0.f), make_float4(s_box[3][lp], s_box[4][lp], s_box[5][lp], 0.f));
-			cout[out] = id;
-		} else {
-			cout[out] = s_cid[li];
+			const uint32_t l = id, r = s_cid[lp];
+			id = cur.node_base + (uint32_t)(pos >> 32);
+			ploc_create_node(t, max_leaf, id, l, r, a, b, make_float4(s_box[0][lp], s_box[1][lp], s_box[2][lp], 0.f),
+			                 make_float4(s_box[3][lp], s_box[4][lp], s_box[5][lp], 0.f), &a, &b);
 		}
+		cout[out] = id;
+		float4* po = reinterpret_cast<float4*>(&cbout[out]);
+		po[0] = a; po[1] = b;
 	}
 }
 
@@ -538,8 +565,8 @@ __global__ void __launch_bounds__(kTile, 6) k_ploc_round(N2* nodes, uint32_t* cn
 // with block barriers in between (no launches, no host read-back): about log_1.5(256) = 14 of the ~30 rounds of a 262 k-triangle
 // build.  state[0] = node_base afterwards, state[1] = rounds run here, state[2] = which cid buffer holds the root.
 template <int kRadius>
-__global__ void __launch_bounds__(kTile) k_ploc_tail(N2* nodes, uint32_t* cnt, uint32_t* cid0, uint32_t* cid1, uint32_t* nn, int n, uint32_t node_base,
-                                                     Dp* dp, const uint32_t max_leaf, int cur, uint32_t* state)
+__global__ void __launch_bounds__(kTile) k_ploc_tail(const Tree t, uint32_t* cid0, uint32_t* cid1, N2* cbox0, N2* cbox1, uint32_t* nn, int n, uint32_t node_base,
+                                                     const uint32_t max_leaf, int cur, uint32_t* state)
 {
 	__shared__ float s_box[6][kTile + 2 * kRadius];
 	__shared__ uint64_t s_warp[kTile / 32 + 1];
@@ -547,60 +574,60 @@ __global__ void __launch_bounds__(kTile) k_ploc_tail(N2* nodes, uint32_t* cnt, u
 	while (n > 1) {
 		uint32_t* cin = cur ? cid1 : cid0;
 		uint32_t* cout = cur ? cid0 : cid1;
-		ploc_nearest_block<kRadius, true>(nodes, cin, n, nn, 0, s_box);
+		N2* cbin = cur ? cbox1 : cbox0;
+		N2* cbout = cur ? cbox0 : cbox1;
+		ploc_nearest_block<kRadius>(cbin, n, nn, s_box);
 		__syncthreads();
 		uint64_t tot;
-		ploc_merge_block(nodes, cnt, cin, cout, nn, n, 0ull, node_base, dp, max_leaf, 0, s_warp, &tot);
+		ploc_merge_block(t, cin, cbin, cout, cbout, nn, n, node_base, max_leaf, s_warp, &tot);
 		__syncthreads();
 		n = (int)(uint32_t)tot; node_base += (uint32_t)(tot >> 32); cur ^= 1; ++rounds;
-		if ((tot >> 32) == 0ull) break;   // (no mutual pair: cannot happen, see k_ploc_nearest; the host checks n)
+		if ((tot >> 32) == 0ull) break;   // (no mutual pair: cannot happen, see ploc_nearest_block; the host checks n)
 	}
 	if (threadIdx.x == 0) { state[0] = node_base; state[1] = rounds; state[2] = (uint32_t)cur; state[3] = (uint32_t)n; }
 }
 
 // ---- 4. collapse to 8-wide + emission ----------------------------------------------------------------------------
-struct Kids { int32_t id[8]; int n; };
+struct Kids { int32_t id[8]; uint32_t prims[8]; int n; };   // prims: primitives of a leaf slot, 0 for a child that becomes a wide node
 
-__device__ __forceinline__ float node_half_area(const N2* __restrict__ nodes, const int32_t id)
-{
-	const float4* p = reinterpret_cast<const float4*>(&nodes[id]);
-	const float4 a = __ldg(p), b = __ldg(p + 1);
-	return half_area(a.x, a.y, a.z, b.x, b.y, b.z);
-}
-
-// the children of one wide node: the cost-optimal cut below the binary node `root` (Dp above); a subtree with at most
-// max_leaf primitives is a leaf slot.  Children come out in left-first order.
-__device__ __forceinline__ void gather_kids(const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt, const Dp* __restrict__ dp,
-                                            const int32_t root, const uint32_t max_leaf, Kids& k)
+// the children of one wide node: the cost-optimal cut below the binary node `root`; a subtree with at most max_leaf primitives
+// is a leaf slot.  Children come out in left-first order.  One 64-byte record per inner node visited.
+__device__ __forceinline__ void gather_kids(const Tree& t, const int32_t root, const uint32_t max_leaf, Kids& k)
 {
 	k.n = 0;
-	if (cnt[root] <= max_leaf) { k.id[0] = root; k.n = 1; return; }
+	if ((uint32_t)root < t.N) { k.id[0] = root; k.prims[0] = 1u; k.n = 1; return; }
 	int32_t st_n[16]; int st_b[16]; int sp = 0;
 	{
-		const int k8 = (int)((dp[root].splits >> 18) & 7u);
-		st_n[sp] = nodes[root].right; st_b[sp++] = 8 - k8;
-		st_n[sp] = nodes[root].left; st_b[sp++] = k8;
+		const float4* p = reinterpret_cast<const float4*>(t.inner + ((uint32_t)root - t.N));
+		const float4 a = __ldg(p), b = __ldg(p + 1), d = __ldg(p + 3);
+		const uint32_t sw = __float_as_uint(d.w), cn = (sw >> 24) & 7u;
+		if (cn <= max_leaf) { k.id[0] = root; k.prims[0] = cn; k.n = 1; return; }
+		const int k8 = (int)((sw >> 18) & 7u);
+		st_n[sp] = __float_as_int(b.w); st_b[sp++] = 8 - k8;
+		st_n[sp] = __float_as_int(a.w); st_b[sp++] = k8;
 	}
 	while (sp > 0) {
 		--sp;
 		const int32_t n = st_n[sp];
 		int i = min(st_b[sp], 7);
-		if (cnt[n] <= max_leaf) { k.id[k.n++] = n; continue; }
-		const float4* p = reinterpret_cast<const float4*>(&dp[n]);
-		const float4 a = __ldg(p), b = __ldg(p + 1);
-		const float c[8] = {0.f, a.x, a.y, a.z, a.w, b.x, b.y, b.z};
+		if ((uint32_t)n < t.N) { k.prims[k.n] = 1u; k.id[k.n++] = n; continue; }
+		const float4* p = reinterpret_cast<const float4*>(t.inner + ((uint32_t)n - t.N));
+		const float4 a = __ldg(p), b = __ldg(p + 1), c0 = __ldg(p + 2), c1 = __ldg(p + 3);
+		const uint32_t sw = __float_as_uint(c1.w), cn = (sw >> 24) & 7u;
+		if (cn <= max_leaf) { k.prims[k.n] = cn; k.id[k.n++] = n; continue; }
+		const float c[8] = {0.f, c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z};
 		while (i > 1 && c[i] == c[i - 1]) --i;
-		if (i == 1) { k.id[k.n++] = n; continue; }   // a wide node of its own
-		const int kl = (int)((__float_as_uint(b.w) >> (3 * (i - 2))) & 7u);
-		st_n[sp] = nodes[n].right; st_b[sp++] = i - kl;
-		st_n[sp] = nodes[n].left; st_b[sp++] = kl;
+		if (i == 1) { k.prims[k.n] = 0u; k.id[k.n++] = n; continue; }   // a wide node of its own
+		const int kl = (int)((sw >> (3 * (i - 2))) & 7u);
+		st_n[sp] = __float_as_int(b.w); st_b[sp++] = i - kl;
+		st_n[sp] = __float_as_int(a.w); st_b[sp++] = kl;
 	}
 }
 
 // per item of the level: (inner children | leaf primitives << 32), reduced to one sum per tile.  The item's children (the
 // cost-optimal cut, a serial walk of up to 15 dependent node reads) are kept for k_collapse_emit, and so is the item's
 // exclusive prefix inside its tile: the emission then needs neither the walk nor a block-wide scan.
-__global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__ nodes, const uint32_t* __restrict__ cnt, const Dp* __restrict__ dp, const int32_t* __restrict__ items,
+__global__ void __launch_bounds__(kTile) k_collapse_count(const Tree t, const int32_t* __restrict__ items,
                                                           const int n_items, const uint32_t max_leaf, uint64_t* __restrict__ item_prefix, int32_t* __restrict__ item_kids,
                                                           uint64_t* __restrict__ tile_sums)
 {
@@ -609,15 +636,14 @@ __global__ void __launch_bounds__(kTile) k_collapse_count(const N2* __restrict__
 	uint64_t f = 0;
 	if (i < n_items) {
 		Kids k;
-		gather_kids(nodes, cnt, dp, items[i], max_leaf, k);
+		gather_kids(t, items[i], max_leaf, k);
 		uint32_t ni = 0, np = 0;
 		int32_t ids[8];
 #pragma unroll
 		for (int q = 0; q < 8; ++q) {
 			ids[q] = q < k.n ? k.id[q] : -1;
 			if (q < k.n) {
-				const uint32_t c = cnt[k.id[q]];
-				if (c > max_leaf) ni++; else np += c;
+				if (k.prims[q] == 0u) ni++; else np += k.prims[q];
 			}
 		}
 		f = (uint64_t)ni | ((uint64_t)np << 32);
@@ -635,7 +661,7 @@ __device__ __forceinline__ double pow2_double(const int e) { return __hiloint2do
 __device__ __forceinline__ int dev_float_exponent(const float v) { return (int)((__float_as_uint(v) >> 23) & 0xffu) - 127; }
 
 struct EmitArgs {
-	const N2* nodes; const uint32_t* cnt; const Dp* dp; const int32_t* items; int n_items; uint32_t max_leaf;
+	Tree t; const int32_t* items; int n_items; uint32_t max_leaf;
 	const uint64_t* item_prefix; const int32_t* item_kids; const uint64_t* tile_offs;
 	uint32_t level_base, next_base, prim_base;
 	int32_t* next_items; Node8* out_nodes; float4* out_prims;
@@ -673,13 +699,13 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 		const uint64_t ex = A.tile_offs[i / kTile] + A.item_prefix[i];
 		float blo[3], bhi[3], clo[3] = {0.f, 0.f, 0.f}, chi[3] = {0.f, 0.f, 0.f};
 		{
-			const float4* p = reinterpret_cast<const float4*>(&A.nodes[self]);
+			const float4* p = A.t.rec((uint32_t)self);
 			const float4 a = __ldg(p), b = __ldg(p + 1);
 			blo[0] = a.x; blo[1] = a.y; blo[2] = a.z; bhi[0] = b.x; bhi[1] = b.y; bhi[2] = b.z;
 		}
 		float cost[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 		if (kid >= 0) {
-			const float4* p = reinterpret_cast<const float4*>(&A.nodes[kid]);
+			const float4* p = A.t.rec((uint32_t)kid);
 			const float4 a = __ldg(p), b = __ldg(p + 1);
 			clo[0] = a.x; clo[1] = a.y; clo[2] = a.z; chi[0] = b.x; chi[1] = b.y; chi[2] = b.z;
 			float d[3];
@@ -731,7 +757,7 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 			inv_scale[a] = pow2_double(-e);
 		}
 		// this child's record count / kind, and what lies before it in SLOT order
-		const uint32_t cc = kid >= 0 ? A.cnt[kid] : 0u;
+		const uint32_t cc = kid >= 0 ? A.t.count((uint32_t)kid) : 0u;
 		const bool inner = kid >= 0 && cc > A.max_leaf, leaf = kid >= 0 && !inner;
 		uint32_t inner_before = 0u, prims_before = 0u;
 #pragma unroll
@@ -767,18 +793,18 @@ __global__ void __launch_bounds__(kTile) k_collapse_emit(const EmitArgs A)
 				my_pvalid = (cc == 1 ? 1u : (cc == 2 ? 3u : 7u)) << (4 * slot);
 				// <= 3 primitives: the tiny subtree is at most two levels deep; left first (the records themselves are written by k_emit_prims)
 				int32_t* dst = A.rec_prim + tri_base + prims_before;
-				const int32_t l0 = A.nodes[kid].left;
+				const int32_t l0 = A.t.left((uint32_t)kid);
 				if (l0 < 0) {
 					dst[0] = -1 - l0;
 				} else {
-					const int32_t r0 = A.nodes[kid].right;
+					const int32_t r0 = A.t.right((uint32_t)kid);
 					uint32_t w = 0;
-					const int32_t ll = A.nodes[l0].left;
+					const int32_t ll = A.t.left((uint32_t)l0);
 					if (ll < 0) dst[w++] = -1 - ll;
-					else { dst[w++] = -1 - A.nodes[ll].left; dst[w++] = -1 - A.nodes[A.nodes[l0].right].left; }
-					const int32_t rl = A.nodes[r0].left;
+					else { dst[w++] = -1 - A.t.leaf[ll].left; dst[w++] = -1 - A.t.leaf[A.t.right((uint32_t)l0)].left; }
+					const int32_t rl = A.t.left((uint32_t)r0);
 					if (rl < 0) dst[w++] = -1 - rl;
-					else { dst[w++] = -1 - A.nodes[rl].left; dst[w++] = -1 - A.nodes[A.nodes[r0].right].left; }
+					else { dst[w++] = -1 - A.t.leaf[rl].left; dst[w++] = -1 - A.t.leaf[A.t.right((uint32_t)r0)].left; }
 				}
 				sah += area2 * A.inv_root_area * cc;
 			}
@@ -871,7 +897,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	// everything the build touches except its two outputs, in one arena; the sort buffers are dead once the sorted
 	// leaves are written, the collapse reuses the cluster arrays for its level queues
 	const size_t need = up256(n * sizeof(N2)) + up256(n * 48) + up256(64) + 2 * up256(n * 8) + 2 * up256(n * 4) + up256(temp_bytes + 256)
-	                    + up256(2 * n * sizeof(N2)) + up256(2 * n * sizeof(Dp)) + up256(2 * n * 4) + 3 * up256(n * 4) + up256(((size_t)tilesN + 1) * 8) + up256(64)
+	                    + up256(n * sizeof(N2)) + up256(n * sizeof(Inner)) + 2 * up256(n * sizeof(N2)) + 3 * up256(n * 4) + up256(((size_t)tilesN + 1) * 8) + up256(64)
 	                    + up256((n / 2 + 2) * 8) + up256((n / 2 + 2) * 32) + up256(64) + up256(kMaxRoundLaunches * 4) + 4096;
 	int rc;
 	if ((rc = arena.reserve(need))) return rc;
@@ -895,9 +921,9 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	CKB(cudaEventRecord(ev[1], st));
 
 	// 3: PLOC
-	N2* nodes = take<N2>(arena, 2 * n);
-	uint32_t* cnt = take<uint32_t>(arena, 2 * n);
-	Dp* dp = take<Dp>(arena, 2 * n);
+	Tree tree;
+	tree.leaf = take<N2>(arena, n); tree.inner = take<Inner>(arena, n); tree.N = (uint32_t)N;
+	N2* cbox[2] = {take<N2>(arena, n), take<N2>(arena, n)};
 	uint32_t* cid[2] = {take<uint32_t>(arena, n), take<uint32_t>(arena, n)};
 	uint32_t* nn = take<uint32_t>(arena, n);
 	uint64_t* tile_sums = take<uint64_t>(arena, (size_t)tilesN + 1);
@@ -907,7 +933,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	double* d_sah = take<double>(arena, 1);
 	uint32_t* tickets = take<uint32_t>(arena, kMaxRoundLaunches);
 	if (arena.off > arena.cap) return set_error(CUPT_ERR_CUDA, "internal: BVH build workspace undersized (%zu > %zu)", arena.off, arena.cap);
-	k_sorted_leaves<<<tilesN, kTile, 0, st>>>(leaf, vals[sorted], N, nodes, cnt, cid[0]);
+	k_sorted_leaves<<<tilesN, kTile, 0, st>>>(leaf, vals[sorted], N, tree.leaf, cbox[0], cid[0]);
 	int cn = (int)N, cur = 0, rounds = 0;
 	uint32_t node_base = (uint32_t)N;
 	if (cn > kTile) {
@@ -929,8 +955,8 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 			const int grid = (bound + kTile * items - 1) / (kTile * items);
 			for (int b = 0; b < batch; ++b, ++launch) {
 #define CUPT_ROUND(R)                                                                                                                                        \
-	if (items == CUPT_PLOC_ITEMS) k_ploc_round<R, CUPT_PLOC_ITEMS><<<grid, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], d_state, launch, tickets, tile_sums, dp, (uint32_t)max_leaf); \
-	else k_ploc_round<R, 1><<<grid, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], d_state, launch, tickets, tile_sums, dp, (uint32_t)max_leaf);
+	if (items == CUPT_PLOC_ITEMS) k_ploc_round<R, CUPT_PLOC_ITEMS><<<grid, kTile, 0, st>>>(tree, cid[0], cid[1], cbox[0], cbox[1], d_state, launch, tickets, tile_sums, (uint32_t)max_leaf); \
+	else k_ploc_round<R, 1><<<grid, kTile, 0, st>>>(tree, cid[0], cid[1], cbox[0], cbox[1], d_state, launch, tickets, tile_sums, (uint32_t)max_leaf);
 				switch (radius) {
 				case 32: CUPT_ROUND(32) break;
 				case 16: CUPT_ROUND(16) break;
@@ -952,12 +978,12 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	if (cn > 1) {   // the remaining rounds in one launch (k_ploc_tail)
 		uint32_t* state = reinterpret_cast<uint32_t*>(tile_sums);
 		switch (radius) {
-		case 32: k_ploc_tail<32><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
-		case 16: k_ploc_tail<16><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
-		case 8: k_ploc_tail<8><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
-		case 2: k_ploc_tail<2><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
-		case 1: k_ploc_tail<1><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
-		default: k_ploc_tail<4><<<1, kTile, 0, st>>>(nodes, cnt, cid[0], cid[1], nn, cn, node_base, dp, (uint32_t)max_leaf, cur, state); break;
+		case 32: k_ploc_tail<32><<<1, kTile, 0, st>>>(tree, cid[0], cid[1], cbox[0], cbox[1], nn, cn, node_base, (uint32_t)max_leaf, cur, state); break;
+		case 16: k_ploc_tail<16><<<1, kTile, 0, st>>>(tree, cid[0], cid[1], cbox[0], cbox[1], nn, cn, node_base, (uint32_t)max_leaf, cur, state); break;
+		case 8: k_ploc_tail<8><<<1, kTile, 0, st>>>(tree, cid[0], cid[1], cbox[0], cbox[1], nn, cn, node_base, (uint32_t)max_leaf, cur, state); break;
+		case 2: k_ploc_tail<2><<<1, kTile, 0, st>>>(tree, cid[0], cid[1], cbox[0], cbox[1], nn, cn, node_base, (uint32_t)max_leaf, cur, state); break;
+		case 1: k_ploc_tail<1><<<1, kTile, 0, st>>>(tree, cid[0], cid[1], cbox[0], cbox[1], nn, cn, node_base, (uint32_t)max_leaf, cur, state); break;
+		default: k_ploc_tail<4><<<1, kTile, 0, st>>>(tree, cid[0], cid[1], cbox[0], cbox[1], nn, cn, node_base, (uint32_t)max_leaf, cur, state); break;
 		}
 		CKB(cudaMemcpyAsync(h_total, state, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 		CKB(cudaStreamSynchronize(st));
@@ -971,7 +997,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 
 	// 4: collapse + emit, level by level, into the caller's buffers (reused when large enough)
 	N2 root_box;
-	CKB(cudaMemcpyAsync(&root_box, nodes + root, sizeof(N2), cudaMemcpyDeviceToHost, st));
+	CKB(cudaMemcpyAsync(&root_box, N == 1 ? static_cast<const void*>(tree.leaf) : static_cast<const void*>(tree.inner + (root - (int32_t)N)), sizeof(N2), cudaMemcpyDeviceToHost, st));
 	CKB(cudaStreamSynchronize(st));
 	const double rdx = (double)root_box.hi[0] - root_box.lo[0], rdy = (double)root_box.hi[1] - root_box.lo[1], rdz = (double)root_box.hi[2] - root_box.lo[2];
 	const double root_area = std::max(2.0 * (rdx * rdy + rdx * rdz + rdy * rdz), 1e-300);
@@ -1003,10 +1029,10 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 			out->nodes = bigger; out->nodes_capacity_bytes = ncap;
 		}
 		const int tiles = (n_items + kTile - 1) / kTile;
-		k_collapse_count<<<tiles, kTile, 0, st>>>(nodes, cnt, dp, items[lvl], n_items, (uint32_t)max_leaf, item_counts, item_kids, tile_sums);
+		k_collapse_count<<<tiles, kTile, 0, st>>>(tree, items[lvl], n_items, (uint32_t)max_leaf, item_counts, item_kids, tile_sums);
 		k_scan_tiles<<<1, kTile, 0, st>>>(tile_sums, tiles, d_total);
 		EmitArgs A;
-		A.nodes = nodes; A.cnt = cnt; A.dp = dp; A.items = items[lvl]; A.n_items = n_items; A.max_leaf = (uint32_t)max_leaf;
+		A.t = tree; A.items = items[lvl]; A.n_items = n_items; A.max_leaf = (uint32_t)max_leaf;
 		A.item_prefix = item_counts; A.item_kids = item_kids; A.tile_offs = tile_sums;
 		A.level_base = level_base; A.next_base = level_base + (uint32_t)n_items; A.prim_base = prim_base;
 		A.next_items = items[lvl ^ 1]; A.out_nodes = static_cast<Node8*>(out->nodes); A.out_prims = static_cast<float4*>(out->prims);
