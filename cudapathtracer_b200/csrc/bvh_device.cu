@@ -159,18 +159,32 @@ struct Tree {
 	__device__ __forceinline__ uint32_t count(const uint32_t id) const { return id < N ? 1u : (inner[id - N].splits >> 24) & 7u; }
 };
 
+// a cluster's box in the per-round cluster list: 24 bytes, read and written as three 8-byte words
+struct alignas(8) CBox { float lo[3], hi[3]; };
+__device__ __forceinline__ void cbox_load(const CBox* p, float4& a, float4& b)
+{
+	const float2* q = reinterpret_cast<const float2*>(p);
+	const float2 x = q[0], y = q[1], z = q[2];
+	a = make_float4(x.x, x.y, y.x, 0.f); b = make_float4(y.y, z.x, z.y, 0.f);
+}
+__device__ __forceinline__ void cbox_store(CBox* p, const float4 a, const float4 b)
+{
+	float2* q = reinterpret_cast<float2*>(p);
+	q[0] = make_float2(a.x, a.y); q[1] = make_float2(a.z, b.x); q[2] = make_float2(b.y, b.z);
+}
+
 // the sorted leaves, and the first round's cluster list: cluster i = leaf i, its box in cbox (every round reads the clusters' boxes
 // from such a list in cluster order — a stream — instead of through the node indices)
 __global__ void __launch_bounds__(kTile) k_sorted_leaves(const N2* __restrict__ leaf, const uint32_t* __restrict__ order, const int64_t N,
-                                                         N2* __restrict__ sorted, N2* __restrict__ cbox, uint32_t* __restrict__ cid)
+                                                         N2* __restrict__ sorted, CBox* __restrict__ cbox, uint32_t* __restrict__ cid)
 {
 	const int64_t i = (int64_t)blockIdx.x * kTile + threadIdx.x;
 	if (i >= N) return;
 	const float4* src = reinterpret_cast<const float4*>(&leaf[order[i]]);
 	const float4 a = __ldg(src), b = __ldg(src + 1);
 	float4* d0 = reinterpret_cast<float4*>(&sorted[i]);
-	float4* d1 = reinterpret_cast<float4*>(&cbox[i]);
-	d0[0] = a; d0[1] = b; d1[0] = a; d1[1] = b;
+	d0[0] = a; d0[1] = b;
+	cbox_store(&cbox[i], a, b);
 	cid[i] = (uint32_t)i;
 }
 
@@ -234,13 +248,13 @@ __global__ void __launch_bounds__(kTile) k_scan_tiles(uint64_t* __restrict__ til
 // always mutual (progress every round) and a run of identical boxes pairs up as (0,1)(2,3)... instead of chaining.
 // (k_ploc_tail's version: one block, plain loads of what it wrote itself a round earlier)
 template <int kRadius>
-__device__ __forceinline__ void ploc_nearest_block(const N2* cbox, const int n, uint32_t* nn, float (*s_box)[kTile + 2 * kRadius])
+__device__ __forceinline__ void ploc_nearest_block(const CBox* cbox, const int n, uint32_t* nn, float (*s_box)[kTile + 2 * kRadius])
 {
 	for (int k = threadIdx.x; k < kTile + 2 * kRadius; k += kTile) {
 		const int g = k - kRadius;
 		if (g >= 0 && g < n) {
-			const float4* p = reinterpret_cast<const float4*>(&cbox[g]);
-			const float4 a = p[0], b = p[1];
+			float4 a, b;
+			cbox_load(&cbox[g], a, b);
 			s_box[0][k] = a.x; s_box[1][k] = a.y; s_box[2][k] = a.z;
 			s_box[3][k] = b.x; s_box[4][k] = b.y; s_box[5][k] = b.z;
 		}
@@ -345,7 +359,7 @@ __device__ __forceinline__ void ploc_create_node(const Tree& t, const uint32_t m
 
 // one tile of a PLOC round (k_ploc_tail): order-preserving compaction of the surviving clusters, creation of the merged nodes and
 // their collapse costs.  *tile_total = (survivors, leaders << 32) of this tile.
-__device__ __forceinline__ void ploc_merge_block(const Tree& t, const uint32_t* cid_in, const N2* cbox_in, uint32_t* cid_out, N2* cbox_out, const uint32_t* nn,
+__device__ __forceinline__ void ploc_merge_block(const Tree& t, const uint32_t* cid_in, const CBox* cbox_in, uint32_t* cid_out, CBox* cbox_out, const uint32_t* nn,
                                                  const int n, const uint32_t node_base, const uint32_t max_leaf, uint64_t* s_warp, uint64_t* tile_total)
 {
 	const int i = threadIdx.x;
@@ -356,18 +370,18 @@ __device__ __forceinline__ void ploc_merge_block(const Tree& t, const uint32_t* 
 	*tile_total = tot;
 	if (!(f & 1ull)) return;
 	const uint32_t out = (uint32_t)pos;
-	const float4* pl = reinterpret_cast<const float4*>(&cbox_in[i]);
-	float4 a = pl[0], b = pl[1];
+	float4 a, b;
+	cbox_load(&cbox_in[i], a, b);
 	uint32_t id = cid_in[i];
 	if (f >> 32) {
-		const float4* pr = reinterpret_cast<const float4*>(&cbox_in[partner]);
+		float4 ra, rb;
+		cbox_load(&cbox_in[partner], ra, rb);
 		const uint32_t l = id, r = cid_in[partner];
 		id = node_base + (uint32_t)(pos >> 32);
-		ploc_create_node(t, max_leaf, id, l, r, a, b, pr[0], pr[1], &a, &b);
+		ploc_create_node(t, max_leaf, id, l, r, a, b, ra, rb, &a, &b);
 	}
 	cid_out[out] = id;
-	float4* po = reinterpret_cast<float4*>(&cbox_out[out]);
-	po[0] = a; po[1] = b;
+	cbox_store(&cbox_out[out], a, b);
 }
 
 // ---- one clustering round = ONE launch (round 2) -------------------------------------------------------------------------------
@@ -404,7 +418,7 @@ __device__ __forceinline__ uint64_t lb_sums(const uint64_t w) { return (w & 0xff
 #define CUPT_PLOC_ITEMS 4
 #endif
 template <int kRadius, int kRoundItems>
-__global__ void __launch_bounds__(kTile, 6) k_ploc_round(const Tree t, uint32_t* cid0, uint32_t* cid1, N2* cbox0, N2* cbox1, PlocState* state, const uint32_t launch,
+__global__ void __launch_bounds__(kTile, 6) k_ploc_round(const Tree t, uint32_t* cid0, uint32_t* cid1, CBox* cbox0, CBox* cbox1, PlocState* state, const uint32_t launch,
                                                       uint32_t* tickets, uint64_t* tile_state, const uint32_t max_leaf)
 {
 	constexpr int kRoundTile = kTile * kRoundItems;
@@ -430,15 +444,15 @@ __global__ void __launch_bounds__(kTile, 6) k_ploc_round(const Tree t, uint32_t*
 	if (tile >= ntiles) return;
 	const uint32_t* cin = (cur.rounds & 1u) ? cid1 : cid0;
 	uint32_t* cout = (cur.rounds & 1u) ? cid0 : cid1;
-	const N2* cbin = (cur.rounds & 1u) ? cbox1 : cbox0;
-	N2* cbout = (cur.rounds & 1u) ? cbox0 : cbox1;
+	const CBox* cbin = (cur.rounds & 1u) ? cbox1 : cbox0;
+	CBox* cbout = (cur.rounds & 1u) ? cbox0 : cbox1;
 	// boxes of positions [tile * kRoundTile - 2R, (tile + 1) * kRoundTile + 2R)
 	const int base = tile * kRoundTile - 2 * kRadius;
 	for (int k = threadIdx.x; k < W; k += kTile) {
 		const int g = base + k;
 		if (g >= 0 && g < n) {
-			const float4* p = reinterpret_cast<const float4*>(&cbin[g]);
-			const float4 a = p[0], b = p[1];
+			float4 a, b;
+			cbox_load(&cbin[g], a, b);
 			s_cid[k] = cin[g];
 			s_box[0][k] = a.x; s_box[1][k] = a.y; s_box[2][k] = a.z;
 			s_box[3][k] = b.x; s_box[4][k] = b.y; s_box[5][k] = b.z;
@@ -556,8 +570,7 @@ __global__ void __launch_bounds__(kTile, 6) k_ploc_round(const Tree t, uint32_t*
 			                 make_float4(s_box[3][lp], s_box[4][lp], s_box[5][lp], 0.f), &a, &b);
 		}
 		cout[out] = id;
-		float4* po = reinterpret_cast<float4*>(&cbout[out]);
-		po[0] = a; po[1] = b;
+		cbox_store(&cbout[out], a, b);
 	}
 }
 
@@ -565,7 +578,7 @@ __global__ void __launch_bounds__(kTile, 6) k_ploc_round(const Tree t, uint32_t*
 // with block barriers in between (no launches, no host read-back): about log_1.5(256) = 14 of the ~30 rounds of a 262 k-triangle
 // build.  state[0] = node_base afterwards, state[1] = rounds run here, state[2] = which cid buffer holds the root.
 template <int kRadius>
-__global__ void __launch_bounds__(kTile) k_ploc_tail(const Tree t, uint32_t* cid0, uint32_t* cid1, N2* cbox0, N2* cbox1, uint32_t* nn, int n, uint32_t node_base,
+__global__ void __launch_bounds__(kTile) k_ploc_tail(const Tree t, uint32_t* cid0, uint32_t* cid1, CBox* cbox0, CBox* cbox1, uint32_t* nn, int n, uint32_t node_base,
                                                      const uint32_t max_leaf, int cur, uint32_t* state)
 {
 	__shared__ float s_box[6][kTile + 2 * kRadius];
@@ -574,8 +587,8 @@ __global__ void __launch_bounds__(kTile) k_ploc_tail(const Tree t, uint32_t* cid
 	while (n > 1) {
 		uint32_t* cin = cur ? cid1 : cid0;
 		uint32_t* cout = cur ? cid0 : cid1;
-		N2* cbin = cur ? cbox1 : cbox0;
-		N2* cbout = cur ? cbox0 : cbox1;
+		CBox* cbin = cur ? cbox1 : cbox0;
+		CBox* cbout = cur ? cbox0 : cbox1;
 		ploc_nearest_block<kRadius>(cbin, n, nn, s_box);
 		__syncthreads();
 		uint64_t tot;
@@ -897,7 +910,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	// everything the build touches except its two outputs, in one arena; the sort buffers are dead once the sorted
 	// leaves are written, the collapse reuses the cluster arrays for its level queues
 	const size_t need = up256(n * sizeof(N2)) + up256(n * 48) + up256(64) + 2 * up256(n * 8) + 2 * up256(n * 4) + up256(temp_bytes + 256)
-	                    + up256(n * sizeof(N2)) + up256(n * sizeof(Inner)) + 2 * up256(n * sizeof(N2)) + 3 * up256(n * 4) + up256(((size_t)tilesN + 1) * 8) + up256(64)
+	                    + up256(n * sizeof(N2)) + up256(n * sizeof(Inner)) + 2 * up256(n * sizeof(CBox)) + 3 * up256(n * 4) + up256(((size_t)tilesN + 1) * 8) + up256(64)
 	                    + up256((n / 2 + 2) * 8) + up256((n / 2 + 2) * 32) + up256(64) + up256(kMaxRoundLaunches * 4) + 4096;
 	int rc;
 	if ((rc = arena.reserve(need))) return rc;
@@ -923,7 +936,7 @@ int build_wide_bvh_device(cudaStream_t st, BuildArena& arena, const float* verts
 	// 3: PLOC
 	Tree tree;
 	tree.leaf = take<N2>(arena, n); tree.inner = take<Inner>(arena, n); tree.N = (uint32_t)N;
-	N2* cbox[2] = {take<N2>(arena, n), take<N2>(arena, n)};
+	CBox* cbox[2] = {take<CBox>(arena, n), take<CBox>(arena, n)};
 	uint32_t* cid[2] = {take<uint32_t>(arena, n), take<uint32_t>(arena, n)};
 	uint32_t* nn = take<uint32_t>(arena, n);
 	uint64_t* tile_sums = take<uint64_t>(arena, (size_t)tilesN + 1);
