@@ -8,12 +8,13 @@
 //                       for Bounding Volume Hierarchy Construction", TVCG 2018): every cluster finds the neighbour
 //                       within +-R positions of the Morton order (R = 4 by default: measured best on config 2, DESIGN.md
 //                       §4) whose union box has the smallest area; mutual pairs
-//                       merge; an order-preserving compaction closes the gaps.  Four launches per round
-//                       (k_ploc_nearest, k_ploc_count, k_scan_tiles, k_ploc_merge), ~log_1.5(N) rounds.
+//                       merge; an order-preserving compaction closes the gaps.  ONE launch per round (k_ploc_round:
+//                       neighbour search in shared memory, decoupled look-back for the compaction, merge), ~50 rounds
+//                       at 100 M primitives, the last ~14 inside one block (k_ploc_tail).
 //   4. collapse + emit  level by level from the root: the cost-optimal cut of every wide node (dynamic programme over
-//                       slot budgets, filled in by k_ploc_merge as nodes are created; same rule as the host builder),
+//                       slot budgets, filled in as nodes are created; same rule as the host builder),
 //                       octant-slot assignment, 8-bit quantisation, breadth-first emission (k_collapse_count,
-//                       k_scan_tiles, k_collapse_emit per level).
+//                       k_scan_tiles, k_collapse_emit per level), then the 48-byte records in tree order (k_emit_prims).
 //
 // The tree differs from the host builder's (binned SAH), the traversal result does not: k_extend returns the argmin
 // over all primitives whatever the tree (tests/test_gpu_parity.py compares with the brute force bit for bit).

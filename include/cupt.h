@@ -168,7 +168,7 @@ int cupt_read_bvh(cupt_context* c, void* nodes80, void* tris48, int64_t* counts)
 /* test hook: the stable LSD radix sort the build uses for the Morton order (csrc/radix_sort.cuh), on host pairs, in
  * place; sorts on key bits [63 - 8 * passes, 63), passes = 1..8 */
 int cupt_debug_sort_pairs(cupt_context* c, uint64_t* keys, uint32_t* vals, int64_t n, int passes);
-/* the build workspace (about 180 B per primitive) stays allocated between builds; this frees it */
+/* the build workspace (about 270 B per primitive) stays allocated between builds; this frees it */
 int cupt_release_workspace(cupt_context* c);
 /* CUDA-event times of the last cupt_build_bvh_device in ms: {total, boxes+Morton+sort, clustering, collapse+emit} */
 int cupt_get_build_times(cupt_context* c, float* ms4);
