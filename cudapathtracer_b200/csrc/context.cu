@@ -341,6 +341,9 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel, bool
 		int per_sm = 0;
 		CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
 		if (per_sm < 1) return set_error(CUPT_ERR_LIMIT, "the extend kernel does not fit an SM with a traversal stack of %d entries (%zu bytes of shared memory per block)", sc.stack_cap, smem);
+#ifdef CUPT_EXTEND_MAX_BLOCKS   // experiment: leave room on every SM for another stream's kernels
+		per_sm = std::min(per_sm, CUPT_EXTEND_MAX_BLOCKS);
+#endif
 		blocks = per_sm * c->num_sms;
 		sized_for = smem;
 	}
