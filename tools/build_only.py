@@ -16,7 +16,7 @@ if os.environ.get("L2FETCH"):   # experiment: cudaLimitMaxL2FetchGranularity (0x
     print("cudaDeviceSetLimit ->", rt.cudaDeviceSetLimit(5, C.c_size_t(int(os.environ["L2FETCH"]))))
     v = C.c_size_t(0); rt.cudaDeviceGetLimit(C.byref(v), 5); print("L2 fetch granularity now", v.value)
 for _ in range(int(os.environ.get("REPS", "2"))):
-    info = ctx.build_bvh_device()
+    info = ctx.build_bvh_device(radius=int(os.environ.get("RADIUS", "0")))
 print({k: (round(v, 3) if isinstance(v, float) else v) for k, v in info.items()})
 if os.environ.get("HASH") and n <= 40_000_000:   # the tree's bytes (nodes + records), to check that a builder change leaves the trees as they were
     import hashlib
