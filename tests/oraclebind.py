@@ -89,6 +89,13 @@ class OracleScene:
         lib().orc_brute_force(C.byref(self.c), _p(rank), _p(rays), C.c_longlong(len(rays)), _p(ids), _p(ts))
         return ids, ts
 
+    def hits_outside_box(self, rays, rel_tol=1e-3):
+        """per ray: does any triangle report a hit outside its own bounding box (rounding noise of a degenerate triangle)?"""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        flags = np.zeros(len(rays), dtype=np.uint8)
+        lib().orc_hits_outside_box(C.byref(self.c), _p(rays), C.c_longlong(len(rays)), C.c_double(rel_tol), _p(flags))
+        return flags.astype(bool)
+
     def render_pt(self, cam, num_bounces=5, seed=1234, first_sample=0, num_samples=1):
         """(mean[P,3] f64, sum[P,3] f64, rays)"""
         cam = np.ascontiguousarray(cam, dtype=CAMERA)
