@@ -3,6 +3,8 @@
 the positional-halving path BVH.h:263-288), duplicated, collinear and point triangles, one huge triangle among tiny ones, coordinates
 at the edge of the +-1e4 world (BVH.h:21-25).  Node arrays and depth must be equal byte for byte; the leaf order derived from them is
 the tie-break rank the wide BVH carries.  Skips where /root/reference was not available at build time (fixture `ref`)."""
+import os
+
 import numpy as np
 import pytest
 from hypothesis import HealthCheck, given, settings, strategies as st
@@ -12,7 +14,7 @@ from test_bvh8_property import tiny_scenes
 
 
 @pytest.mark.timeout(600)
-@settings(max_examples=200, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
+@settings(max_examples=int(os.environ.get("CUPT_FUZZ_EXAMPLES", "200")), deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
 @given(tiny_scenes(), st.integers(1, 6))
 def test_generated_scenes_build_the_reference_tree(lib, ref, scene, copies):
     v, idx, seed = scene

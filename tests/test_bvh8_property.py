@@ -9,6 +9,8 @@ ones, coordinates at the edge of the reference's +-1e4 world (BVH.h:21-25); rays
 edges and vertices), axis-parallel rays (1/0 in the slab test), rays starting on a triangle's plane."""
 import ctypes as C
 
+import os
+
 import numpy as np
 import pytest
 from hypothesis import HealthCheck, given, settings, strategies as st
@@ -83,7 +85,7 @@ def make_rays(v, idx, seed, n=160):
     return np.concatenate(rays).astype(np.float32)
 
 
-@settings(max_examples=300, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
+@settings(max_examples=int(os.environ.get("CUPT_FUZZ_EXAMPLES", "300")), deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
 @given(tiny_scenes(), st.sampled_from([1, 3]), st.sampled_from([-1, 0]))
 def test_wide_traversal_equals_brute_force_on_any_scene(lib, oracle, emul, scene, max_leaf, reinsert):
     v, idx, seed = scene

@@ -6,6 +6,8 @@ Needs /root/reference at build time, so it runs in the authoring container and s
 What is varied: the spelling of numbers (sign, leading '.', trailing '.', exponents, many digits, leading zeros, values that underflow
 or are huge), index spellings (v, v/vt, v/vt/vn, v//vn, negative = relative), polygons (fans), shape splits (g / o / usemtl), white
 space (tabs, runs of blanks, trailing blanks, CRLF), comments and blank lines, the order and presence of Kd / Ke / Ka in the MTL."""
+import os
+
 import numpy as np
 import pytest
 from hypothesis import HealthCheck, given, settings, strategies as st
@@ -98,7 +100,7 @@ def obj_files(draw):
     return obj, mtl
 
 
-@settings(max_examples=250, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
+@settings(max_examples=int(os.environ.get("CUPT_FUZZ_EXAMPLES", "250")), deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
 @given(obj_files(), st.sampled_from([((0.0, 0.0, 0.0), 1.0, False), ((0.35, -2.0, 1e3), 0.75, True)]))
 def test_generated_obj_files_load_like_the_reference(lib, ref, tmp_path_factory, files, xform):
     obj, mtl = files
