@@ -329,7 +329,7 @@ int launch_extend(cupt_context* c, const DevScene& sc, int depth, int qsel, bool
 	const size_t smem = mode == 0 ? (size_t)sc.stack_cap * 128 * sizeof(uint2) + 128 * 16 : 0;   // stacks + per-warp keys/list/ids
 	ExtendTuning tune;
 	tune.fetch_thresh = c->opts.fetch_threshold > 0 ? std::min(c->opts.fetch_threshold, 31) : 24;
-	tune.defer_pairs = c->opts.defer_pairs > 0 ? std::min(c->opts.defer_pairs, 64) : 16;
+	tune.defer_pairs = c->opts.defer_pairs > 0 ? std::min(c->opts.defer_pairs, 64) : 20;
 	tune.qbias_bits = CUPT_QBIAS_BITS;
 	void (*kern)(DevScene, PathBuffers, int, int, ExtendTuning) =
 		mode == 0 ? (vis ? (stats ? k_extend<0, true, true> : k_extend<0, false, true>) : (stats ? k_extend<0, true, false> : k_extend<0, false, false>))
@@ -1131,7 +1131,7 @@ int cupt_trace_rays_noalloc(cupt_context* c, const float* rays, int64_t n, int32
 	}
 	ExtendTuning tune;
 	tune.fetch_thresh = c->opts.fetch_threshold > 0 ? std::min(c->opts.fetch_threshold, 31) : 24;
-	tune.defer_pairs = c->opts.defer_pairs > 0 ? std::min(c->opts.defer_pairs, 64) : 16;
+	tune.defer_pairs = c->opts.defer_pairs > 0 ? std::min(c->opts.defer_pairs, 64) : 20;
 	tune.qbias_bits = CUPT_QBIAS_BITS;
 	// the caller's pointers may be host or device memory (unified addressing decides); device pointers involve no host staging
 	CK(cudaMemcpyAsync(d_rays, rays, (size_t)m * 6 * sizeof(float), cudaMemcpyDefault, c->stream));

@@ -183,6 +183,9 @@ struct ExtendTuning {
 #ifndef CUPT_EXTEND_MIN_BLOCKS
 #define CUPT_EXTEND_MIN_BLOCKS 7
 #endif
+#ifndef CUPT_WAIT_LANES
+#define CUPT_WAIT_LANES 32   // primitive phase of extend_wide: a round is forced once this many lanes wait for one (1 = the round-1 rule: any)
+#endif
 #ifndef CUPT_NODE_FAST
 #define CUPT_NODE_FAST 1   // 0: the hot kernel uses wide_node_step (the definition) instead of wide_node_step_fast
 #endif
@@ -240,7 +243,11 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 		if (act == 0u) break;
 
 		// ---- node step ------------------------------------------------------------------------------------------
+#if CUPT_WAIT_LANES > 1
+		if (active && group_has_node(ngroup) && !(tgroup.y != 0u && pgroup.y != 0u)) {   // (a lane holding two primitive groups waits for the flush)
+#else
 		if (active && group_has_node(ngroup)) {   // (only node groups are ever pushed, so a popped group always has one)
+#endif
 			uint2 rest;
 #if CUPT_NODE_FAST
 			wide_node_step_fast(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits, perm + (r.oct_inv << 8), nib);
@@ -264,9 +271,17 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 			if (total0 != 0u) {
 				const bool last = !group_has_node(ngroup) && sp == 0;        // this ray ends after the iteration
 				const bool clash = tgroup.y != 0u && pgroup.y != 0u;         // both slots taken
+#if CUPT_WAIT_LANES > 1
+				// a lane that cannot go on without its tests (its ray would end, or it holds two groups) WAITS instead of forcing a
+				// round for the whole warp, until CUPT_WAIT_LANES lanes wait, the warp holds defer_pairs pairs or nobody else moves
+				const bool waiting = cnt0 != 0u && (last || clash);
+				const uint32_t wmask = __ballot_sync(FULL, waiting);
+				const bool flush = total0 >= (uint32_t)tune.defer_pairs || __popc(wmask) >= CUPT_WAIT_LANES || !__any_sync(FULL, active && !waiting);
+#else
 				const bool flush = total0 >= (uint32_t)tune.defer_pairs || __any_sync(FULL, cnt0 != 0u && (last || clash));
+#endif
 				if (!flush) {
-					if (active && tgroup.y != 0u) { pgroup = tgroup; tgroup.y = 0u; }
+					if (active && tgroup.y != 0u && pgroup.y == 0u) { pgroup = tgroup; tgroup.y = 0u; }
 				} else {
 					for (;;) {
 						const uint32_t cnt = active ? (uint32_t)(__popc(tgroup.y) + __popc(pgroup.y)) : 0u;
@@ -360,8 +375,13 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 		if (VIS && active && r.best < tstop) { ngroup.y = 0u; tgroup.y = 0u; pgroup.y = 0u; sp = 0; }   // an occluder is known: whatever is nearer changes nothing
 		if (active && !group_has_node(ngroup)) {
 			if (sp == 0) {     // (a ray that ends has had its pending primitives flushed above)
-				reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(r.best, __int_as_float(r.best_id));
-				active = false;
+#if CUPT_WAIT_LANES > 1
+				if ((tgroup.y | pgroup.y) == 0u)
+#endif
+				{
+					reinterpret_cast<float2*>(&pb.rayB[slot])[1] = make_float2(r.best, __int_as_float(r.best_id));
+					active = false;
+				}
 			} else {
 				--sp;
 				ngroup = stack[sp * stride];
@@ -638,6 +658,7 @@ __global__ void __launch_bounds__(256, CUPT_SHADE_MIN_BLOCKS) k_shade(DevScene s
 			const uint32_t qn = qi + gridDim.x * blockDim.x;
 			if (qn < count) slot_next = qin[qn];
 		}
+
 		if (qi < count) {
 			const float4 ra = pb.rayA[slot], rb = pb.rayB[slot], s0 = pb.st0[slot];
 			const f3 o = mk3(ra.x, ra.y, ra.z), d = mk3(ra.w, rb.x, rb.y);

@@ -200,7 +200,7 @@ typedef struct cupt_render_opts {
 	int32_t collect_stats;    /* 1: count node visits / triangle tests (slower; for the roofline's bytes/ray) */
 	int32_t time_stages;      /* 1: CUDA events around every stage launch */
 	int32_t fetch_threshold;  /* extend: refill idle lanes of a warp from the ray queue when <= this many are busy (0 = default 24) */
-	int32_t defer_pairs;      /* extend: hold primitive tests one traversal step while a warp has fewer (ray, primitive) pairs than this (0 = default 16, 1 = never) */
+	int32_t defer_pairs;      /* extend: hold primitive tests one traversal step while a warp has fewer (ray, primitive) pairs than this (0 = default 20, 1 = never) */
 	int32_t share_primary_hits; /* 1: with a pinhole camera (radius == 0, the reference's setting, kernel.cu:646) every sample of a
 	                             * pixel has the same primary ray: trace it once per pixel and pass and reuse the hit.  Same image
 	                             * bit for bit, fewer rays traced (and counted).  Default 0; CUPT_INTEGRATOR_PT and CUPT_TRAVERSAL_WIDE
