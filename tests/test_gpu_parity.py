@@ -741,3 +741,35 @@ def test_last_segment_early_stop_changes_nothing(ctx, get_case, name):
     assert ra == rb > 0   # every ray is still traced, only some of them less far
     assert a.sum() > 0 and abs(float(a.sum()) - float(b.sum())) <= 1e-3 * float(a.sum())
 
+
+
+@pytest.mark.parametrize("name", ["atrium20k", "soup5k"])
+def test_extend_tuning_changes_no_hit_and_no_image(ctx, get_case, name):
+    """fetch_threshold (when idle lanes are refilled) and defer_pairs (how many (ray, primitive) pairs a warp collects before a
+    shared test round; lanes that cannot go on without their tests wait for it) schedule the work of k_extend's warps and must
+    not show in any result: the closest hit is an argmin with a total tie-break order, whichever lane tests which pair when.
+    1 pair = a round in every iteration, 64 = rounds only when nothing else can move (every lane waiting)."""
+    c = get_case(name)
+    rng = np.random.default_rng(17)
+    pos = c.verts.view(np.float32).reshape(-1, 3)
+    o = rng.uniform(pos.min(0), pos.max(0), size=(40000, 3))
+    d = rng.normal(size=(40000, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.concatenate([o, d], axis=1).astype(np.float32)
+    base = None
+    try:
+        for ft, dp in [(0, 0), (1, 1), (8, 1), (31, 1), (24, 8), (24, 31), (31, 64), (4, 64), (16, 33)]:
+            for integ in (api.INTEGRATOR_PT, api.INTEGRATOR_BDPT):
+                load(ctx, c, api.TRAVERSAL_WIDE, max_depth=5, seed=3, integrator=integ, fetch_threshold=ft, defer_pairs=dp, collect_stats=0)
+                ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 4)
+                got = (ctx.trace_rays(rays), ctx.read_accum(False).tobytes(), ctx.stats()["rays"], integ)
+                if base is None or base[integ] is None:
+                    base = base or {api.INTEGRATOR_PT: None, api.INTEGRATOR_BDPT: None}
+                    base[integ] = got
+                    continue
+                ref = base[integ]
+                assert hits_equal(got[0], ref[0]), (ft, dp, integ)
+                assert got[1] == ref[1] and got[2] == ref[2], (ft, dp, integ)
+    finally:
+        ctx.set_options(fetch_threshold=0, defer_pairs=0, integrator=api.INTEGRATOR_PT)
+    bi, bt = c.osc.brute_force(rays, c.rank)
+    assert np.array_equal(base[api.INTEGRATOR_PT][0][0], bi) and base[api.INTEGRATOR_PT][0][1].tobytes() == bt.tobytes()
