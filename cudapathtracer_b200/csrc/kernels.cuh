@@ -275,8 +275,12 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 				// a lane that cannot go on without its tests (its ray would end, or it holds two groups) WAITS instead of forcing a
 				// round for the whole warp, until CUPT_WAIT_LANES lanes wait, the warp holds defer_pairs pairs or nobody else moves
 				const bool waiting = cnt0 != 0u && (last || clash);
+#if CUPT_WAIT_LANES >= 32
+				const bool flush = total0 >= (uint32_t)tune.defer_pairs || !__any_sync(FULL, active && !waiting);
+#else
 				const uint32_t wmask = __ballot_sync(FULL, waiting);
 				const bool flush = total0 >= (uint32_t)tune.defer_pairs || __popc(wmask) >= CUPT_WAIT_LANES || !__any_sync(FULL, active && !waiting);
+#endif
 #else
 				const bool flush = total0 >= (uint32_t)tune.defer_pairs || __any_sync(FULL, cnt0 != 0u && (last || clash));
 #endif
