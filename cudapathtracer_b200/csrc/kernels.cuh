@@ -186,9 +186,6 @@ struct ExtendTuning {
 #ifndef CUPT_WAIT_LANES
 #define CUPT_WAIT_LANES 32   // primitive phase of extend_wide: a round is forced once this many lanes wait for one (1 = the round-1 rule: any)
 #endif
-#ifndef CUPT_PRIM_PREFETCH
-#define CUPT_PRIM_PREFETCH 0
-#endif
 #ifndef CUPT_NODE_FAST
 #define CUPT_NODE_FAST 1   // 0: the hot kernel uses wide_node_step (the definition) instead of wide_node_step_fast
 #endif
@@ -259,19 +256,6 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 #endif
 			if (group_has_node(rest)) { stack[sp * stride] = rest; ++sp; }
 			if (STATS) ++n_nodes;
-#if CUPT_PRIM_PREFETCH && CUPT_NODE_FAST
-			// the records of the leaves just hit are tested an iteration or more from now (deferral, waiting): start their fetch
-			if (tgroup.y != 0u) {
-				const uint2 tv = node_records(sc.nodes, tgroup.x);   // (an L1 hit: the node was fetched a moment ago)
-				const float4* pp = sc.prims + (size_t)sparse_record(tv, __ffs(tgroup.y) - 1u) * 3u;
-#if CUPT_PRIM_PREFETCH == 2
-				asm volatile("prefetch.global.L1 [%0];" :: "l"(pp));
-#else
-				asm volatile("prefetch.global.L2 [%0];" :: "l"(pp));
-#endif
-			}
-#endif
-		}
 		// ---- primitive tests, shared across the warp ----------------------------------------------------------------
 		// Lanes with pending primitives are few (3.2 of 32 in profiles/r1c, where this phase took 40 % of the issue
 		// slots), so the (ray, primitive) pairs of the whole warp are listed in shared memory and every lane tests
