@@ -256,6 +256,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 #endif
 			if (group_has_node(rest)) { stack[sp * stride] = rest; ++sp; }
 			if (STATS) ++n_nodes;
+		}
 		// ---- primitive tests, shared across the warp ----------------------------------------------------------------
 		// Lanes with pending primitives are few (3.2 of 32 in profiles/r1c, where this phase took 40 % of the issue
 		// slots), so the (ray, primitive) pairs of the whole warp are listed in shared memory and every lane tests
