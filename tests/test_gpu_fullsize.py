@@ -6,6 +6,8 @@ reference by tests/test_oracle.py) — not GPU mode against GPU mode:
              differs from the reference is one the strict mode lists as "the reference would not have reached this hit";
              radiance of the three modes against the oracle's integrator, the bench's own mode (wide, last-segment early
              stop on) included
+             the reference's LIVE integrator (BDPT, kernel.cu:217-415) at the same size: three modes against the oracle's
+             restatement of it
   config 3   the same scene at 3840 x 2160: the only check of the 8x4 tile-major slot indexing on a non-square,
              non-power-of-two image (the reference's 16-bit Morton map, camera.h:57-65, cannot express it)
   config 1   Cornell box at 256 x 256, 16 spp, depth 5, seed 1234 — triangle-only (parity pinned) and with the two
@@ -144,6 +146,41 @@ def test_config2_radiance_vs_oracle(ctx, full, spp, seed):
     # rays: zero-weight paths are dropped instead of traced to the end, never more than the reference traces
     assert 0.5 * orays < ctx.stats()["rays"] <= orays
     ctx.set_options(collect_stats=0)
+
+
+def test_config2_bdpt_vs_oracle(ctx, full):
+    """The reference's LIVE integrator (radianceAlongSingleStep, kernel.cu:217-415 — what drawPixel calls at HEAD) at config 2's
+    size: 1024 x 1024, 1 spp, seed 1234, against the oracle's restatement of it (bit-exact against the compiled reference,
+    tests/test_oracle.py).  Reference-exact traversal modes: 99.9 % of the pixels within 1e-3 (1 + ref), relative RMSE 1 %, and the
+    reference's ray count to 1e-5; the wide mode the same on the pixels none of whose rays the strict mode re-traced, its ray
+    count within 0.2 % (a path that continues differently makes different connections)."""
+    cam = api.make_camera(1024, 1024, **full.sc.camera)
+    _, osum, orays = full.osc.render_bdpt(cam, 1234, 0, 1)
+    want = osum
+    imgs = {}
+    for mode in (api.TRAVERSAL_REF_BVH2, api.TRAVERSAL_WIDE_STRICT):
+        full.load(ctx, cam, mode, integrator=api.INTEGRATOR_BDPT, seed=1234, collect_stats=1, record_retraces=int(mode == api.TRAVERSAL_WIDE_STRICT))
+        ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 1)
+        imgs[mode] = ctx.read_accum(False)
+        f, rel, dm = image_stats(imgs[mode], want)
+        print(f"config 2 BDPT mode {mode}: {f:.6f} of the pixels within tolerance, rel. RMSE {rel:.2e}, rays {ctx.stats()['rays']} (reference {orays})")
+        assert f >= 0.999 and rel <= 0.01 and dm <= 0.001, (mode, f, rel, dm)
+        # (a connection gets its visibility ray when its weight exceeds 0.01, kernel.cu:396: a device sinf / cosf ulp moves a
+        # handful of weights across that threshold — 2 of 5.8 M rays here; the small cases of test_gpu_parity.py agree exactly)
+        assert abs(ctx.stats()["rays"] - orays) <= 1e-5 * orays
+    assert imgs[api.TRAVERSAL_REF_BVH2].tobytes() == imgs[api.TRAVERSAL_WIDE_STRICT].tobytes()
+    clean = ctx.read_retrace_counts() == 0
+    assert clean.mean() >= 0.99
+    full.load(ctx, cam, api.TRAVERSAL_WIDE, integrator=api.INTEGRATOR_BDPT, seed=1234, collect_stats=1)
+    ctx.reset_accum(); ctx.reset_stats(); ctx.render(0, 1)
+    wide = ctx.read_accum(False)
+    f, rel, dm = image_stats(wide, want, clean)
+    print(f"config 2 BDPT WIDE, pixels without a re-traced ray ({clean.mean():.4f} of all): {f:.6f} within tolerance, rel. RMSE {rel:.2e}")
+    assert f >= 0.999 and rel <= 0.01 and dm <= 0.001, (f, rel, dm)
+    f_all, _, dm_all = image_stats(wide, want)
+    assert f_all >= 0.99 and dm_all <= 0.01, (f_all, dm_all)
+    assert abs(ctx.stats()["rays"] - orays) <= 0.002 * orays
+    ctx.set_options(integrator=api.INTEGRATOR_PT, collect_stats=0, record_retraces=0)
 
 
 def test_config1_full_size(ctx, get_case, oracle):
