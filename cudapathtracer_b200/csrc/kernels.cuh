@@ -263,8 +263,9 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 		// one pair: lane i fetches the owner's ray by shuffle, runs the exact test and merges its hit into the
 		// owner's 64-bit key (t bits << 32 | rank) with a shared-memory atomicMin, which is the acceptance rule
 		// `t < best || (t == best && rank < best_rank)` because positive floats order like their bit patterns.
-		// A warp that holds fewer than `defer_pairs` pairs keeps them one iteration (tgroup -> pgroup) unless a ray
-		// would end or a lane would need a third group, so that a round runs with more lanes (10.7 in profiles/r1e).
+		// A warp that holds fewer than `defer_pairs` pairs keeps them (tgroup -> pgroup).  A lane that cannot go on without its
+		// tests — its ray would end, or it would need a third group — waits for the round instead of forcing one (round 1 forced
+		// it, which was the case in most iterations: rounds at 15 lanes, now 23; profiles/r2ba_extend_lines.txt).
 		{
 			const uint32_t cnt0 = active ? (uint32_t)(__popc(tgroup.y) + __popc(pgroup.y)) : 0u;
 			const uint32_t total0 = __reduce_add_sync(FULL, cnt0);
