@@ -573,6 +573,12 @@ def write_ppm(path: str, rgb_mean: np.ndarray, width: int, height: int):
     _check(load_library().cupt_write_ppm(path.encode(), _ptr(rgb_mean), width, height))
 
 
+def write_pfm(path: str, rgb: np.ndarray, width: int, height: int):
+    rgb = np.ascontiguousarray(rgb, dtype=np.float32)
+    assert rgb.size == width * height * 3
+    _check(load_library().cupt_write_pfm(path.encode(), _ptr(rgb), width, height))
+
+
 def write_ppm8(path: str, rgb8: np.ndarray):
     rgb8 = np.ascontiguousarray(rgb8, dtype=np.uint8)
     _check(load_library().cupt_write_ppm8(path.encode(), _ptr(rgb8), rgb8.shape[1], rgb8.shape[0]))

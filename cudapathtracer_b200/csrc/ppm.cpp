@@ -60,4 +60,22 @@ int cupt_write_ppm8(const char* path, const uint8_t* rgb, int width, int height)
 	return rc == 0 ? CUPT_OK : set_error(CUPT_ERR_IO, "write to %s failed", path);
 }
 
+// The raw accumulator as a Portable Float Map ("PF", three f32 per pixel, little-endian = negative scale, rows bottom to top by
+// the format's convention): no tonemap, no mirroring, every bit of the image survives the file.  SURVEY 8(f) rank 4; the
+// reference itself only writes the tonemapped P3 text (kernel.cu:763-778).
+int cupt_write_pfm(const char* path, const float* rgb, int width, int height)
+{
+	if (!path || !rgb || width <= 0 || height <= 0)
+		return set_error(CUPT_ERR_INVALID, "bad arguments");
+	FILE* fp = fopen(path, "wb");
+	if (!fp)
+		return set_error(CUPT_ERR_IO, "cannot open %s for writing", path);
+	fprintf(fp, "PF\n%d %d\n-1.0\n", width, height);
+	size_t written = 0;
+	for (int y = height - 1; y >= 0; --y)
+		written += fwrite(rgb + 3 * (size_t)y * width, sizeof(float), 3 * (size_t)width, fp);
+	int rc = fclose(fp);
+	return (rc == 0 && written == 3 * (size_t)width * height) ? CUPT_OK : set_error(CUPT_ERR_IO, "write to %s failed", path);
+}
+
 }  // extern "C"

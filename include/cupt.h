@@ -310,6 +310,9 @@ int cupt_write_ppm(const char* path, const float* rgb_mean, int width, int heigh
  * the reference's writer (kernel.cu:768).  rgb: width*height*3 bytes, row-major. */
 int cupt_read_image_rgb8(cupt_context* c, uint8_t* rgb, int mirror_x);
 int cupt_write_ppm8(const char* path, const uint8_t* rgb, int width, int height);   /* P3 text like kernel.cu:763-778, no mirroring */
+/* the float image itself as a Portable Float Map (binary "PF", little-endian, rows bottom to top): what cupt_read_accum returned,
+ * bit for bit, for tools that want the radiance and not the reference's 8-bit tonemapped text (kernel.cu:763-778 has no such output) */
+int cupt_write_pfm(const char* path, const float* rgb, int width, int height);
 /* traversal-cost heat map of the primary rays: wide-BVH nodes visited / primitives tested per pixel (the reference's
  * per-ray step counter, kernel.cu:121,132,152, which drew keepers/"sponza bvh.ppm").  Either pointer may be NULL. */
 int cupt_read_heatmap(cupt_context* c, float* nodes_visited, float* prims_tested);

@@ -115,6 +115,23 @@ def test_ppm_writer_matches_reference_tonemap(lib, tmp_path):
     assert np.array_equal(vals[:, ::-1, :].reshape(-1, 3), out[: w * h])   # x mirrored, kernel.cu:768
 
 
+def test_pfm_writer_keeps_every_bit(lib, tmp_path):
+    """cupt_write_pfm: binary "PF" header, little-endian scale, rows bottom to top; NaN / inf / denormals / -0 survive"""
+    rng = np.random.default_rng(4)
+    w, h = 13, 7
+    img = rng.standard_normal((h, w, 3)).astype(np.float32) * 1e3
+    img[0, 0] = [np.nan, np.inf, -0.0]; img[1, 2] = [1e-45, -1e-45, 3.4e38]
+    p = tmp_path / "img.pfm"
+    api.write_pfm(str(p), img, w, h)
+    raw = p.read_bytes()
+    head = b"PF\n13 7\n-1.0\n"
+    assert raw.startswith(head) and len(raw) == len(head) + w * h * 12
+    back = np.frombuffer(raw[len(head):], dtype="<f4").reshape(h, w, 3)[::-1]
+    assert back.tobytes() == img.tobytes()
+    with pytest.raises(api.CuptError):
+        api.write_pfm(str(tmp_path / "no" / "dir.pfm"), img, w, h)
+
+
 TWO_MAT_OBJ = """mtllib s.mtl
 v 0 0 0
 v 1 0 0
