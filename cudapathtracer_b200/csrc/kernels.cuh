@@ -186,6 +186,9 @@ struct ExtendTuning {
 #ifndef CUPT_WAIT_LANES
 #define CUPT_WAIT_LANES 32   // primitive phase of extend_wide: a round is forced once this many lanes wait for one (1 = the round-1 rule: any)
 #endif
+#ifndef CUPT_NODE_STEPS
+#define CUPT_NODE_STEPS 2   // node steps (and the pops between them) per look at the primitive groups and the queue; 1 = one, the loop up to r2ba
+#endif
 #ifndef CUPT_NODE_FAST
 #define CUPT_NODE_FAST 1   // 0: the hot kernel uses wide_node_step (the definition) instead of wide_node_step_fast
 #endif
@@ -243,6 +246,20 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 		if (act == 0u) break;
 
 		// ---- node step ------------------------------------------------------------------------------------------
+#if CUPT_NODE_STEPS > 1
+		// CUPT_NODE_STEPS node steps (with the pops between them) per look at the primitive groups and the queue
+#pragma unroll 1
+		for (int rep = 0; rep < CUPT_NODE_STEPS; ++rep) {
+			if (rep > 0 && active && !group_has_node(ngroup) && sp > 0) { --sp; ngroup = stack[sp * stride]; }
+			if (active && group_has_node(ngroup) && !(tgroup.y != 0u && pgroup.y != 0u)) {
+				if (tgroup.y != 0u) { pgroup = tgroup; }   // (pgroup is free here; the step overwrites tgroup)
+				uint2 rest;
+				wide_node_step_fast(sc.nodes, r, ngroup, rest, tgroup, tune.qbias_bits, perm + (r.oct_inv << 8), nib);
+				if (group_has_node(rest)) { stack[sp * stride] = rest; ++sp; }
+				if (STATS) ++n_nodes;
+			}
+		}
+#else
 #if CUPT_WAIT_LANES > 1
 		if (active && group_has_node(ngroup) && !(tgroup.y != 0u && pgroup.y != 0u)) {   // (a lane holding two primitive groups waits for the flush)
 #else
@@ -257,6 +274,7 @@ __device__ __forceinline__ void extend_wide(const DevScene& sc, const PathBuffer
 			if (group_has_node(rest)) { stack[sp * stride] = rest; ++sp; }
 			if (STATS) ++n_nodes;
 		}
+#endif
 		// ---- primitive tests, shared across the warp ----------------------------------------------------------------
 		// Lanes with pending primitives are few (3.2 of 32 in profiles/r1c, where this phase took 40 % of the issue
 		// slots), so the (ray, primitive) pairs of the whole warp are listed in shared memory and every lane tests
