@@ -711,10 +711,11 @@ __global__ void __launch_bounds__(256, CUPT_SHADE_MIN_BLOCKS) k_shade(DevScene s
 				m0 = sc.spheres[3 * si + 1]; m1 = sc.spheres[3 * si + 2];
 			}
 			if (m0.w != 0.f) {                                                      // kernel.cu:453-457
-				// the radiance record is touched only here: a path meets an emitter at most once (its weight is zero after)
-				float4 s1 = pb.st1[slot];
-				s1.x += wr * m1.x; s1.y += wg * m1.y; s1.z += wb * m1.z;
-				pb.st1[slot] = s1;
+				// The radiance record is touched only here, and at most once per path: its weight is zero after (the path is dropped
+				// below), and k_raygen zeroed the record.  So this is a plain store of 0 + w * emission, not a read-modify-write: the
+				// read was the fifth dependent access of the chain queue -> records -> triangle -> material -> radiance record and 10 %
+				// of the kernel's stall samples (profiles/r2bb_shade_lines.txt).  (0 + x: a zero product keeps the sign the sum had.)
+				pb.st1[slot] = make_float4(fmaf(wr, m1.x, 0.0f), fmaf(wg, m1.y, 0.0f), fmaf(wb, m1.z, 0.0f), 0.0f);
 				wr = wg = wb = 0.f;
 			}
 			const bool dead = !(wr != 0.f || wg != 0.f || wb != 0.f);
