@@ -460,7 +460,7 @@ def main():
     host_t = torch.empty((W * H, 3), dtype=torch.float32, pin_memory=True)   # the caller's image buffer: pinned, so the read-back is one DMA
     host_img = host_t.numpy()
     nv, nt, nm, nl, _ = s.counts()
-    h2d = nv * 12 + nt * 28 + nt * 16 + nm * 32 + (nl + 1) * 48 + 32
+    h2d = nv * 12 + nt * 28 + nt * 16 + nm * 56 + (nl + 1) * 48 + 32
     if args.bvh == "host":
         h2d += info["num_nodes"] * 80 + info["num_tri_records"] * 48      # the device builder uploads no tree
     if mode != api.TRAVERSAL_WIDE:

@@ -11,8 +11,7 @@
 //   k_bdpt_connect  light vertex 1, eye vertex 2, the 2 x 2 connection weights in f64 like `color`
 //                   (kernel.cu:353-395), a visibility ray for every weight above 0.01      -> <= 4 rays per path
 //   extend
-//   k_bdpt_resolve  visible iff |t - len| <= 0.01 (kernel.cu:396-405)
-//   k_bdpt_accumulate
+//   k_bdpt_accumulate  visible iff |t - len| <= 0.01 (kernel.cu:396-405), per-pixel sum
 //
 // Ray records live at index 4 * slot + k of rayA / rayB; st0[4 * slot + c] holds connection c's weight and length,
 // st1[slot] four times the primary hit's emission (xyz) and the sampled light triangle (w).  No vertex array is kept
@@ -160,7 +159,10 @@ __global__ void __launch_bounds__(256) k_bdpt_mid(DevScene sc, PassParams pp, Pa
 
 struct dcol { double r, g, b; };   // `color` (color.h:4-6): the reference keeps radiance in f64
 
-__global__ void __launch_bounds__(256) k_bdpt_connect(DevScene sc, PassParams pp, PathBuffers pb)
+#ifndef CUPT_BDPT_CONNECT_BLOCKS
+#define CUPT_BDPT_CONNECT_BLOCKS 4   // 64 registers + 76 spilled bytes instead of 112 / none: mid + connect 11.3 -> 9.3 ms per frame (1 / 3 / 4 / 5 / 6 / 8 blocks: 11.3 / 10.4 / 9.3 / 11.7 / 14.3 / 14.0)
+#endif
+__global__ void __launch_bounds__(256, CUPT_BDPT_CONNECT_BLOCKS) k_bdpt_connect(DevScene sc, PassParams pp, PathBuffers pb, const double* __restrict__ mat_fs /* albedo / 3.14159f per material, f64 (cupt_set_scene) */)
 {
 	__shared__ uint32_t s_warp[9];
 	const uint32_t total = (uint32_t)pp.p_pad * (uint32_t)pp.samples;
@@ -215,7 +217,6 @@ __global__ void __launch_bounds__(256) k_bdpt_connect(DevScene sc, PassParams pp
 			}
 			const float4 me0 = sc.mats[2 * mat[0] + 1];
 			const dcol L_e = {(double)me0.x, (double)me0.y, (double)me0.z};
-			const double inv_pi_f = (double)3.14159f;
 #pragma unroll
 			for (int i = 0; i < 2; ++i)
 #pragma unroll
@@ -228,20 +229,20 @@ __global__ void __launch_bounds__(256) k_bdpt_connect(DevScene sc, PassParams pp
 						const f3 ray = rnormalized(seg);
 						float G = rdiv(fabsf(rmul(rdot(ray, norm[k]), rdot(ray, norm[k - 1]))), rdot(seg, seg));
 						if (G != G) G = 0.0f;
-						const float4 mk = sc.mats[2 * mat[k]];
-						w.r = ((w.r * ((double)mk.x / inv_pi_f)) * (double)G) * (double)invProb[k];
-						w.g = ((w.g * ((double)mk.y / inv_pi_f)) * (double)G) * (double)invProb[k];
-						w.b = ((w.b * ((double)mk.z / inv_pi_f)) * (double)G) * (double)invProb[k];
+						const double* fk = mat_fs + 3 * mat[k];   // f_s = albedo / 3.14159f (kernel.cu:367,379)
+						w.r = ((w.r * fk[0]) * (double)G) * (double)invProb[k];
+						w.g = ((w.g * fk[1]) * (double)G) * (double)invProb[k];
+						w.b = ((w.b * fk[2]) * (double)G) * (double)invProb[k];
 					}
 					const f3 seg = rsub3(x[j], x[i]);
 					const float len = rlength(seg);
 					const f3 ray = rnormalized(seg);
 					float G = rdiv(fmaxf(0.0f, rmul(rdot(ray, norm[j]), rdot(rmul3(ray, -1.0f), norm[i]))), rdot(seg, seg));
 					if (G != G) G = 0.0f;
-					const float4 mj = sc.mats[2 * mat[j]];
-					w.r = ((w.r * ((double)mj.x / inv_pi_f)) * (double)G) * (double)invProb[j];
-					w.g = ((w.g * ((double)mj.y / inv_pi_f)) * (double)G) * (double)invProb[j];
-					w.b = ((w.b * ((double)mj.z / inv_pi_f)) * (double)G) * (double)invProb[j];
+					const double* fj = mat_fs + 3 * mat[j];   // kernel.cu:391
+					w.r = ((w.r * fj[0]) * (double)G) * (double)invProb[j];
+					w.g = ((w.g * fj[1]) * (double)G) * (double)invProb[j];
+					w.b = ((w.b * fj[2]) * (double)G) * (double)invProb[j];
 					const float m = (float)fmax(w.r, fmax(w.g, w.b));
 					const int c = i * 2 + (j - 2);
 					want[c] = (double)m > 0.01;
@@ -275,18 +276,11 @@ __global__ void __launch_bounds__(256) k_bdpt_connect(DevScene sc, PassParams pp
 	}
 }
 
-// visible iff |t - len| <= 0.01 (kernel.cu:396-405); an occluded connection's weight is cleared
-__global__ void __launch_bounds__(256) k_bdpt_resolve(PathBuffers pb)
-{
-	const uint32_t count = pb.counters[2];
-	for (uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x; qi < count; qi += gridDim.x * blockDim.x) {
-		const uint32_t r = pb.queue[0][qi];
-		const float t = pb.rayB[r].z;
-		const float4 w = pb.st0[r];
-		if (!((double)fabsf(rsub(t, w.w)) <= 0.01)) pb.st0[r] = make_float4(0.f, 0.f, 0.f, w.w);
-	}
-}
-
+// The last stage: visibility of the connections (visible iff |t - len| <= 0.01, kernel.cu:396-405: an occluded connection
+// contributes nothing), then the per-pixel sum.  Until r2bc a kernel of its own (k_bdpt_resolve) walked the queue of visibility
+// rays and cleared the weights of the occluded ones — queue entry, hit and weight record read and the weight written back, about
+// 68 bytes per visibility ray at 70 % of the DRAM peak, 0.96 ms per pass — before this one read the weights again.  Now the hit
+// distances are read here, next to the weights (64 more bytes per sample, contiguous), and the test is made on the way to the sum.
 __global__ void __launch_bounds__(256) k_bdpt_accumulate(PassParams pp, PathBuffers pb, float* __restrict__ accum)
 {
 	const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
@@ -299,7 +293,11 @@ __global__ void __launch_bounds__(256) k_bdpt_accumulate(PassParams pp, PathBuff
 		const size_t slot = (size_t)s * pp.p_pad + r;
 		float cr = 0.f, cg = 0.f, cb = 0.f;
 		for (int c = 0; c < 4; ++c) {                   // accum = ((w0 + e) + (w1 + e)) ... in the reference's order
-			const float4 w = pb.st0[slot * 4u + c];
+			float4 w = pb.st0[slot * 4u + c];           // (w.w = connection length; -1: no visibility ray was wanted, weight 0)
+			if (w.w >= 0.f) {
+				const float t = pb.rayB[slot * 4u + c].z;
+				if (!((double)fabsf(rsub(t, w.w)) <= 0.01)) { w.x = 0.f; w.y = 0.f; w.z = 0.f; }
+			}
 			cr += w.x; cg += w.y; cb += w.z;
 		}
 		const float4 e4 = pb.st1[slot];

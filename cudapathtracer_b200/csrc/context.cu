@@ -523,7 +523,18 @@ int cupt_set_scene(cupt_context* c, const cupt_scene* s)
 		mf[i].emissive_flag = s->mats[i].emission[0] != 0 ? 1.f : 0.f;  // kernel.cu:453 tests the f64 value
 		mf[i].specular_flag = (i < s->mat_specular.size() && s->mat_specular[i]) ? 1.f : 0.f;
 	}
-	if ((rc = upload(c, &c->d_mats, mf.data(), nm * sizeof(MatF)))) return rc;
+	// behind the table: f_s = albedo / 3.14159f per material in double, as the live integrator forms it for every vertex of every
+	// connection (kernel.cu:367,379,391: `color` is f64, the division is by (double)3.14159f) — the same IEEE quotient, taken
+	// once per material here instead of 24 times per sample in k_bdpt_connect.  One buffer, so that it travels with the table
+	// wherever that goes (cupt_group's broadcast).
+	std::vector<uint8_t> mbuf(nm * (sizeof(MatF) + 3 * sizeof(double)));
+	if (nm) memcpy(mbuf.data(), mf.data(), nm * sizeof(MatF));
+	for (size_t i = 0; i < nm; ++i)
+		for (int k = 0; k < 3; ++k) {
+			const double fs = (double)mf[i].albedo[k] / (double)3.14159f;
+			memcpy(mbuf.data() + nm * sizeof(MatF) + (3 * i + k) * sizeof(double), &fs, sizeof(double));
+		}
+	if ((rc = upload(c, reinterpret_cast<uint8_t**>(&c->d_mats), mbuf.data(), mbuf.size()))) return rc;
 	// light table: per light v0, a1 = v1 - v0, a2 = v2 - v0 and area = length(cross(a1, a2)) / 2 (kernel.cu:472-477),
 	// plus the fallback entry for `selectedTri = 0` (kernel.cu:469)
 	std::vector<LightTri> lt(nl + 1);
@@ -735,14 +746,16 @@ int cupt_render(cupt_context* c, int first_sample, int num_samples)
 			stage_end(c, ev);
 			if ((rc = launch_extend(c, sc, 1, 1, false, &pp, 4))) return rc;
 			stage_begin(c, 2, ev);
-			k_bdpt_connect<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb);
+			{
+				const size_t nm = c->used[(void**)&c->d_mats] / (sizeof(MatF) + 3 * sizeof(double));   // (the f_s table lies behind the material table)
+				k_bdpt_connect<<<grid, 256, 0, c->stream>>>(sc, pp, c->pb, reinterpret_cast<const double*>(reinterpret_cast<const uint8_t*>(c->d_mats) + nm * sizeof(MatF)));
+			}
 			stage_end(c, ev);
 			if ((rc = launch_extend(c, sc, 2, 0, true, &pp, 4))) return rc;   // visibility rays: t limit + early stop
 			stage_begin(c, 3, ev);
-			k_bdpt_resolve<<<grid, 256, 0, c->stream>>>(c->pb);
 			k_bdpt_accumulate<<<(pp.p_pad + 255) / 256, 256, 0, c->stream>>>(pp, c->pb, c->d_accum);
 			stage_end(c, ev);
-			c->launches += 5;
+			c->launches += 4;
 			CK(cudaGetLastError());
 			c->samples_accumulated += (uint64_t)s_now;
 			continue;
