@@ -164,7 +164,7 @@ struct dcol { double r, g, b; };   // `color` (color.h:4-6): the reference keeps
 #endif
 __global__ void __launch_bounds__(256, CUPT_BDPT_CONNECT_BLOCKS) k_bdpt_connect(DevScene sc, PassParams pp, PathBuffers pb, const double* __restrict__ mat_fs /* albedo / 3.14159f per material, f64 (cupt_set_scene) */)
 {
-	__shared__ uint32_t s_warp[9];
+	__shared__ uint32_t s_warp[33];
 	const uint32_t total = (uint32_t)pp.p_pad * (uint32_t)pp.samples;
 	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += gridDim.x * blockDim.x) {
 		const uint32_t slot = base + threadIdx.x;
@@ -268,11 +268,11 @@ __global__ void __launch_bounds__(256, CUPT_BDPT_CONNECT_BLOCKS) k_bdpt_connect(
 			const float4 me3 = sc.mats[2 * mat[3] + 1];   // accum += emission of the primary hit, four times (kernel.cu:409-410)
 			pb.st1[slot] = make_float4(4.0f * me3.x, 4.0f * me3.y, 4.0f * me3.z, 0.f);
 		}
+		uint32_t qpos[4];
+		block_queue_reserve4(want, &pb.counters[2], s_warp, qpos);
 #pragma unroll
-		for (int c = 0; c < 4; ++c) {
-			const uint32_t p = block_queue_reserve(want[c], &pb.counters[2], s_warp);
-			if (want[c]) pb.queue[0][p] = slot * 4u + (uint32_t)c;
-		}
+		for (int c = 0; c < 4; ++c)
+			if (want[c]) pb.queue[0][qpos[c]] = slot * 4u + (uint32_t)c;
 	}
 }
 

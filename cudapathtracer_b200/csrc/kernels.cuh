@@ -110,6 +110,33 @@ __device__ __forceinline__ uint32_t block_queue_reserve(bool push, uint32_t* cou
 	return pos;
 }
 
+// The same for up to four entries per thread (k_bdpt_connect: one visibility ray per connection): ONE reservation — three
+// barriers and one atomic — instead of four.  The block's entries are laid out connection by connection, as four separate
+// reservations would (a chunk of 64 consecutive queue entries then holds rays of one kind: laid out warp by warp instead, the
+// visibility extend was 0.3 ms per frame slower).  s_cnt: 4 x 8 + 1 words.
+__device__ __forceinline__ void block_queue_reserve4(const bool push[4], uint32_t* counter, uint32_t* s_cnt /* [33] */, uint32_t pos[4])
+{
+	const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+	const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+	for (int c = 0; c < 4; ++c) {
+		const uint32_t m = __ballot_sync(0xffffffffu, push[c]);
+		pos[c] = (uint32_t)__popc(m & lt);
+		if (lane == 0u) s_cnt[c * 8 + w] = (uint32_t)__popc(m);
+	}
+	__syncthreads();
+	if (threadIdx.x == 0u) {
+		uint32_t tot = 0u;
+		for (uint32_t i = 0; i < 4u * (blockDim.x >> 5); ++i) { const uint32_t c = s_cnt[i]; s_cnt[i] = tot; tot += c; }   // (blockDim.x = 256: 8 warps, entries in (connection, warp) order)
+		s_cnt[32] = tot ? atomicAdd(counter, tot) : 0u;
+	}
+	__syncthreads();
+	const uint32_t base = s_cnt[32];
+#pragma unroll
+	for (int c = 0; c < 4; ++c) pos[c] += base + s_cnt[c * 8 + w];
+	__syncthreads();   // s_cnt is reused by the next loop iteration
+}
+
 // ---- raygen --------------------------------------------------------------------------------------------------
 // share_primary: additionally list the slots of the pass's first sample in queue[1] / counters[63] (cupt_render_opts.share_primary_hits)
 __global__ void __launch_bounds__(256) k_raygen(PassParams pp, PathBuffers pb, const bool share_primary = false)
