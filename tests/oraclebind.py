@@ -89,8 +89,9 @@ class OracleScene:
         lib().orc_brute_force(C.byref(self.c), _p(rank), _p(rays), C.c_longlong(len(rays)), _p(ids), _p(ts))
         return ids, ts
 
-    def hits_outside_box(self, rays, rel_tol=1e-3):
-        """per ray: does any triangle report a hit outside its own bounding box (rounding noise of a degenerate triangle)?"""
+    def hits_outside_box(self, rays, rel_tol=4.8e-7):
+        """per ray: does any triangle report a hit outside its own bounding box as the builders pad it (4 ulp per axis) — rounding
+        noise of a (nearly) degenerate triangle, which a tree may or may not see?"""
         rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
         flags = np.zeros(len(rays), dtype=np.uint8)
         lib().orc_hits_outside_box(C.byref(self.c), _p(rays), C.c_longlong(len(rays)), C.c_double(rel_tol), _p(flags))

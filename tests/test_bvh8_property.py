@@ -146,3 +146,36 @@ def test_degenerate_triangle_noise_is_what_it_is_documented_to_be(lib, oracle, e
     assert np.all(ts[noisy] >= bt[noisy])            # with noise: never a nearer hit than exists
     assert noisy[0] and bi[0] == 0 and noisy.sum() >= 1
     print(f"rays with a hit outside its triangle's box: {noisy.sum()} of {len(rays)}, of which the wide traversal differs on {(~same & noisy).sum()}")
+
+
+def test_sliver_triangle_noise_close_to_the_plane(lib, oracle, emul):
+    """The second case the property tests found (round 2, GPU run with 600 examples; tests/golden/sliver_scene.npz is that scene):
+    triangle 17 has vertices (-2, -4, 2), (1, 1, 2) and (-0.5000298, -1.4998645, 2.0000086) — the third one 3e-5 off the segment
+    between the other two — and on ray 170 triIntersect reports t = 0.99888 where the ray meets the triangle's plane at t = 0.999998:
+    a point 0.0033 in front of the triangle's box (which is 8.6e-6 thick on that axis).  The brute force takes it (it is nearer
+    than triangle 15's honest hit at 0.99983); a tree culls the sliver's box, whose entry distance lies behind that hit.  The first
+    version of orc_hits_outside_box allowed 1e-3 of the triangle's largest coordinate (0.004 here) and called this ray clean; the
+    margin is now what rounding explains (4.8e-7 of the magnitudes that enter the plane distance), and the ray is noise."""
+    d = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sliver_scene.npz"))
+    v, idx, seed = d["v"], d["idx"], int(d["seed"])
+    verts = np.ascontiguousarray(v).view(api.VEC3).reshape(-1)
+    tris = np.zeros(len(idx), dtype=api.TRIANGLE)
+    tris["v0"], tris["v1"], tris["v2"] = idx[:, 0], idx[:, 1], idx[:, 2]
+    mats = np.zeros(1, dtype=api.MATERIAL)
+    s = api.SceneHandle(); s.set_arrays(verts, tris, mats, np.zeros(0, np.int32), 0.0)
+    sv, stt, sm, sl = s.arrays()
+    osc = oracle.OracleScene(sv, stt, sm, sl, 0.0, np.zeros(1, api.BVH2_NODE))
+    rays = make_rays(v, idx, seed)
+    bi, bt = osc.brute_force(rays, None)
+    noisy = osc.hits_outside_box(rays)
+    assert bi[170] == 17 and abs(float(bt[170]) - 0.9988839) < 1e-6 and noisy[170]
+    assert not osc.hits_outside_box(rays, 2e-3)[170]            # (0.0033 outside on an axis whose magnitudes are 1 .. 3)
+    for max_leaf in (1, 3):
+        b = s.build_bvh(max_leaf_tris=max_leaf)
+        nodes, prims = b.arrays()
+        for fast in (False, True):
+            ids, ts, _ = emul_trace(emul, nodes, prims, b.info()["depth"], rays, fast=fast)
+            same = (ids == bi) & (ts.view(np.uint32) == bt.view(np.uint32))
+            assert np.all(same[~noisy]) and np.all(ts[noisy] >= bt[noisy])
+        b.close()
+    s.close()

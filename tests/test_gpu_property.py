@@ -21,7 +21,7 @@ def ctx(lib):
     c.close()
 
 
-@settings(max_examples=int(os.environ.get("CUPT_FUZZ_EXAMPLES", "150")), deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
+@settings(max_examples=int(os.environ.get("CUPT_FUZZ_EXAMPLES", "600")), deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
 @given(tiny_scenes(), st.sampled_from([1, 3]))
 def test_gpu_traversal_equals_brute_force_on_any_scene(ctx, oracle, scene, max_leaf):
     v, idx, seed = scene
@@ -56,7 +56,7 @@ def test_gpu_traversal_equals_brute_force_on_any_scene(ctx, oracle, scene, max_l
     s.close()
 
 
-@settings(max_examples=int(os.environ.get("CUPT_FUZZ_EXAMPLES", "150")), deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
+@settings(max_examples=int(os.environ.get("CUPT_FUZZ_EXAMPLES", "600")), deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow], derandomize=True)
 @given(tiny_scenes())
 def test_gpu_reference_modes_equal_trace_on_any_scene(ctx, oracle, scene):
     """REF_BVH2 mode == the oracle's trace() (pinned to the real reference on the same generator by tests/test_trace_fuzz.py) on EVERY
