@@ -1,3 +1,6 @@
+"""Developer tool (GPU box): one line per build of libcupt.so — config 2 through the reference's live integrator (BDPT): frame time by stage, image checksum.
+
+    CUPT_LIB=variants/libcupt_x.so python tools/bdpt_variant_bench.py [label]"""
 import os, sys, time
 sys.path.insert(0, os.getcwd())
 from cudapathtracer_b200 import api, scenes
