@@ -741,7 +741,7 @@ __global__ void __launch_bounds__(256, CUPT_SHADE_MIN_BLOCKS) k_shade(DevScene s
 				// The radiance record is touched only here, and at most once per path: its weight is zero after (the path is dropped
 				// below), and k_raygen zeroed the record.  So this is a plain store of 0 + w * emission, not a read-modify-write: the
 				// read was the fifth dependent access of the chain queue -> records -> triangle -> material -> radiance record and 10 %
-				// of the kernel's stall samples (profiles/r2bb_shade_lines.txt).  (0 + x: a zero product keeps the sign the sum had.)
+				// of the kernel's stall samples (ncu capture before this change; profiles/r2bc_shade_lines.txt is after).  (0 + x: a zero product keeps the sign the sum had.)
 				pb.st1[slot] = make_float4(fmaf(wr, m1.x, 0.0f), fmaf(wg, m1.y, 0.0f), fmaf(wb, m1.z, 0.0f), 0.0f);
 				wr = wg = wb = 0.f;
 			}
